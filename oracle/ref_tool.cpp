@@ -1,0 +1,436 @@
+// oracle/ref_tool.cpp -- TEST INFRASTRUCTURE (not product code).
+//
+// Driver around the UNMODIFIED reference (GTSAM 4.3a0 compiled from
+// /root/reference by oracle/Makefile into oracle/_ref/libgtsam_ref.so).  It
+// reads a flat problem file (GTB1 container, schema in
+// gtsam_petercdev_b200/problem.py), builds the reference's own
+// NonlinearFactorGraph / Values from it and dumps what the parity tests compare
+// against: whitened Jacobians, ordering, clique layout, [R S d] per clique,
+// delta, errors, LM traces, and stage timings for the CPU baseline.
+//
+//   ref_tool <problem.gtb> <out.gtb> key=value ...
+//     mode=linearize | solve | lm | gn | time | symbolic
+//     ordering=colamd|metis|schur|natural|file   (file: array "ordering" in problem)
+//     lambda=<double> diag=0|1                    (solve: LM damping, 0 => none)
+//     ceres=0|1 maxiter=<n> lambda0=<d>           (lm)
+//     iters=<n>                                   (time)
+#include <gtsam/geometry/Cal3Bundler.h>
+#include <gtsam/geometry/PinholeCamera.h>
+#include <gtsam/geometry/Point3.h>
+#include <gtsam/geometry/Pose2.h>
+#include <gtsam/geometry/Pose3.h>
+#include <gtsam/inference/Ordering.h>
+#include <gtsam/inference/Symbol.h>
+#include <gtsam/linear/GaussianBayesTree.h>
+#include <gtsam/linear/GaussianFactorGraph.h>
+#include <gtsam/linear/JacobianFactor.h>
+#include <gtsam/linear/NoiseModel.h>
+#include <gtsam/linear/VectorValues.h>
+#include <gtsam/nonlinear/GaussNewtonOptimizer.h>
+#include <gtsam/nonlinear/LevenbergMarquardtOptimizer.h>
+#include <gtsam/nonlinear/NonlinearFactorGraph.h>
+#include <gtsam/nonlinear/PriorFactor.h>
+#include <gtsam/nonlinear/Values.h>
+#include <gtsam/nonlinear/internal/LevenbergMarquardtState.h>
+#include <gtsam/slam/BetweenFactor.h>
+#include <gtsam/slam/GeneralSFMFactor.h>
+
+#include <chrono>
+#include <fstream>
+#include <iostream>
+#include <sstream>
+
+#include "gtb_io.h"
+
+using namespace gtsam;
+typedef PinholeCamera<Cal3Bundler> Camera;
+typedef GeneralSFMFactor<Camera, Point3> SfmFactor;
+
+static std::map<std::string, std::string> g_opt;
+static std::string opt(const std::string& k, const std::string& d) {
+  auto it = g_opt.find(k);
+  return it == g_opt.end() ? d : it->second;
+}
+static double optd(const std::string& k, double d) {
+  auto it = g_opt.find(k);
+  return it == g_opt.end() ? d : std::stod(it->second);
+}
+
+static SharedNoiseModel make_noise(int kind, const double* p, int d) {
+  switch (kind) {
+    case 0: return noiseModel::Unit::Create(d);
+    case 1: return noiseModel::Isotropic::Sigma(d, p[0]);
+    case 2: { Vector s(d); for (int i = 0; i < d; ++i) s(i) = p[i]; return noiseModel::Diagonal::Sigmas(s); }
+    case 5: { Vector s(d); for (int i = 0; i < d; ++i) s(i) = p[i]; return noiseModel::Diagonal::Variances(s); }
+    case 3: case 4: {
+      Matrix M(d, d);
+      for (int i = 0; i < d; ++i) for (int j = 0; j < d; ++j) M(i, j) = p[i * d + j];
+      return kind == 3 ? noiseModel::Gaussian::Information(M) : noiseModel::Gaussian::SqrtInformation(M);
+    }
+  }
+  throw std::runtime_error("bad noise kind");
+}
+static Pose2 mk_pose2(const double* p) { return Pose2(p[0], p[1], p[2]); }
+static Pose3 mk_pose3(const double* p) {
+  Matrix3 R;
+  R << p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8];
+  return Pose3(Rot3(R), Point3(p[9], p[10], p[11]));
+}
+static Camera mk_cam(const double* p) {
+  return Camera(mk_pose3(p), Cal3Bundler(p[12], p[13], p[14], p[15], p[16]));
+}
+
+struct Built {
+  NonlinearFactorGraph graph;
+  Values values;
+  // per bucket: graph index of each factor
+  std::vector<std::vector<size_t>> where = std::vector<std::vector<size_t>>(7);
+};
+
+static const char* kBucket[7] = {"between2", "between3", "sfm", "prior2", "prior3", "priorcam", "priorpt"};
+static const int kZ[7] = {3, 12, 2, 3, 12, 17, 3};
+static const int kDim[7] = {3, 6, 2, 3, 6, 9, 3};
+
+static NonlinearFactor::shared_ptr make_factor(const gtbio::File& P, int b, size_t i) {
+  std::string n = kBucket[b];
+  const auto& keys = P.at(n + "_keys");
+  const double* z = P.at(n + "_z").f64() + i * kZ[b];
+  int d = kDim[b];
+  int kind = P.at(n + "_nk").i32()[i];
+  const double* np = P.at(n + "_noise").f64() + i * d * d;
+  auto model = make_noise(kind, np, d);
+  const uint64_t* k = keys.u64() + i * (b < 3 ? 2 : 1);
+  switch (b) {
+    case 0: return std::make_shared<BetweenFactor<Pose2>>(k[0], k[1], mk_pose2(z), model);
+    case 1: return std::make_shared<BetweenFactor<Pose3>>(k[0], k[1], mk_pose3(z), model);
+    case 2: return std::make_shared<SfmFactor>(Point2(z[0], z[1]), model, k[0], k[1]);
+    case 3: return std::make_shared<PriorFactor<Pose2>>(k[0], mk_pose2(z), model);
+    case 4: return std::make_shared<PriorFactor<Pose3>>(k[0], mk_pose3(z), model);
+    case 5: return std::make_shared<PriorFactor<Camera>>(k[0], mk_cam(z), model);
+    case 6: return std::make_shared<PriorFactor<Point3>>(k[0], Point3(z[0], z[1], z[2]), model);
+  }
+  throw std::runtime_error("bad bucket");
+}
+
+static Built build(const gtbio::File& P) {
+  Built B;
+  if (P.has("pose2_keys")) {
+    const auto& k = P.at("pose2_keys");
+    for (size_t i = 0; i < k.rows(); ++i) B.values.insert(k.u64()[i], mk_pose2(P.at("pose2").f64() + 3 * i));
+  }
+  if (P.has("pose3_keys")) {
+    const auto& k = P.at("pose3_keys");
+    for (size_t i = 0; i < k.rows(); ++i) B.values.insert(k.u64()[i], mk_pose3(P.at("pose3").f64() + 12 * i));
+  }
+  if (P.has("cam_keys")) {
+    const auto& k = P.at("cam_keys");
+    for (size_t i = 0; i < k.rows(); ++i) B.values.insert(k.u64()[i], mk_cam(P.at("cam").f64() + 17 * i));
+  }
+  if (P.has("point_keys")) {
+    const auto& k = P.at("point_keys");
+    for (size_t i = 0; i < k.rows(); ++i) {
+      const double* p = P.at("point").f64() + 3 * i;
+      B.values.insert(k.u64()[i], Point3(p[0], p[1], p[2]));
+    }
+  }
+  if (P.has("graph_order")) {
+    const auto& go = P.at("graph_order");
+    for (size_t r = 0; r < go.rows(); ++r) {
+      int b = go.i64()[2 * r];
+      size_t i = go.i64()[2 * r + 1];
+      if (B.where[b].size() <= i) B.where[b].resize(i + 1);
+      B.where[b][i] = B.graph.size();
+      B.graph.push_back(make_factor(P, b, i));
+    }
+  } else {
+    for (int b = 0; b < 7; ++b) {
+      std::string n = kBucket[b];
+      if (!P.has(n + "_keys")) continue;
+      size_t m = P.at(n + "_keys").rows();
+      for (size_t i = 0; i < m; ++i) {
+        B.where[b].push_back(B.graph.size());
+        B.graph.push_back(make_factor(P, b, i));
+      }
+    }
+  }
+  return B;
+}
+
+static Ordering make_ordering(const gtbio::File& P, const Built& B) {
+  std::string o = opt("ordering", "colamd");
+  if (o == "colamd") return Ordering::Colamd(B.graph);
+  if (o == "metis") return Ordering::Metis(B.graph);
+  if (o == "natural") return Ordering::Natural(B.graph);
+  if (o == "schur") {
+    Ordering ord;
+    if (P.has("point_keys")) for (size_t i = 0; i < P.at("point_keys").rows(); ++i) ord.push_back(P.at("point_keys").u64()[i]);
+    if (P.has("cam_keys")) for (size_t i = 0; i < P.at("cam_keys").rows(); ++i) ord.push_back(P.at("cam_keys").u64()[i]);
+    return ord;
+  }
+  if (o == "file") {
+    Ordering ord;
+    const auto& a = P.at("ordering");
+    for (size_t i = 0; i < a.rows(); ++i) ord.push_back(a.u64()[i]);
+    return ord;
+  }
+  throw std::runtime_error("unknown ordering " + o);
+}
+
+static double now() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// whitened [A|b] per bucket, row-major m x (sum n_j + 1), in bucket order
+static void dump_jacobians(const Built& B, const GaussianFactorGraph& gfg, gtbio::File& out) {
+  for (int b = 0; b < 7; ++b) {
+    if (B.where[b].empty()) continue;
+    std::vector<double> buf;
+    size_t width = 0;
+    for (size_t gi : B.where[b]) {
+      auto jf = std::dynamic_pointer_cast<JacobianFactor>(gfg[gi]);
+      if (!jf) throw std::runtime_error("not a JacobianFactor");
+      Matrix Ab = jf->augmentedJacobian();  // whitened (model is unit/null here)
+      width = Ab.rows() * Ab.cols();
+      for (int r = 0; r < Ab.rows(); ++r) for (int c = 0; c < Ab.cols(); ++c) buf.push_back(Ab(r, c));
+    }
+    out.put_f64(std::string(kBucket[b]) + "_Ab", buf, {B.where[b].size(), width});
+  }
+}
+
+static void dump_ordering(const Ordering& ord, gtbio::File& out) {
+  std::vector<uint64_t> k(ord.begin(), ord.end());
+  out.put_u64("ordering", k);
+}
+
+// Clique layout and (optionally) numeric [R S d] in DFS post-order with children in stored order.
+static void dump_bayes_tree(const GaussianBayesTree& bt, gtbio::File& out, bool numeric) {
+  typedef GaussianBayesTree::sharedClique C;
+  std::vector<C> post;
+  std::vector<int64_t> parent;
+  {
+    struct Item { C c; bool expanded; };
+    std::vector<Item> st;
+    for (auto it = bt.roots().rbegin(); it != bt.roots().rend(); ++it) st.push_back({*it, false});
+    while (!st.empty()) {
+      Item& top = st.back();
+      if (top.expanded) { post.push_back(top.c); st.pop_back(); continue; }
+      top.expanded = true;
+      C c = top.c;
+      for (auto it = c->children.rbegin(); it != c->children.rend(); ++it) st.push_back({*it, false});
+    }
+  }
+  std::map<const void*, int64_t> index;
+  for (size_t i = 0; i < post.size(); ++i) index[post[i].get()] = i;
+  std::vector<int64_t> nfront, nkeys;
+  std::vector<uint64_t> keys;
+  std::vector<double> rsd;
+  for (auto& c : post) {
+    auto cond = c->conditional();
+    nfront.push_back(cond->nrFrontals());
+    nkeys.push_back(cond->size());
+    for (Key k : cond->keys()) keys.push_back(k);
+    parent.push_back(c->parent() ? index.at(c->parent().get()) : -1);
+    if (numeric) {
+      Matrix Ab = cond->augmentedJacobian();  // [R S d], F x (N+1)
+      for (int r = 0; r < Ab.rows(); ++r) for (int cc = 0; cc < Ab.cols(); ++cc) rsd.push_back(Ab(r, cc));
+    }
+  }
+  out.put_i64("clique_nfrontal", nfront);
+  out.put_i64("clique_nkeys", nkeys);
+  out.put_u64("clique_keys", keys);
+  out.put_i64("clique_parent", parent);
+  if (numeric) out.put_f64("clique_Rsd", rsd);
+}
+
+static void dump_delta(const VectorValues& delta, gtbio::File& out) {
+  std::vector<uint64_t> keys;
+  std::vector<double> v;
+  std::vector<int64_t> dims;
+  for (const auto& kv : delta) keys.push_back(kv.first);
+  std::sort(keys.begin(), keys.end());
+  for (Key k : keys) {
+    const Vector& x = delta.at(k);
+    dims.push_back(x.size());
+    for (int i = 0; i < x.size(); ++i) v.push_back(x(i));
+  }
+  out.put_u64("delta_keys", keys);
+  out.put_i64("delta_dims", dims);
+  out.put_f64("delta", v);
+}
+
+static void dump_values(const Values& v, gtbio::File& out, const std::string& prefix) {
+  std::vector<double> p2, p3, cam, pt;
+  std::vector<uint64_t> k2, k3, kc, kp;
+  for (const auto& kv : v) {
+    Key k = kv.key;
+    if (auto g = dynamic_cast<const GenericValue<Pose2>*>(&kv.value)) {
+      const Pose2& p = g->value();
+      k2.push_back(k); p2.insert(p2.end(), {p.r().c(), p.r().s(), p.x(), p.y()});
+    } else if (auto g = dynamic_cast<const GenericValue<Pose3>*>(&kv.value)) {
+      const Pose3& p = g->value(); Matrix3 R = p.rotation().matrix();
+      k3.push_back(k);
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) p3.push_back(R(r, c));
+      p3.insert(p3.end(), {p.x(), p.y(), p.z()});
+    } else if (auto g = dynamic_cast<const GenericValue<Camera>*>(&kv.value)) {
+      const Camera& cm = g->value(); Matrix3 R = cm.pose().rotation().matrix();
+      kc.push_back(k);
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) cam.push_back(R(r, c));
+      cam.insert(cam.end(), {cm.pose().x(), cm.pose().y(), cm.pose().z(), cm.calibration().fx(),
+                             cm.calibration().k1(), cm.calibration().k2(), cm.calibration().px(),
+                             cm.calibration().py()});
+    } else if (auto g = dynamic_cast<const GenericValue<Point3>*>(&kv.value)) {
+      const Point3& p = g->value();
+      kp.push_back(k); pt.insert(pt.end(), {p.x(), p.y(), p.z()});
+    }
+  }
+  if (!k2.empty()) { out.put_u64(prefix + "pose2_keys", k2); out.put_f64(prefix + "pose2_cs", p2, {k2.size(), 4}); }
+  if (!k3.empty()) { out.put_u64(prefix + "pose3_keys", k3); out.put_f64(prefix + "pose3", p3, {k3.size(), 12}); }
+  if (!kc.empty()) { out.put_u64(prefix + "cam_keys", kc); out.put_f64(prefix + "cam", cam, {kc.size(), 17}); }
+  if (!kp.empty()) { out.put_u64(prefix + "point_keys", kp); out.put_f64(prefix + "point", pt, {kp.size(), 3}); }
+}
+
+static GaussianFactorGraph damp(const GaussianFactorGraph& gfg, const Values& values, double lambda, bool diag) {
+  if (lambda <= 0) return gfg;
+  internal::LevenbergMarquardtState st(values, 0.0, lambda, 10.0);
+  if (!diag) return st.buildDampedSystem(gfg);
+  // mirrors LevenbergMarquardtOptimizer.cpp:293-299 with default min/maxDiagonal
+  LevenbergMarquardtParams prm;
+  VectorValues sq = gfg.hessianDiagonal();
+  for (auto& kv : sq) kv.second = kv.second.cwiseMax(prm.minDiagonal).cwiseMin(prm.maxDiagonal).cwiseSqrt();
+  return st.buildDampedSystem(gfg, sq);
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) { std::cerr << "usage: ref_tool problem.gtb out.gtb key=value...\n"; return 2; }
+  for (int i = 3; i < argc; ++i) {
+    std::string a = argv[i];
+    auto p = a.find('=');
+    if (p != std::string::npos) g_opt[a.substr(0, p)] = a.substr(p + 1);
+  }
+  try {
+    gtbio::File P, out;
+    P.load(argv[1]);
+    Built B = build(P);
+    std::string mode = opt("mode", "solve");
+    out.put_f64("error0", {B.graph.error(B.values)});
+    out.put_i64("n_factors", {(int64_t)B.graph.size()});
+
+    if (mode == "linearize") {
+      auto gfg = B.graph.linearize(B.values);
+      dump_jacobians(B, *gfg, out);
+      VectorValues hd = gfg->hessianDiagonal();
+      std::vector<uint64_t> hk; std::vector<double> hv;
+      for (auto& kv : hd) { hk.push_back(kv.first); }
+      std::sort(hk.begin(), hk.end());
+      for (auto k : hk) for (int i = 0; i < hd.at(k).size(); ++i) hv.push_back(hd.at(k)(i));
+      out.put_u64("hdiag_keys", hk);
+      out.put_f64("hdiag", hv);
+    } else if (mode == "symbolic" || mode == "solve") {
+      Ordering ord = make_ordering(P, B);
+      dump_ordering(ord, out);
+      auto gfg = B.graph.linearize(B.values);
+      double lambda = optd("lambda", 0.0);
+      bool diag = optd("diag", 0) != 0;
+      GaussianFactorGraph sys = damp(*gfg, B.values, lambda, diag);
+      bool failed = false;
+      try {
+        auto bt = sys.eliminateMultifrontal(ord);
+        dump_bayes_tree(*bt, out, mode == "solve");
+        if (mode == "solve") {
+          VectorValues delta = bt->optimize();
+          dump_delta(delta, out);
+          out.put_f64("linear_error0", {gfg->error(VectorValues::Zero(delta))});
+          out.put_f64("linear_error1", {gfg->error(delta)});
+          Values nv = B.values.retract(delta);
+          out.put_f64("error1", {B.graph.error(nv)});
+          dump_values(nv, out, "new_");
+        }
+      } catch (const IndeterminantLinearSystemException& e) {
+        failed = true;
+        out.put_u64("failed_key", {e.nearbyVariable()});
+      }
+      out.put_i64("failed", {failed ? 1 : 0});
+    } else if (mode == "lm" || mode == "gn") {
+      Ordering ord = make_ordering(P, B);
+      dump_ordering(ord, out);
+      std::string log = std::string(argv[2]) + ".lmlog";
+      double t0 = now();
+      Values result;
+      int64_t iters = 0, inner = 0;
+      double err = 0, lam = 0;
+      if (mode == "lm") {
+        LevenbergMarquardtParams prm;
+        if (optd("ceres", 0) != 0) LevenbergMarquardtParams::SetCeresDefaults(&prm);
+        prm.maxIterations = (int)optd("maxiter", prm.maxIterations);
+        prm.lambdaInitial = optd("lambda0", prm.lambdaInitial);
+        prm.relativeErrorTol = optd("reltol", prm.relativeErrorTol);
+        prm.absoluteErrorTol = optd("abstol", prm.absoluteErrorTol);
+        prm.setOrdering(ord);
+        prm.logFile = log;
+        LevenbergMarquardtOptimizer lm(B.graph, B.values, prm);
+        result = lm.optimize();
+        iters = lm.iterations(); inner = lm.getInnerIterations(); err = lm.error(); lam = lm.lambda();
+      } else {
+        GaussNewtonParams prm;
+        prm.maxIterations = (int)optd("maxiter", prm.maxIterations);
+        prm.relativeErrorTol = optd("reltol", prm.relativeErrorTol);
+        prm.absoluteErrorTol = optd("abstol", prm.absoluteErrorTol);
+        prm.setOrdering(ord);
+        GaussNewtonOptimizer gn(B.graph, B.values, prm);
+        result = gn.optimize();
+        iters = gn.iterations(); err = gn.error();
+      }
+      double t1 = now();
+      out.put_f64("final_error", {err});
+      out.put_f64("final_lambda", {lam});
+      out.put_i64("iterations", {iters});
+      out.put_i64("inner_iterations", {inner});
+      out.put_f64("seconds", {t1 - t0});
+      dump_values(result, out, "final_");
+      // LM log: rows [inner, time, error, lambda, outer]
+      std::ifstream lf(log);
+      std::vector<double> rows; std::string line; size_t nrows = 0;
+      while (std::getline(lf, line)) {
+        for (auto& ch : line) if (ch == ',') ch = ' ';
+        std::istringstream is(line); double v; int n = 0;
+        std::vector<double> r;
+        while (is >> v) { r.push_back(v); ++n; }
+        if (n == 5) { rows.insert(rows.end(), r.begin(), r.end()); ++nrows; }
+      }
+      out.put_f64("lm_log", rows, {nrows, 5});
+      std::remove(log.c_str());
+    } else if (mode == "time") {
+      // CPU baseline: stage timings + LM inner iterations/s with the reference's own code.
+      Ordering ord = make_ordering(P, B);
+      int iters = (int)optd("iters", 3);
+      double lambda = optd("lambda", 1e-5);
+      std::vector<double> tl, te, tb, tt;
+      for (int it = 0; it < iters + 1; ++it) {
+        double a = now();
+        auto gfg = B.graph.linearize(B.values);
+        double b = now();
+        GaussianFactorGraph sys = damp(*gfg, B.values, lambda, optd("diag", 0) != 0);
+        auto bt = sys.eliminateMultifrontal(ord);
+        double c = now();
+        VectorValues delta = bt->optimize();
+        double d = now();
+        double e0 = gfg->error(VectorValues::Zero(delta)), e1 = gfg->error(delta);
+        Values nv = B.values.retract(delta);
+        double en = B.graph.error(nv);
+        double e = now();
+        (void)e0; (void)e1; (void)en;
+        if (it == 0) continue;  // warm-up
+        tl.push_back(b - a); te.push_back(c - b); tb.push_back(d - c); tt.push_back(e - a);
+      }
+      out.put_f64("t_linearize", tl); out.put_f64("t_eliminate", te);
+      out.put_f64("t_backsub", tb); out.put_f64("t_iter", tt);
+    } else {
+      throw std::runtime_error("unknown mode " + mode);
+    }
+    out.save(argv[2]);
+  } catch (const std::exception& e) {
+    std::cerr << "ref_tool: " << e.what() << "\n";
+    return 1;
+  }
+  return 0;
+}
