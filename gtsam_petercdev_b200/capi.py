@@ -1,0 +1,88 @@
+"""ctypes binding of include/gtsam_b200.h.  Loads the in-tree libgtsam_b200.so and fails loudly if it is missing:
+there is no Python or CPU fallback for any numeric entry point."""
+import ctypes as C
+import os
+import re
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgtsam_b200.so")
+HEADER = os.path.join(os.path.dirname(HERE), "include", "gtsam_b200.h")
+
+OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_INDETERMINATE, ERR_KEY_MISSING, ERR_NOISE_MODEL, ERR_INCONSISTENT = range(8)
+
+
+class LMParams(C.Structure):
+    _fields_ = [("max_iterations", C.c_int32), ("relative_error_tol", C.c_double), ("absolute_error_tol", C.c_double),
+                ("error_tol", C.c_double), ("lambda_initial", C.c_double), ("lambda_factor", C.c_double),
+                ("lambda_upper_bound", C.c_double), ("lambda_lower_bound", C.c_double),
+                ("min_model_fidelity", C.c_double), ("diagonal_damping", C.c_int32),
+                ("use_fixed_lambda_factor", C.c_int32), ("min_diagonal", C.c_double), ("max_diagonal", C.c_double)]
+
+
+class LMResult(C.Structure):
+    _fields_ = [("initial_error", C.c_double), ("final_error", C.c_double), ("final_lambda", C.c_double),
+                ("iterations", C.c_int32), ("inner_iterations", C.c_int32), ("log_rows", C.c_int32)]
+
+
+_P = C.c_void_p
+_SIGS = {
+    "gtb_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
+    "gtb_destroy": (None, [_P]),
+    "gtb_last_error": (C.c_char_p, [_P]),
+    "gtb_version": (C.c_char_p, []),
+    "gtb_set_variables": (C.c_int, [_P, C.c_int, C.c_int64, _P, _P]),
+    "gtb_set_factors": (C.c_int, [_P, C.c_int, C.c_int64, _P, _P, _P, _P]),
+    "gtb_set_graph_order": (C.c_int, [_P, C.c_int64, _P]),
+    "gtb_finalize_problem": (C.c_int, [_P]),
+    "gtb_set_ordering": (C.c_int, [_P, C.c_int64, _P]),
+    "gtb_set_ordering_builtin": (C.c_int, [_P, C.c_int]),
+    "gtb_plan_sizes": (C.c_int, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "gtb_plan_get": (C.c_int, [_P, _P, _P, _P, _P]),
+    "gtb_plan_stats": (C.c_int, [_P, _P]),
+    "gtb_linearize": (C.c_int, [_P]),
+    "gtb_get_jacobians": (C.c_int, [_P, C.c_int, _P]),
+    "gtb_hessian_diagonal": (C.c_int, [_P, _P]),
+    "gtb_factorize": (C.c_int, [_P, C.c_double, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_uint64)]),
+    "gtb_backsolve": (C.c_int, [_P]),
+    "gtb_get_delta": (C.c_int, [_P, _P]),
+    "gtb_get_conditionals": (C.c_int, [_P, _P]),
+    "gtb_linear_errors": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "gtb_retract": (C.c_int, [_P]),
+    "gtb_error": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
+    "gtb_accept": (C.c_int, [_P]),
+    "gtb_get_variables": (C.c_int, [_P, C.c_int, C.c_int, _P]),
+    "gtb_lm_params_default": (None, [C.POINTER(LMParams)]),
+    "gtb_lm_params_ceres": (None, [C.POINTER(LMParams)]),
+    "gtb_lm_optimize": (C.c_int, [_P, C.POINTER(LMParams), C.POINTER(LMResult), _P, C.c_int64]),
+    "gtb_lm_iterate": (C.c_int, [_P, C.POINTER(LMParams), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                 C.POINTER(C.c_double), C.POINTER(C.c_int32)]),
+    "gtb_gn_optimize": (C.c_int, [_P, C.c_int32, C.c_double, C.c_double, C.POINTER(LMResult)]),
+    "gtb_kernel_launches": (C.c_int64, [_P]),
+    "gtb_stage_ms": (C.c_int, [_P, _P]),
+    "gtb_set_stage_timing": (C.c_int, [_P, C.c_int]),
+    "gtb_stream": (_P, [_P]),
+}
+
+_lib = None
+
+
+def header_symbols():
+    """Every function name declared in include/gtsam_b200.h."""
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(gtb_[a-z0-9_]+)\s*\(", text)))
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `python -m gtsam_petercdev_b200.build` "
+                              "(there is no fallback implementation)")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib

@@ -1,0 +1,1246 @@
+// engine.cu -- the engine behind the C ABI (include/gtsam_b200.h): problem tables, device buffers, the level
+// schedule that drives the kernels in factors.cuh / eliminate.cuh, and the LM / GN control flow.
+//
+// Host control flow mirrors the reference exactly where it decides anything:
+//   LevenbergMarquardtOptimizer::iterate / tryLambda   nonlinear/LevenbergMarquardtOptimizer.cpp:121-304
+//   LevenbergMarquardtState::increase/decreaseLambda   nonlinear/internal/LevenbergMarquardtState.h:70-94
+//   NonlinearOptimizer::defaultOptimize, checkConvergence   nonlinear/NonlinearOptimizer.cpp:62-117, 182-231
+//   GaussNewtonOptimizer::iterate                      nonlinear/GaussNewtonOptimizer.cpp:44-66
+// There is no CPU fallback: every numeric entry point needs a CUDA device.
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/gtsam_b200.h"
+#include "eliminate.cuh"
+#include "factors.cuh"
+#include "plan.h"
+
+namespace gtb {
+
+static const int kZIn[7] = {3, 12, 2, 3, 12, 17, 3};       // measurement doubles per factor as given by the caller
+static const int kZDev[7] = {4, 12, 2, 4, 12, 17, 3};      // ... as kept on the device (Pose2 -> cos, sin, x, y)
+static const int kM[7] = {3, 6, 2, 3, 6, 9, 3};
+static const int kW[7] = {7, 13, 13, 4, 7, 10, 4};
+static const int kNKeys[7] = {2, 2, 2, 1, 1, 1, 1};
+static const int kVT[7][2] = {{0, 0}, {1, 1}, {2, 3}, {0, -1}, {1, -1}, {2, -1}, {3, -1}};
+static const int kStateIn[4] = {3, 12, 17, 3};
+static const int kStateDev[4] = {4, 12, 17, 3};
+static const int kDim[4] = {3, 6, 9, 3};
+static const int kSmallMax = 128;   // fronts with F+S+1 <= kSmallMax are eliminated in shared memory
+
+struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t _e = (call);                                                                       \
+    if (_e != cudaSuccess)                                                                         \
+      throw CudaError(std::string(#call) + ": " + cudaGetErrorString(_e));                         \
+  } while (0)
+
+struct StatusError : std::runtime_error {
+  gtb_status st;
+  StatusError(gtb_status s, const std::string& m) : std::runtime_error(m), st(s) {}
+};
+
+template <class T> struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  void alloc(size_t count) {
+    release();
+    n = count;
+    if (count) CK(cudaMalloc(&p, count * sizeof(T)));
+  }
+  void upload(const std::vector<T>& h, cudaStream_t s) {
+    if (h.size() != n || (!p && n)) alloc(h.size());
+    if (n) CK(cudaMemcpyAsync(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice, s));
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  ~DevBuf() { release(); }
+};
+
+struct LevelSched {
+  // small fronts split into thread classes; each class is a contiguous range of the level list
+  struct Cls { int64_t begin; int32_t count; int32_t threads; int32_t smem; };
+  std::vector<Cls> small;
+  int64_t large_begin = 0;
+  int32_t n_large = 0;
+  int32_t max_F = 0, max_dim = 0, min_F = 0;
+  int64_t work_begin = 0;     // child extend-add work items for large parents
+  int32_t n_work = 0;
+  int32_t n_all = 0;          // all cliques at the level (back-substitution)
+  int32_t bs_smem = 0, bs_threads = 32;
+  int64_t zero_blocks = 0;
+};
+
+}  // namespace gtb
+
+using namespace gtb;
+
+struct gtb_engine {
+  int device = -1;
+  bool has_device = false;
+  cudaStream_t stream = nullptr;
+  mutable std::string err;
+  int64_t launches = 0;
+
+  // ---- host problem ----
+  struct VarsHost { int64_t n = 0; std::vector<uint64_t> keys; std::vector<double> state; } vars[4];
+  struct FacHost {
+    int64_t n = 0;
+    std::vector<uint64_t> keys;
+    std::vector<double> z;       // device layout
+    std::vector<int8_t> nk;      // resolved kinds
+    std::vector<double> noise;   // n x m*m
+    bool any_noise = false;
+  } fac[7];
+  std::vector<int64_t> graph_order;
+  bool finalized = false;
+
+  // variable table, ascending key
+  std::vector<uint64_t> vkeys;
+  std::vector<int8_t> vtype;
+  std::vector<int32_t> vrow, vdim;
+  std::vector<int64_t> voff;
+  int64_t n_scalars = 0;
+  std::vector<int32_t> type_var[4];   // row -> variable id
+
+  SymbolicInput sym;
+  std::vector<int32_t> g_bucket, g_index;   // graph position -> (bucket, index)
+  Plan plan;
+  bool has_plan = false;
+  std::vector<LevelSched> sched;
+  std::vector<ChildWork> child_work;
+
+  // ---- device ----
+  DevBuf<double> d_state[2][4];
+  int cur = 0;
+  DevBuf<int32_t> d_type_goff[4];
+  DevBuf<int32_t> d_row[7][2], d_goff[7][2];
+  DevBuf<double> d_z[7], d_noise[7], d_Ab[7];
+  DevBuf<int8_t> d_nk[7];
+  BucketDev bk[7];
+  DevBuf<double> d_partials, d_scalars, d_delta, d_hdiag, d_damp, d_arena;
+  int64_t partial_off[7] = {0};
+  int64_t n_partials = 0;
+  double* h_scalars = nullptr;   // pinned
+  DevBuf<int64_t> d_inc_off;
+  DevBuf<int32_t> d_inc_bucket, d_inc_index, d_inc_slot, d_var_goff, d_var_dim;
+  DevBuf<CliqueDev> d_cliques;
+  DevBuf<SlotDev> d_slots;
+  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail;
+  DevBuf<ChildWork> d_child_work;
+  bool linearized = false, factorized = false, solved = false, have_hdiag = false;
+
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  double stage_ms[8] = {0};
+  bool time_stages = true;
+
+  // LM state across gtb_lm_iterate calls
+  bool lm_have_error = false;
+  double lm_error = 0;
+
+  ~gtb_engine() {
+    if (h_scalars) cudaFreeHost(h_scalars);
+    if (ev[0]) cudaEventDestroy(ev[0]);
+    if (ev[1]) cudaEventDestroy(ev[1]);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+namespace gtb {
+
+typedef gtb_engine Engine;
+
+static void need_device(Engine* e) {
+  if (!e->has_device) throw StatusError(GTB_ERR_NO_DEVICE, "this engine was created without a CUDA device; there is no CPU fallback");
+}
+static void need(bool cond, const char* msg) {
+  if (!cond) throw StatusError(GTB_ERR_INVALID, msg);
+}
+
+// ---- noise model resolution: the reference's smart factories (linear/NoiseModel.cpp:84-132,284-315,625-634) ----
+static bool is_diagonal(const double* M, int d) {
+  for (int i = 0; i < d; ++i)
+    for (int j = i + 1; j < d; ++j)
+      if (std::abs(M[i * d + j]) > 1e-9) return false;
+  return true;
+}
+static int iso_sigma(double sigma, double* out) {
+  if (std::abs(sigma - 1.0) < 1e-9) return NK_UNIT;
+  out[0] = 1.0 / sigma;
+  return NK_ISO;
+}
+static int iso_variance(double var, double* out) {
+  if (std::abs(var - 1.0) < 1e-9) return NK_UNIT;
+  out[0] = 1.0 / std::sqrt(var);
+  return NK_ISO;
+}
+static int diag_variances(const double* v, int d, double* out) {
+  bool same = true;
+  for (int i = 1; i < d; ++i) same = same && (v[i] == v[0]);
+  if (same) return iso_variance(v[0], out);
+  for (int i = 0; i < d; ++i) out[i] = 1.0 / std::sqrt(v[i]);
+  return NK_DIAG;
+}
+static int diag_sigmas(const double* s, int d, double* out) {
+  for (int i = 0; i < d; ++i)
+    if (s[i] < 1e-8)
+      throw StatusError(GTB_ERR_NOISE_MODEL, "constrained noise model (sigma < 1e-8) needs the QR path, which is not available on device");
+  bool same = true;
+  for (int i = 1; i < d; ++i) same = same && (s[i] == s[0]);
+  if (same) return iso_sigma(s[0], out);
+  for (int i = 0; i < d; ++i) out[i] = 1.0 / s[i];
+  return NK_DIAG;
+}
+static int resolve_noise(int kind, const double* data, int d, double* out) {
+  for (int i = 0; i < d * d; ++i) out[i] = 0.0;
+  double tmp[16];
+  switch (kind) {
+    case GTB_NOISE_UNIT: return NK_UNIT;
+    case GTB_NOISE_ISO_SIGMA: return iso_sigma(data[0], out);
+    case GTB_NOISE_DIAG_SIGMAS: return diag_sigmas(data, d, out);
+    case GTB_NOISE_DIAG_VARIANCES: return diag_variances(data, d, out);
+    case GTB_NOISE_INFORMATION: {
+      if (is_diagonal(data, d)) {
+        for (int i = 0; i < d; ++i) tmp[i] = 1.0 / data[i * d + i];
+        return diag_variances(tmp, d, out);
+      }
+      // R = chol_upper(information)  (Eigen::LLT(...).matrixU(), linear/NoiseModel.cpp:108-110)
+      std::vector<double> L(d * d, 0.0);
+      for (int j = 0; j < d; ++j) {
+        double s = data[j * d + j];
+        for (int k = 0; k < j; ++k) s -= L[j * d + k] * L[j * d + k];
+        if (!(s > 0)) throw StatusError(GTB_ERR_NOISE_MODEL, "information matrix is not positive definite");
+        const double ljj = std::sqrt(s);
+        L[j * d + j] = ljj;
+        for (int i = j + 1; i < d; ++i) {
+          double t = data[i * d + j];
+          for (int k = 0; k < j; ++k) t -= L[i * d + k] * L[j * d + k];
+          L[i * d + j] = t / ljj;
+        }
+      }
+      for (int i = 0; i < d; ++i)
+        for (int j = 0; j < d; ++j) out[i * d + j] = L[j * d + i];
+      return NK_FULL;
+    }
+    case GTB_NOISE_SQRT_INFORMATION: {
+      if (is_diagonal(data, d)) {
+        for (int i = 0; i < d; ++i) tmp[i] = 1.0 / data[i * d + i];
+        return diag_sigmas(tmp, d, out);
+      }
+      for (int i = 0; i < d * d; ++i) out[i] = data[i];
+      return NK_FULL;
+    }
+  }
+  throw StatusError(GTB_ERR_NOISE_MODEL, "unknown noise kind");
+}
+
+static void to_device_state(int vtype, const double* in, double* out) {
+  if (vtype == GTB_POSE2) {  // Pose2(x, y, theta): Rot2::fromAngle (geometry/Pose2.h:74-76)
+    out[0] = std::cos(in[2]);
+    out[1] = std::sin(in[2]);
+    out[2] = in[0];
+    out[3] = in[1];
+  } else {
+    std::memcpy(out, in, sizeof(double) * kStateIn[vtype]);
+  }
+}
+
+// ---- timing helpers ----
+struct StageTimer {
+  Engine* e;
+  int slot;
+  StageTimer(Engine* e_, int s) : e(e_), slot(s) {
+    if (e->time_stages) cudaEventRecord(e->ev[0], e->stream);
+  }
+  void stop() {
+    if (!e->time_stages) return;
+    cudaEventRecord(e->ev[1], e->stream);
+    cudaEventSynchronize(e->ev[1]);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]);
+    e->stage_ms[slot] = ms;
+  }
+};
+
+static void check_launch(Engine* e) {
+  e->launches++;
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) throw CudaError(std::string("kernel launch: ") + cudaGetErrorString(err));
+}
+
+// ------------------------------------------------------------------------------------------------------
+// problem set-up
+// ------------------------------------------------------------------------------------------------------
+static void set_variables(Engine* e, int vt, int64_t n, const uint64_t* keys, const double* state) {
+  need(vt >= 0 && vt < 4, "bad variable type");
+  need(n >= 0 && (n == 0 || state), "null state");
+  auto& v = e->vars[vt];
+  if (e->finalized) {
+    // state refresh (the per-step host -> device copy)
+    need(n == v.n, "variable count changed after gtb_finalize_problem");
+    for (int64_t i = 0; i < n; ++i) to_device_state(vt, state + i * kStateIn[vt], &v.state[i * kStateDev[vt]]);
+    if (e->has_device && n) {
+      CK(cudaMemcpyAsync(e->d_state[e->cur][vt].p, v.state.data(), v.state.size() * sizeof(double),
+                         cudaMemcpyHostToDevice, e->stream));
+      e->linearized = e->factorized = e->solved = false;
+      e->lm_have_error = false;
+    }
+    return;
+  }
+  need(n == 0 || keys, "null keys");
+  v.n = n;
+  v.keys.assign(keys, keys + n);
+  v.state.resize(n * kStateDev[vt]);
+  for (int64_t i = 0; i < n; ++i) to_device_state(vt, state + i * kStateIn[vt], &v.state[i * kStateDev[vt]]);
+}
+
+static void set_factors(Engine* e, int b, int64_t n, const uint64_t* keys, const double* z, const int32_t* nk,
+                        const double* noise) {
+  need(b >= 0 && b < 7, "bad bucket");
+  need(!e->finalized, "gtb_set_factors after gtb_finalize_problem");
+  need(n >= 0 && (n == 0 || (keys && z)), "null factor arrays");
+  auto& f = e->fac[b];
+  const int m = kM[b];
+  f.n = n;
+  f.keys.assign(keys, keys + n * kNKeys[b]);
+  f.z.resize(n * kZDev[b]);
+  f.nk.resize(n);
+  f.noise.assign(n * m * m, 0.0);
+  f.any_noise = false;
+  for (int64_t i = 0; i < n; ++i) {
+    const double* zi = z + i * kZIn[b];
+    double* zo = &f.z[i * kZDev[b]];
+    if (b == GTB_BETWEEN2 || b == GTB_PRIOR2) to_device_state(GTB_POSE2, zi, zo);
+    else std::memcpy(zo, zi, sizeof(double) * kZIn[b]);
+    const int kind = nk ? nk[i] : GTB_NOISE_UNIT;
+    need(kind == GTB_NOISE_UNIT || noise, "noise data required for non-unit noise kinds");
+    f.nk[i] = (int8_t)resolve_noise(kind, noise ? noise + i * m * m : nullptr, m, &f.noise[i * m * m]);
+    if (f.nk[i] != NK_UNIT) f.any_noise = true;
+  }
+}
+
+static void finalize_problem(Engine* e) {
+  need(!e->finalized, "problem already finalized");
+  // variable table in ascending key order (the iteration order of gtsam::Values, a std::map)
+  int64_t V = 0;
+  for (int t = 0; t < 4; ++t) V += e->vars[t].n;
+  need(V > 0, "no variables");
+  need(V < INT32_MAX, "too many variables");
+  std::vector<std::pair<uint64_t, std::pair<int8_t, int32_t>>> all;
+  all.reserve(V);
+  for (int t = 0; t < 4; ++t)
+    for (int64_t i = 0; i < e->vars[t].n; ++i) all.push_back({e->vars[t].keys[i], {(int8_t)t, (int32_t)i}});
+  std::sort(all.begin(), all.end());
+  e->vkeys.resize(V); e->vtype.resize(V); e->vrow.resize(V); e->vdim.resize(V); e->voff.resize(V);
+  for (int t = 0; t < 4; ++t) e->type_var[t].assign(e->vars[t].n, -1);
+  int64_t off = 0;
+  for (int64_t i = 0; i < V; ++i) {
+    if (i && all[i].first == all[i - 1].first) throw StatusError(GTB_ERR_INVALID, "duplicate key in Values (ValuesKeyAlreadyExists)");
+    e->vkeys[i] = all[i].first;
+    e->vtype[i] = all[i].second.first;
+    e->vrow[i] = all[i].second.second;
+    e->vdim[i] = kDim[e->vtype[i]];
+    e->voff[i] = off;
+    off += e->vdim[i];
+    e->type_var[e->vtype[i]][e->vrow[i]] = (int32_t)i;
+  }
+  need(off < INT32_MAX, "too many scalars");
+  e->n_scalars = off;
+
+  // graph order
+  int64_t Mtot = 0;
+  for (int b = 0; b < 7; ++b) Mtot += e->fac[b].n;
+  need(Mtot < INT32_MAX, "too many factors");
+  if (e->graph_order.empty()) {
+    for (int b = 0; b < 7; ++b)
+      for (int64_t i = 0; i < e->fac[b].n; ++i) { e->graph_order.push_back(b); e->graph_order.push_back(i); }
+  }
+  need((int64_t)e->graph_order.size() == 2 * Mtot, "graph order must list every factor exactly once");
+  e->g_bucket.resize(Mtot);
+  e->g_index.resize(Mtot);
+  {
+    std::vector<std::vector<uint8_t>> seen(7);
+    for (int b = 0; b < 7; ++b) seen[b].assign(e->fac[b].n, 0);
+    for (int64_t g = 0; g < Mtot; ++g) {
+      const int64_t b = e->graph_order[2 * g], i = e->graph_order[2 * g + 1];
+      need(b >= 0 && b < 7 && i >= 0 && i < e->fac[b].n && !seen[b][i], "bad graph order entry");
+      seen[b][i] = 1;
+      e->g_bucket[g] = (int32_t)b;
+      e->g_index[g] = (int32_t)i;
+    }
+  }
+
+  // key -> variable id (binary search), typed
+  auto find_var = [&](uint64_t key, int want_type) -> int32_t {
+    auto it = std::lower_bound(e->vkeys.begin(), e->vkeys.end(), key);
+    if (it == e->vkeys.end() || *it != key) {
+      char buf[96];
+      snprintf(buf, sizeof buf, "factor key %llu is not in Values (ValuesKeyDoesNotExist)", (unsigned long long)key);
+      throw StatusError(GTB_ERR_KEY_MISSING, buf);
+    }
+    const int32_t v = (int32_t)(it - e->vkeys.begin());
+    if (e->vtype[v] != want_type) throw StatusError(GTB_ERR_INVALID, "factor key has the wrong variable type (ValuesIncorrectType)");
+    return v;
+  };
+  std::vector<int32_t> fvar[7];
+  for (int b = 0; b < 7; ++b) {
+    const auto& f = e->fac[b];
+    fvar[b].resize(f.n * 2, -1);
+    for (int64_t i = 0; i < f.n; ++i)
+      for (int k = 0; k < kNKeys[b]; ++k) fvar[b][2 * i + k] = find_var(f.keys[i * kNKeys[b] + k], kVT[b][k]);
+  }
+  SymbolicInput& s = e->sym;
+  s.n_vars = (int32_t)V;
+  s.var_dim = e->vdim;
+  s.var_off = e->voff;
+  s.n_factors = Mtot;
+  s.fac_nkeys.resize(Mtot);
+  s.fac_var.resize(2 * Mtot);
+  for (int64_t g = 0; g < Mtot; ++g) {
+    const int b = e->g_bucket[g];
+    const int64_t i = e->g_index[g];
+    s.fac_nkeys[g] = kNKeys[b];
+    s.fac_var[2 * g] = fvar[b][2 * i];
+    s.fac_var[2 * g + 1] = fvar[b][2 * i + 1];
+    if (kNKeys[b] == 2 && s.fac_var[2 * g] == s.fac_var[2 * g + 1])
+      throw StatusError(GTB_ERR_INVALID, "binary factor with the same key twice");
+  }
+  e->finalized = true;
+  if (!e->has_device) return;
+
+  // ---- device upload ----
+  cudaStream_t st = e->stream;
+  for (int t = 0; t < 4; ++t) {
+    if (!e->vars[t].n) continue;
+    e->d_state[0][t].upload(e->vars[t].state, st);
+    e->d_state[1][t].alloc(e->vars[t].state.size());
+    std::vector<int32_t> goff(e->vars[t].n);
+    for (int64_t i = 0; i < e->vars[t].n; ++i) goff[i] = (int32_t)e->voff[e->type_var[t][i]];
+    e->d_type_goff[t].upload(goff, st);
+  }
+  e->n_partials = 0;
+  for (int b = 0; b < 7; ++b) {
+    auto& f = e->fac[b];
+    BucketDev& bk = e->bk[b];
+    std::memset(&bk, 0, sizeof bk);
+    e->partial_off[b] = e->n_partials;
+    if (!f.n) continue;
+    e->n_partials += (f.n + kFactorThreads - 1) / kFactorThreads;
+    for (int k = 0; k < kNKeys[b]; ++k) {
+      std::vector<int32_t> row(f.n), goff(f.n);
+      for (int64_t i = 0; i < f.n; ++i) {
+        const int32_t v = fvar[b][2 * i + k];
+        row[i] = e->vrow[v];
+        goff[i] = (int32_t)e->voff[v];
+      }
+      e->d_row[b][k].upload(row, st);
+      e->d_goff[b][k].upload(goff, st);
+    }
+    e->d_z[b].upload(f.z, st);
+    e->d_nk[b].upload(f.nk, st);
+    if (f.any_noise) e->d_noise[b].upload(f.noise, st);
+    e->d_Ab[b].alloc((size_t)f.n * kM[b] * kW[b]);
+    bk.n = (int32_t)f.n;
+    bk.any_noise = f.any_noise ? 1 : 0;
+    bk.row0 = e->d_row[b][0].p; bk.row1 = e->d_row[b][1].p;
+    bk.goff0 = e->d_goff[b][0].p; bk.goff1 = e->d_goff[b][1].p;
+    bk.z = e->d_z[b].p; bk.nk = e->d_nk[b].p; bk.noise = e->d_noise[b].p; bk.Ab = e->d_Ab[b].p;
+  }
+  e->d_partials.alloc(2 * std::max<int64_t>(e->n_partials, 1));
+  e->d_scalars.alloc(8);
+  CK(cudaMallocHost(&e->h_scalars, 8 * sizeof(double)));
+  e->d_delta.alloc(e->n_scalars);
+  e->d_hdiag.alloc(e->n_scalars);
+  e->d_damp.alloc(e->n_scalars);
+  CK(cudaMemsetAsync(e->d_delta.p, 0, e->n_scalars * sizeof(double), st));
+
+  // variable -> factor incidence in graph order (Hessian diagonal gather)
+  {
+    std::vector<int64_t> ioff(V + 1, 0);
+    for (int64_t g = 0; g < Mtot; ++g)
+      for (int k = 0; k < s.fac_nkeys[g]; ++k) ioff[s.fac_var[2 * g + k] + 1]++;
+    for (int64_t v = 0; v < V; ++v) ioff[v + 1] += ioff[v];
+    std::vector<int32_t> ib(ioff[V]), ii(ioff[V]), is(ioff[V]);
+    std::vector<int64_t> fill(ioff.begin(), ioff.end() - 1);
+    for (int64_t g = 0; g < Mtot; ++g)
+      for (int k = 0; k < s.fac_nkeys[g]; ++k) {
+        const int64_t q = fill[s.fac_var[2 * g + k]]++;
+        ib[q] = e->g_bucket[g]; ii[q] = e->g_index[g]; is[q] = k;
+      }
+    e->d_inc_off.upload(ioff, st);
+    e->d_inc_bucket.upload(ib, st);
+    e->d_inc_index.upload(ii, st);
+    e->d_inc_slot.upload(is, st);
+    std::vector<int32_t> vg(V);
+    for (int64_t v = 0; v < V; ++v) vg[v] = (int32_t)e->voff[v];
+    e->d_var_goff.upload(vg, st);
+    e->d_var_dim.upload(e->vdim, st);
+  }
+  CK(cudaStreamSynchronize(st));
+}
+
+// ------------------------------------------------------------------------------------------------------
+// symbolic plan -> device
+// ------------------------------------------------------------------------------------------------------
+static void install_plan(Engine* e) {
+  const Plan& p = e->plan;
+  const int32_t C = p.n_cliques;
+  // level schedules
+  e->sched.assign(p.n_levels, LevelSched());
+  e->child_work.clear();
+  for (int32_t l = 0; l < p.n_levels; ++l) {
+    LevelSched& L = e->sched[l];
+    const int64_t b = p.level_off[l], ns = p.level_n_small[l], en = p.level_off[l + 1];
+    L.n_all = (int32_t)(en - b);
+    // small classes by front dimension; the list inside the level is re-sorted by dim so classes are contiguous
+    L.large_begin = b + ns;
+    L.n_large = (int32_t)(en - b - ns);
+    L.min_F = INT_MAX;
+    for (int64_t q = L.large_begin; q < en; ++q) {
+      const int32_t c = p.level_cliques[q];
+      L.max_F = std::max(L.max_F, p.F[c]);
+      L.min_F = std::min(L.min_F, p.F[c]);
+      L.max_dim = std::max(L.max_dim, p.F[c] + p.S[c] + 1);
+      L.zero_blocks = std::max<int64_t>(L.zero_blocks, ((int64_t)p.ld[c] * (p.F[c] + p.S[c] + 1) / 2 + 255) / 256);
+    }
+    L.zero_blocks = std::min<int64_t>(L.zero_blocks, 64);
+    L.work_begin = (int64_t)e->child_work.size();
+    for (int64_t q = L.large_begin; q < en; ++q) {
+      const int32_t c = p.level_cliques[q];
+      for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k) {
+        const int32_t ch = p.children[k];
+        const int32_t S1 = p.S[ch] + 1;
+        // chunks of roughly equal triangle area
+        const int32_t nchunk = std::max(1, std::min(64, (int32_t)(((int64_t)S1 * S1 / 2) / 8192)));
+        int32_t c0 = 0;
+        for (int32_t k2 = 1; k2 <= nchunk; ++k2) {
+          int32_t c1 = (k2 == nchunk) ? S1 : (int32_t)std::lround(S1 * std::sqrt((double)k2 / nchunk));
+          c1 = std::max(c1, c0);
+          if (c1 > c0) e->child_work.push_back(ChildWork{ch, c0, c1, 0});
+          c0 = c1;
+        }
+      }
+    }
+    L.n_work = (int32_t)(e->child_work.size() - L.work_begin);
+    int32_t maxN = 0, maxFall = 0;
+    for (int64_t q = b; q < en; ++q) {
+      const int32_t c = p.level_cliques[q];
+      maxN = std::max(maxN, p.F[c] + p.S[c]);
+      maxFall = std::max(maxFall, p.F[c]);
+    }
+    L.bs_smem = maxN * (int32_t)sizeof(double);
+    L.bs_threads = maxFall <= 32 ? 32 : (maxFall <= 128 ? 128 : 256);
+  }
+  // re-sort the small part of every level by dimension and cut into thread classes
+  std::vector<int32_t> lc = p.level_cliques;
+  for (int32_t l = 0; l < p.n_levels; ++l) {
+    LevelSched& L = e->sched[l];
+    const int64_t b = p.level_off[l], ns = p.level_n_small[l];
+    auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
+    std::stable_sort(lc.begin() + b, lc.begin() + b + ns, [&](int32_t a, int32_t c2) { return dim_of(a) < dim_of(c2); });
+    const int32_t bounds[4] = {32, 64, 96, kSmallMax};
+    const int32_t threads[4] = {32, 64, 128, 256};
+    int64_t q = b;
+    for (int k = 0; k < 4; ++k) {
+      int64_t q0 = q;
+      int32_t md = 0;
+      while (q < b + ns && dim_of(lc[q]) <= bounds[k]) { md = std::max(md, dim_of(lc[q])); ++q; }
+      if (q > q0) L.small.push_back({q0, (int32_t)(q - q0), threads[k], (md | 1) * md * (int32_t)sizeof(double)});
+    }
+  }
+  e->plan.level_cliques = lc;
+  if (!e->has_device) return;
+
+  cudaStream_t st = e->stream;
+  std::vector<CliqueDev> cd(C);
+  for (int32_t c = 0; c < C; ++c) {
+    CliqueDev& d = cd[c];
+    d.front_off = p.front_off[c];
+    d.F = p.F[c]; d.S = p.S[c]; d.ld = p.ld[c]; d.parent = p.parent[c];
+    d.fac_begin = (int32_t)p.fac_off[c]; d.fac_end = (int32_t)p.fac_off[c + 1];
+    d.child_begin = (int32_t)p.child_off[c]; d.child_end = (int32_t)p.child_off[c + 1];
+    need(p.pmap_off[c] < INT32_MAX && p.gidx_off[c] < INT32_MAX, "plan index overflow");
+    d.pmap_off = (int32_t)p.pmap_off[c]; d.gidx_off = (int32_t)p.gidx_off[c];
+    d.first_key_var = p.vars[p.vars_off[c]];
+    d.pad = 0;
+  }
+  std::vector<SlotDev> sd(p.slots.size());
+  for (size_t i = 0; i < sd.size(); ++i) {
+    const FactorSlot& f = p.slots[i];
+    sd[i] = SlotDev{f.col0, f.col1, e->g_bucket[f.factor], e->g_index[f.factor]};
+  }
+  e->d_cliques.upload(cd, st);
+  e->d_slots.upload(sd, st);
+  e->d_children.upload(p.children, st);
+  e->d_pmap.upload(p.pmap, st);
+  e->d_gidx.upload(p.gidx, st);
+  e->d_level_cliques.upload(e->plan.level_cliques, st);
+  e->d_child_work.upload(e->child_work, st);
+  e->d_fail.alloc(1);
+  e->d_arena.alloc((size_t)p.arena_doubles + 16);
+  CK(cudaStreamSynchronize(st));
+  e->factorized = e->solved = false;
+}
+
+static void set_ordering_ids(Engine* e, const std::vector<int32_t>& order) {
+  need(e->finalized, "gtb_finalize_problem must be called first");
+  e->sym.order = order;
+  try {
+    build_plan(e->sym, kSmallMax, &e->plan);
+  } catch (const std::runtime_error& ex) {
+    throw StatusError(GTB_ERR_INCONSISTENT, ex.what());
+  }
+  e->has_plan = true;
+  install_plan(e);
+}
+
+// ------------------------------------------------------------------------------------------------------
+// numeric stages
+// ------------------------------------------------------------------------------------------------------
+template <int B> static void launch_linearize(Engine* e) {
+  typedef BucketTraits<B> T;
+  const BucketDev& bk = e->bk[B];
+  if (!bk.n) return;
+  constexpr int MW = T::M * T::W;
+  constexpr int LDS = (MW % 2 == 0) ? MW + 1 : MW;
+  const int smem = kFactorThreads * LDS * sizeof(double);
+  static bool attr = false;
+  if (!attr) {
+    CK(cudaFuncSetAttribute(linearize_kernel<B>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr = true;
+  }
+  const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
+  const double* s0 = e->d_state[e->cur][T::T0].p;
+  const double* s1 = T::T1 >= 0 ? e->d_state[e->cur][T::T1 >= 0 ? T::T1 : 0].p : nullptr;
+  linearize_kernel<B><<<grid, kFactorThreads, smem, e->stream>>>(bk, s0, s1);
+  check_launch(e);
+}
+static void linearize(Engine* e) {
+  need_device(e);
+  need(e->finalized, "problem not finalized");
+  StageTimer tm(e, 0);
+  launch_linearize<0>(e); launch_linearize<1>(e); launch_linearize<2>(e); launch_linearize<3>(e);
+  launch_linearize<4>(e); launch_linearize<5>(e); launch_linearize<6>(e);
+  tm.stop();
+  e->linearized = true;
+  e->factorized = e->solved = e->have_hdiag = false;
+}
+
+template <int B> static void launch_error(Engine* e, int which) {
+  typedef BucketTraits<B> T;
+  const BucketDev& bk = e->bk[B];
+  if (!bk.n) return;
+  const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
+  const double* s0 = e->d_state[which][T::T0].p;
+  const double* s1 = T::T1 >= 0 ? e->d_state[which][T::T1 >= 0 ? T::T1 : 0].p : nullptr;
+  error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(bk, s0, s1, e->d_partials.p + e->partial_off[B]);
+  check_launch(e);
+}
+static double nonlinear_error(Engine* e, int which) {
+  need_device(e);
+  need(e->finalized, "problem not finalized");
+  StageTimer tm(e, 5);
+  const int w = which ? (e->cur ^ 1) : e->cur;
+  launch_error<0>(e, w); launch_error<1>(e, w); launch_error<2>(e, w); launch_error<3>(e, w);
+  launch_error<4>(e, w); launch_error<5>(e, w); launch_error<6>(e, w);
+  sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p);
+  check_launch(e);
+  CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  tm.stop();
+  return e->h_scalars[0];
+}
+
+template <int B> static void launch_linear_error(Engine* e) {
+  const BucketDev& bk = e->bk[B];
+  if (!bk.n) return;
+  const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
+  linear_error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(
+      bk, e->d_delta.p, e->d_partials.p + e->partial_off[B], e->d_partials.p + e->n_partials + e->partial_off[B]);
+  check_launch(e);
+}
+static void linear_errors(Engine* e, double* e0, double* e1) {
+  need_device(e);
+  need(e->linearized && e->solved, "gtb_linear_errors needs gtb_linearize and gtb_backsolve first");
+  StageTimer tm(e, 3);
+  launch_linear_error<0>(e); launch_linear_error<1>(e); launch_linear_error<2>(e); launch_linear_error<3>(e);
+  launch_linear_error<4>(e); launch_linear_error<5>(e); launch_linear_error<6>(e);
+  sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p);
+  check_launch(e);
+  sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p + e->n_partials, (int)e->n_partials, e->d_scalars.p + 1);
+  check_launch(e);
+  CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  tm.stop();
+  *e0 = e->h_scalars[0];
+  *e1 = e->h_scalars[1];
+}
+
+static void hessian_diagonal(Engine* e) {
+  need_device(e);
+  need(e->linearized, "gtb_hessian_diagonal needs gtb_linearize first");
+  StageTimer tm(e, 7);
+  IncidenceDev inc{e->d_inc_off.p, e->d_inc_bucket.p, e->d_inc_index.p, e->d_inc_slot.p,
+                   e->d_var_goff.p, e->d_var_dim.p, (int32_t)e->vkeys.size()};
+  AbTable tab;
+  for (int b = 0; b < 7; ++b) tab.Ab[b] = e->d_Ab[b].p;
+  const int grid = ((int)e->vkeys.size() + 3) / 4;
+  hessian_diag_kernel<<<grid, 128, 0, e->stream>>>(inc, tab, e->d_hdiag.p);
+  check_launch(e);
+  tm.stop();
+  e->have_hdiag = true;
+}
+
+static ElimDev elim_dev(Engine* e, bool damp) {
+  ElimDev E;
+  E.cliques = e->d_cliques.p; E.slots = e->d_slots.p; E.children = e->d_children.p;
+  E.pmap = e->d_pmap.p; E.gidx = e->d_gidx.p; E.arena = e->d_arena.p;
+  for (int b = 0; b < 7; ++b) E.Ab[b] = e->d_Ab[b].p;
+  E.damp = damp ? e->d_damp.p : nullptr;
+  E.fail = e->d_fail.p;
+  return E;
+}
+
+// returns failing clique id or -1
+static int32_t factorize(Engine* e, double lambda, int diag, double lo, double hi) {
+  need_device(e);
+  need(e->has_plan, "gtb_set_ordering must be called first");
+  need(e->linearized, "gtb_factorize needs gtb_linearize first");
+  cudaStream_t st = e->stream;
+  StageTimer tm(e, 1);
+  const bool damp = lambda > 0;
+  if (damp) {
+    if (diag && !e->have_hdiag) {
+      const bool keep = e->time_stages;
+      e->time_stages = false;
+      hessian_diagonal(e);
+      e->time_stages = keep;
+    }
+    const double s = 1.0 / (1.0 / std::sqrt(lambda));   // CachedModel sigma = 1/sqrt(lambda), whitened A = I / sigma
+    const int n = (int)e->n_scalars;
+    damping_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, s, diag, lo, hi, e->d_hdiag.p, e->d_damp.p);
+    check_launch(e);
+  }
+  const int32_t init = INT_MAX;
+  CK(cudaMemcpyAsync(e->d_fail.p, &init, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  const ElimDev E = elim_dev(e, damp);
+  static bool attr = false;
+  if (!attr) {
+    CK(cudaFuncSetAttribute(small_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(backsolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr = true;
+  }
+  const int32_t* lists = e->d_level_cliques.p;
+  for (int32_t l = 0; l < e->plan.n_levels; ++l) {
+    const LevelSched& L = e->sched[l];
+    for (const auto& c : L.small) {
+      small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin);
+      check_launch(e);
+    }
+    if (!L.n_large) continue;
+    const int32_t* ll = lists + L.large_begin;
+    large_zero_kernel<<<dim3((unsigned)L.zero_blocks, L.n_large), 256, 0, st>>>(E, ll);
+    check_launch(e);
+    large_factors_kernel<<<L.n_large, 256, 0, st>>>(E, ll);
+    check_launch(e);
+    if (L.n_work) {
+      large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin);
+      check_launch(e);
+    }
+    const int npanels = (L.max_F + NB - 1) / NB;
+    for (int p = 0; p < npanels; ++p) {
+      potrf_kernel<<<L.n_large, 256, 0, st>>>(E, ll, p);
+      check_launch(e);
+      const int rb = std::min((p + 1) * NB, L.max_F);
+      const int gx_trsm = (L.max_dim - std::min((p + 1) * NB, L.min_F) + 127) / 128;
+      if (gx_trsm > 0) {
+        trsm_kernel<<<dim3(gx_trsm, L.n_large), 128, 0, st>>>(E, ll, p);
+        check_launch(e);
+      }
+      const int gy = (L.max_F - rb + TW - 1) / TW;
+      const int gx = (L.max_dim - rb + TW - 1) / TW;
+      if (gy > 0 && gx > 0) {
+        syrk_kernel<<<dim3(gx, gy, L.n_large), 256, 0, st>>>(E, ll, 0, p);
+        check_launch(e);
+      }
+    }
+    {
+      // Schur complement update: rows [F, dim)
+      int maxS1 = 0;
+      for (int q = 0; q < L.n_large; ++q) {
+        const int32_t c = e->plan.level_cliques[L.large_begin + q];
+        maxS1 = std::max(maxS1, e->plan.S[c] + 1);
+      }
+      const int g = (maxS1 + TW - 1) / TW;
+      syrk_kernel<<<dim3(g, g, L.n_large), 256, 0, st>>>(E, ll, 1, 0);
+      check_launch(e);
+    }
+  }
+  CK(cudaMemcpyAsync(e->h_scalars + 4, e->d_fail.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  tm.stop();
+  int32_t fail;
+  std::memcpy(&fail, e->h_scalars + 4, sizeof(int32_t));
+  e->factorized = (fail == INT_MAX);
+  e->solved = false;
+  return fail == INT_MAX ? -1 : fail;
+}
+
+static void backsolve(Engine* e) {
+  need_device(e);
+  need(e->factorized, "gtb_backsolve needs a successful gtb_factorize first");
+  StageTimer tm(e, 2);
+  const ElimDev E = elim_dev(e, false);
+  for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
+    const LevelSched& L = e->sched[l];
+    backsolve_kernel<<<L.n_all, L.bs_threads, L.bs_smem, e->stream>>>(E, e->d_level_cliques.p + e->plan.level_off[l],
+                                                                      e->d_delta.p);
+    check_launch(e);
+  }
+  tm.stop();
+  e->solved = true;
+}
+
+template <int VT> static void launch_retract(Engine* e) {
+  const int n = (int)e->vars[VT].n;
+  if (!n) return;
+  retract_kernel<VT><<<(n + 127) / 128, 128, 0, e->stream>>>(n, e->d_state[e->cur][VT].p, e->d_type_goff[VT].p,
+                                                             e->d_delta.p, e->d_state[e->cur ^ 1][VT].p);
+  check_launch(e);
+}
+static void retract(Engine* e) {
+  need_device(e);
+  need(e->solved, "gtb_retract needs gtb_backsolve first");
+  StageTimer tm(e, 4);
+  launch_retract<0>(e); launch_retract<1>(e); launch_retract<2>(e); launch_retract<3>(e);
+  tm.stop();
+}
+
+// ------------------------------------------------------------------------------------------------------
+// LM / GN drivers
+// ------------------------------------------------------------------------------------------------------
+struct LMState { double error, lambda, factor; int iterations, inner; };
+
+struct Trace {
+  double* rows; int64_t cap; int64_t n = 0;
+  void add(const LMState& s) {
+    if (rows && n < cap) {
+      double* r = rows + 5 * n;
+      r[0] = s.inner; r[1] = 0; r[2] = s.error; r[3] = s.lambda; r[4] = s.iterations;
+    }
+    n++;
+  }
+};
+
+// one tryLambda; returns true when the lambda search of this outer iteration is over
+static bool try_lambda(Engine* e, const gtb_lm_params& P, LMState& S) {
+  double modelFidelity = 0.0;
+  bool step_ok = false, stop = false;
+  double newError = std::numeric_limits<double>::infinity();
+  const int32_t fail = factorize(e, S.lambda, P.diagonal_damping, P.min_diagonal, P.max_diagonal);
+  if (fail < 0) {
+    backsolve(e);
+    double oldLin, newLin;
+    linear_errors(e, &oldLin, &newLin);
+    const double linearizedCostChange = oldLin - newLin;
+    if (linearizedCostChange >= 0) {
+      retract(e);
+      newError = nonlinear_error(e, 1);
+      const double costChange = S.error - newError;
+      if (linearizedCostChange > std::numeric_limits<double>::epsilon() * oldLin) {
+        modelFidelity = costChange / linearizedCostChange;
+        step_ok = modelFidelity > P.min_model_fidelity;
+      }
+      const double minAbsoluteTolerance = P.relative_error_tol * S.error;
+      if (std::abs(costChange) < minAbsoluteTolerance) stop = true;
+    }
+  }
+  if (step_ok) {
+    // decreaseLambda (LevenbergMarquardtState.h:81-94)
+    double newLambda = S.lambda, newFactor = S.factor;
+    if (P.use_fixed_lambda_factor) {
+      newLambda /= S.factor;
+    } else {
+      newLambda *= std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * modelFidelity - 1.0, 3));
+      newFactor = 2.0 * S.factor;
+    }
+    newLambda = std::max(P.lambda_lower_bound, newLambda);
+    e->cur ^= 1;
+    e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+    S.error = newError; S.lambda = newLambda; S.factor = newFactor;
+    S.iterations += 1; S.inner += 1;
+    return true;
+  } else if (!stop) {
+    S.lambda *= S.factor;
+    S.inner += 1;
+    if (!P.use_fixed_lambda_factor) S.factor *= 2.0;
+    return S.lambda >= P.lambda_upper_bound;
+  }
+  return true;
+}
+
+static void lm_iterate(Engine* e, const gtb_lm_params& P, LMState& S, Trace* tr) {
+  linearize(e);
+  if (S.inner == 0 && tr) tr->add(S);
+  if (P.diagonal_damping) hessian_diagonal(e);
+  while (!try_lambda(e, P, S))
+    if (tr) tr->add(S);
+}
+
+static bool check_convergence(double rel, double abs_, double errThr, double cur, double next) {
+  if (next <= errThr) return true;
+  const double absoluteDecrease = cur - next;
+  const double relativeDecrease = absoluteDecrease / cur;
+  return (rel && (relativeDecrease <= rel)) || (absoluteDecrease <= abs_);
+}
+
+}  // namespace gtb
+
+// ------------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------------
+#define GTB_TRY(e) try {
+#define GTB_CATCH(e)                                                                         \
+  }                                                                                          \
+  catch (const StatusError& ex) { (e)->err = ex.what(); return ex.st; }                      \
+  catch (const CudaError& ex) { (e)->err = ex.what(); return GTB_ERR_CUDA; }                 \
+  catch (const std::bad_alloc&) { (e)->err = "out of host memory"; return GTB_ERR_INVALID; } \
+  catch (const std::exception& ex) { (e)->err = ex.what(); return GTB_ERR_INVALID; }         \
+  return GTB_OK;
+
+extern "C" {
+
+const char* gtb_version(void) { return "gtsam_b200 0.1 (sm_100a)"; }
+
+gtb_status gtb_create(int device, gtb_engine** out) {
+  if (!out) return GTB_ERR_INVALID;
+  *out = nullptr;
+  gtb_engine* e = new gtb_engine();
+  e->device = device;
+  if (device >= 0) {
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+    if (err != cudaSuccess || device >= count) {
+      delete e;
+      return GTB_ERR_NO_DEVICE;
+    }
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&e->ev[0]) != cudaSuccess || cudaEventCreate(&e->ev[1]) != cudaSuccess) {
+      delete e;
+      return GTB_ERR_CUDA;
+    }
+    e->has_device = true;
+  }
+  *out = e;
+  return GTB_OK;
+}
+
+void gtb_destroy(gtb_engine* e) { delete e; }
+const char* gtb_last_error(const gtb_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+gtb_status gtb_set_variables(gtb_engine* e, int vtype, int64_t n, const uint64_t* keys, const double* state) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) set_variables(e, vtype, n, keys, state); GTB_CATCH(e)
+}
+gtb_status gtb_set_factors(gtb_engine* e, int bucket, int64_t n, const uint64_t* keys, const double* z,
+                           const int32_t* noise_kind, const double* noise) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) set_factors(e, bucket, n, keys, z, noise_kind, noise); GTB_CATCH(e)
+}
+gtb_status gtb_set_graph_order(gtb_engine* e, int64_t n, const int64_t* pairs) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need(!e->finalized, "gtb_set_graph_order after gtb_finalize_problem");
+  e->graph_order.assign(pairs, pairs + 2 * n);
+  GTB_CATCH(e)
+}
+gtb_status gtb_finalize_problem(gtb_engine* e) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) finalize_problem(e); GTB_CATCH(e)
+}
+
+gtb_status gtb_set_ordering(gtb_engine* e, int64_t n, const uint64_t* keys) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need(e->finalized, "gtb_finalize_problem must be called first");
+  std::vector<int32_t> order(n);
+  for (int64_t j = 0; j < n; ++j) {
+    auto it = std::lower_bound(e->vkeys.begin(), e->vkeys.end(), keys[j]);
+    if (it == e->vkeys.end() || *it != keys[j]) throw StatusError(GTB_ERR_KEY_MISSING, "ordering key is not a variable");
+    order[j] = (int32_t)(it - e->vkeys.begin());
+  }
+  set_ordering_ids(e, order);
+  GTB_CATCH(e)
+}
+gtb_status gtb_set_ordering_builtin(gtb_engine* e, int which) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need(e->finalized, "gtb_finalize_problem must be called first");
+  const int32_t V = (int32_t)e->vkeys.size();
+  std::vector<int32_t> order;
+  order.reserve(V);
+  if (which == 0) {
+    for (int32_t v = 0; v < V; ++v) order.push_back(v);
+  } else if (which == 1) {
+    for (int64_t i = 0; i < e->vars[GTB_POINT3].n; ++i) order.push_back(e->type_var[GTB_POINT3][i]);
+    for (int64_t i = 0; i < e->vars[GTB_CAMERA].n; ++i) order.push_back(e->type_var[GTB_CAMERA][i]);
+    need((int32_t)order.size() == V, "Schur ordering needs a problem with only cameras and points");
+  } else {
+    need(false, "unknown builtin ordering");
+  }
+  set_ordering_ids(e, order);
+  GTB_CATCH(e)
+}
+gtb_status gtb_plan_sizes(const gtb_engine* e, int64_t* n_cliques, int64_t* n_clique_keys, int64_t* n_cond,
+                          int64_t* n_scalars) {
+  if (!e) return GTB_ERR_INVALID;
+  if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
+  if (n_cliques) *n_cliques = e->plan.n_cliques;
+  if (n_clique_keys) *n_clique_keys = (int64_t)e->plan.vars.size();
+  if (n_cond) *n_cond = e->plan.cond_off[e->plan.n_cliques];
+  if (n_scalars) *n_scalars = e->n_scalars;
+  return GTB_OK;
+}
+gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, uint64_t* keys, int64_t* parent) {
+  if (!e) return GTB_ERR_INVALID;
+  if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
+  const Plan& p = e->plan;
+  for (int32_t c = 0; c < p.n_cliques; ++c) {
+    if (nfrontal) nfrontal[c] = p.n_frontal_vars[c];
+    if (nkeys) nkeys[c] = p.n_vars[c];
+    if (parent) parent[c] = p.parent[c];
+  }
+  if (keys)
+    for (size_t i = 0; i < p.vars.size(); ++i) keys[i] = e->vkeys[p.vars[i]];
+  return GTB_OK;
+}
+gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
+  if (!e || !out) return GTB_ERR_INVALID;
+  if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
+  const Plan& p = e->plan;
+  out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)p.arena_doubles;
+  out[4] = (double)p.n_small; out[5] = (double)p.n_large; out[6] = p.flops_large; out[7] = p.assembly_bytes;
+  return GTB_OK;
+}
+
+gtb_status gtb_linearize(gtb_engine* e) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) linearize(e); GTB_CATCH(e)
+}
+gtb_status gtb_get_jacobians(gtb_engine* e, int bucket, double* out) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(bucket >= 0 && bucket < 7 && e->linearized, "gtb_get_jacobians needs gtb_linearize first");
+  const size_t n = (size_t)e->fac[bucket].n * kM[bucket] * kW[bucket];
+  if (n) CK(cudaMemcpyAsync(out, e->d_Ab[bucket].p, n * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  GTB_CATCH(e)
+}
+gtb_status gtb_hessian_diagonal(gtb_engine* e, double* out) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  hessian_diagonal(e);
+  if (out) CK(cudaMemcpyAsync(out, e->d_hdiag.p, e->n_scalars * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  GTB_CATCH(e)
+}
+gtb_status gtb_factorize(gtb_engine* e, double lambda, int diag, double lo, double hi, uint64_t* failed_key) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  const int32_t fail = factorize(e, lambda, diag, lo, hi);
+  if (fail >= 0) {
+    const uint64_t key = e->vkeys[e->plan.vars[e->plan.vars_off[fail]]];
+    if (failed_key) *failed_key = key;
+    char buf[128];
+    snprintf(buf, sizeof buf, "indeterminant linear system detected while working near variable %llu", (unsigned long long)key);
+    throw StatusError(GTB_ERR_INDETERMINATE, buf);
+  }
+  GTB_CATCH(e)
+}
+gtb_status gtb_backsolve(gtb_engine* e) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) backsolve(e); GTB_CATCH(e)
+}
+gtb_status gtb_get_delta(gtb_engine* e, double* out) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(e->solved && out, "gtb_get_delta needs gtb_backsolve first");
+  CK(cudaMemcpyAsync(out, e->d_delta.p, e->n_scalars * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  GTB_CATCH(e)
+}
+gtb_status gtb_get_conditionals(gtb_engine* e, double* out) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(e->factorized && out, "gtb_get_conditionals needs a successful gtb_factorize first");
+  const Plan& p = e->plan;
+  // parity dump: not a hot path; stage the whole arena through the host
+  std::vector<double> arena((size_t)p.arena_doubles);
+  CK(cudaMemcpyAsync(arena.data(), e->d_arena.p, arena.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  for (int32_t c = 0; c < p.n_cliques; ++c) {
+    const int F = p.F[c], dim = F + p.S[c] + 1, ld = p.ld[c];
+    const double* A = arena.data() + p.front_off[c];
+    double* o = out + p.cond_off[c];
+    for (int i = 0; i < F; ++i)
+      for (int j = 0; j < dim; ++j) o[(int64_t)i * dim + j] = (j >= i) ? A[i + (int64_t)j * ld] : 0.0;
+  }
+  GTB_CATCH(e)
+}
+gtb_status gtb_linear_errors(gtb_engine* e, double* e0, double* e1) {
+  if (!e || !e0 || !e1) return GTB_ERR_INVALID;
+  GTB_TRY(e) linear_errors(e, e0, e1); GTB_CATCH(e)
+}
+gtb_status gtb_retract(gtb_engine* e) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) retract(e); CK(cudaStreamSynchronize(e->stream)); GTB_CATCH(e)
+}
+gtb_status gtb_error(gtb_engine* e, int which, double* error) {
+  if (!e || !error) return GTB_ERR_INVALID;
+  GTB_TRY(e) *error = nonlinear_error(e, which); GTB_CATCH(e)
+}
+gtb_status gtb_accept(gtb_engine* e) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  e->cur ^= 1;
+  e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+  e->lm_have_error = false;
+  GTB_CATCH(e)
+}
+gtb_status gtb_get_variables(gtb_engine* e, int vtype, int which, double* state) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(vtype >= 0 && vtype < 4 && state, "bad arguments");
+  const int w = which ? (e->cur ^ 1) : e->cur;
+  const size_t n = (size_t)e->vars[vtype].n * kStateDev[vtype];
+  if (n) CK(cudaMemcpyAsync(state, e->d_state[w][vtype].p, n * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  GTB_CATCH(e)
+}
+
+void gtb_lm_params_default(gtb_lm_params* p) {
+  p->max_iterations = 100; p->relative_error_tol = 1e-5; p->absolute_error_tol = 1e-5; p->error_tol = 0.0;
+  p->lambda_initial = 1e-5; p->lambda_factor = 10.0; p->lambda_upper_bound = 1e5; p->lambda_lower_bound = 0.0;
+  p->min_model_fidelity = 1e-3; p->diagonal_damping = 0; p->use_fixed_lambda_factor = 1;
+  p->min_diagonal = 1e-6; p->max_diagonal = 1e32;
+}
+void gtb_lm_params_ceres(gtb_lm_params* p) {
+  gtb_lm_params_default(p);
+  p->max_iterations = 50; p->absolute_error_tol = 0; p->relative_error_tol = 1e-6;
+  p->lambda_upper_bound = 1e32; p->lambda_lower_bound = 1e-16; p->lambda_initial = 1e-4; p->lambda_factor = 2.0;
+  p->min_model_fidelity = 1e-3; p->diagonal_damping = 1; p->use_fixed_lambda_factor = 0;
+}
+
+gtb_status gtb_lm_optimize(gtb_engine* e, const gtb_lm_params* p, gtb_lm_result* result, double* trace,
+                           int64_t trace_rows) {
+  if (!e || !p || !result) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(e->has_plan, "gtb_set_ordering must be called first");
+  const gtb_lm_params& P = *p;
+  LMState S;
+  S.error = nonlinear_error(e, 0);
+  S.lambda = P.lambda_initial; S.factor = P.lambda_factor; S.iterations = 0; S.inner = 0;
+  Trace tr{trace, trace_rows};
+  result->initial_error = S.error;
+  // NonlinearOptimizer::defaultOptimize
+  double currentError = S.error;
+  if (!(currentError <= P.error_tol) && S.iterations < P.max_iterations) {
+    double newError = currentError;
+    do {
+      currentError = newError;
+      lm_iterate(e, P, S, &tr);
+      newError = S.error;
+    } while (S.iterations < P.max_iterations &&
+             !check_convergence(P.relative_error_tol, P.absolute_error_tol, P.error_tol, currentError, newError) &&
+             std::isfinite(currentError));
+  }
+  result->final_error = S.error; result->final_lambda = S.lambda;
+  result->iterations = S.iterations; result->inner_iterations = S.inner;
+  result->log_rows = (int32_t)std::min<int64_t>(tr.n, trace ? trace_rows : 0);
+  e->lm_error = S.error; e->lm_have_error = true;
+  GTB_CATCH(e)
+}
+
+gtb_status gtb_lm_iterate(gtb_engine* e, const gtb_lm_params* p, double* lambda_io, double* factor_io,
+                          double* error_io, int32_t* inner) {
+  if (!e || !p || !lambda_io || !factor_io || !error_io) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(e->has_plan, "gtb_set_ordering must be called first");
+  LMState S;
+  S.error = e->lm_have_error ? e->lm_error : nonlinear_error(e, 0);
+  S.lambda = *lambda_io; S.factor = *factor_io; S.iterations = 0; S.inner = 1;  // inner != 0: no initial trace row
+  lm_iterate(e, *p, S, nullptr);
+  *lambda_io = S.lambda; *factor_io = S.factor; *error_io = S.error;
+  if (inner) *inner = S.inner - 1;
+  e->lm_error = S.error; e->lm_have_error = true;
+  GTB_CATCH(e)
+}
+
+gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double rel, double abs_, gtb_lm_result* result) {
+  if (!e || !result) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(e->has_plan, "gtb_set_ordering must be called first");
+  double err = nonlinear_error(e, 0);
+  result->initial_error = err;
+  int it = 0;
+  double currentError = err;
+  if (!(currentError <= 0.0) && it < max_iterations) {
+    double newError = currentError;
+    do {
+      currentError = newError;
+      linearize(e);
+      const int32_t fail = factorize(e, 0.0, 0, 0, 0);
+      if (fail >= 0) {
+        char buf[128];
+        snprintf(buf, sizeof buf, "indeterminant linear system detected while working near variable %llu",
+                 (unsigned long long)e->vkeys[e->plan.vars[e->plan.vars_off[fail]]]);
+        throw StatusError(GTB_ERR_INDETERMINATE, buf);
+      }
+      backsolve(e);
+      retract(e);
+      newError = nonlinear_error(e, 1);
+      e->cur ^= 1;
+      e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+      ++it;
+    } while (it < max_iterations && !check_convergence(rel, abs_, 0.0, currentError, newError) && std::isfinite(currentError));
+    err = newError;
+  }
+  result->final_error = err; result->final_lambda = 0; result->iterations = it; result->inner_iterations = 0;
+  result->log_rows = 0;
+  e->lm_error = err; e->lm_have_error = true;
+  GTB_CATCH(e)
+}
+
+int64_t gtb_kernel_launches(const gtb_engine* e) { return e ? e->launches : 0; }
+gtb_status gtb_stage_ms(gtb_engine* e, double* out) {
+  if (!e || !out) return GTB_ERR_INVALID;
+  for (int i = 0; i < 8; ++i) out[i] = e->stage_ms[i];
+  return GTB_OK;
+}
+gtb_status gtb_set_stage_timing(gtb_engine* e, int on) {
+  if (!e) return GTB_ERR_INVALID;
+  e->time_stages = on != 0;
+  return GTB_OK;
+}
+void* gtb_stream(gtb_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// plan.h -- symbolic elimination plan (host), flattened to index arrays for the device.
+//
+// Built once per ordering by build_plan() (symbolic.cpp).  The reference rebuilds the same structure on every
+// solve (inference/EliminateableFactorGraph-inst.h:131-137); it is invariant across LM iterations and lambda.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace gtb {
+
+struct SymbolicInput {
+  int32_t n_vars = 0;                 // variables, ids = rank in ascending key order
+  std::vector<int32_t> var_dim;       // tangent dimension per variable
+  std::vector<int64_t> var_off;       // scalar offset of each variable in the key-sorted delta vector
+  int64_t n_factors = 0;              // factors in graph order
+  std::vector<int32_t> fac_nkeys;     // 1 or 2
+  std::vector<int32_t> fac_var;       // 2 per factor (second = -1 for unary)
+  std::vector<int32_t> order;         // elimination position -> variable id
+};
+
+// One factor as seen by the clique that assembles it.
+struct FactorSlot {
+  int32_t factor;   // graph index
+  int32_t col0;     // first front column of key 0's block
+  int32_t col1;     // first front column of key 1's block, -1 for unary factors
+  int32_t pad;
+};
+
+struct Plan {
+  int32_t n_cliques = 0;
+  // cliques are numbered in DFS post-order (children in stored order, roots in order)
+  std::vector<int32_t> parent;          // clique id or -1
+  std::vector<int32_t> level;           // 0 = leaves; parent level > every child's level
+  std::vector<int32_t> n_frontal_vars;  // number of frontal variables
+  std::vector<int32_t> n_vars;          // frontal + separator variables
+  std::vector<int64_t> vars_off;        // [n_cliques+1] into vars
+  std::vector<int32_t> vars;            // frontal variables in elimination order, then separator ascending
+  std::vector<int32_t> F, S;            // scalar dims
+  std::vector<int32_t> ld;              // leading dimension of the front (>= F+S+1)
+  std::vector<int64_t> front_off;       // offset (doubles) of the front in the arena
+  int64_t arena_doubles = 0;
+  std::vector<int64_t> child_off;       // [n_cliques+1] into children
+  std::vector<int32_t> children;        // child clique ids in stored order
+  std::vector<int64_t> fac_off;         // [n_cliques+1] into slots
+  std::vector<FactorSlot> slots;        // own factors in gather order
+  std::vector<int64_t> pmap_off;        // [n_cliques] into pmap; S+1 entries per clique
+  std::vector<int32_t> pmap;            // front column in the PARENT of each separator scalar, then of the rhs
+  std::vector<int64_t> gidx_off;        // [n_cliques] into gidx; F+S entries per clique
+  std::vector<int32_t> gidx;            // global (key-sorted) scalar index of every front column
+  std::vector<int64_t> cond_off;        // [n_cliques+1] offsets of row-major [R S d] in the conditional dump
+  // level schedule
+  int32_t n_levels = 0;
+  std::vector<int64_t> level_off;       // [n_levels+1] into level_cliques
+  std::vector<int32_t> level_cliques;   // cliques of each level, small fronts first (ascending id within class)
+  std::vector<int32_t> level_n_small;   // number of small-front cliques at each level
+  // statistics
+  double flops = 0, flops_large = 0, assembly_bytes = 0;
+  int32_t max_front = 0;
+  int64_t n_small = 0, n_large = 0;
+};
+
+// Throws std::runtime_error with a message on inconsistent input.
+// small_max: fronts with F+S+1 <= small_max are handled by the shared-memory kernel.
+void build_plan(const SymbolicInput& in, int32_t small_max, Plan* out);
+
+}  // namespace gtb

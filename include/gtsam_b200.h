@@ -1,0 +1,187 @@
+/* gtsam_b200.h -- C ABI of the B200-native batch nonlinear least-squares engine.
+ *
+ * This is the drop-in boundary.  GTSAM has no FFI or plugin
+ * registry of its own; the seams a maintainer binds are the two virtuals
+ *   LevenbergMarquardtOptimizer::linearize()            nonlinear/LevenbergMarquardtOptimizer.h:113
+ *   NonlinearOptimizer::solve(gfg, params)              nonlinear/NonlinearOptimizer.h:129-130
+ * (or iterate(), NonlinearOptimizer.h:136).  Every entry point below cites the reference code whose work it
+ * replaces.  INTEGRATION.md shows the C++ subclass that calls them.
+ *
+ * Conventions: plain C types only; all pointers are caller-owned HOST buffers unless noted; device memory
+ * is owned by the engine; one CUDA stream per engine; an engine is not thread-safe; every function returns
+ * a gtb_status and never throws; gtb_last_error() gives the message for the last non-OK status.
+ * There is NO CPU fallback: numeric entry points on an engine created without a device return
+ * GTB_ERR_NO_DEVICE.
+ */
+#ifndef GTSAM_B200_H
+#define GTSAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gtb_engine gtb_engine;
+
+typedef enum {
+  GTB_OK = 0,
+  GTB_ERR_INVALID = 1,        /* bad argument / call order (std::invalid_argument in the reference)        */
+  GTB_ERR_NO_DEVICE = 2,      /* numeric call on a host-only engine, or CUDA unavailable                    */
+  GTB_ERR_CUDA = 3,           /* CUDA runtime error                                                          */
+  GTB_ERR_INDETERMINATE = 4,  /* IndeterminantLinearSystemException   linear/linearExceptions.h:94          */
+  GTB_ERR_KEY_MISSING = 5,    /* ValuesKeyDoesNotExist                 nonlinear/Values.h                    */
+  GTB_ERR_NOISE_MODEL = 6,    /* constrained / unsupported noise model (no QR path on device)               */
+  GTB_ERR_INCONSISTENT = 7    /* InconsistentEliminationRequested     inference/inferenceExceptions.h       */
+} gtb_status;
+
+/* Variable types = the Values payloads on the hot path. State layout per row, float64:
+ *   POSE2  (x, y, theta)                    -> kept on device as (cos, sin, x, y), geometry/Pose2.h, Rot2.h
+ *   POSE3  (R row-major 9, t 3)             geometry/Pose3.h, Rot3M.cpp
+ *   CAMERA (R 9, t 3, f, k1, k2, u0, v0)    PinholeCamera<Cal3Bundler>, geometry/PinholeCamera.h
+ *   POINT3 (x, y, z)                                                                                       */
+enum { GTB_POSE2 = 0, GTB_POSE3 = 1, GTB_CAMERA = 2, GTB_POINT3 = 3, GTB_NUM_VTYPES = 4 };
+
+/* Factor buckets (one launch per bucket replaces the per-factor virtual call of
+ * NonlinearFactorGraph::linearize, nonlinear/NonlinearFactorGraph.cpp:239-278):
+ *   BETWEEN2  BetweenFactor<Pose2>   slam/BetweenFactor.h:111     keys 2, z = Pose2 (x,y,theta),  m = 3
+ *   BETWEEN3  BetweenFactor<Pose3>                                keys 2, z = Pose3 (R9,t3),      m = 6
+ *   SFM       GeneralSFMFactor<PinholeCamera<Cal3Bundler>,Point3> slam/GeneralSFMFactor.h:141
+ *                                                                 keys 2 (camera, point), z = (u,v), m = 2
+ *   PRIOR2 / PRIOR3 / PRIORCAM / PRIORPT   PriorFactor<T>  nonlinear/PriorFactor.h:98   keys 1            */
+enum { GTB_BETWEEN2 = 0, GTB_BETWEEN3 = 1, GTB_SFM = 2, GTB_PRIOR2 = 3, GTB_PRIOR3 = 4, GTB_PRIORCAM = 5,
+       GTB_PRIORPT = 6, GTB_NUM_BUCKETS = 7 };
+
+/* Noise models as the user constructs them (linear/NoiseModel.h); the engine applies the reference's
+ * smart-factory downgrade Gaussian -> Diagonal -> Isotropic -> Unit (linear/NoiseModel.cpp:84-132,284-315,
+ * 625-634).  `noise` holds d*d doubles per factor (d = residual dimension), row-major, left-packed.       */
+enum { GTB_NOISE_UNIT = 0, GTB_NOISE_ISO_SIGMA = 1, GTB_NOISE_DIAG_SIGMAS = 2, GTB_NOISE_INFORMATION = 3,
+       GTB_NOISE_SQRT_INFORMATION = 4, GTB_NOISE_DIAG_VARIANCES = 5 };
+
+/* ---- lifecycle ------------------------------------------------------------------------------------ */
+/* device >= 0: CUDA device ordinal.  device < 0: host-only engine (problem set-up and symbolic analysis). */
+gtb_status gtb_create(int device, gtb_engine** out);
+void gtb_destroy(gtb_engine* e);
+const char* gtb_last_error(const gtb_engine* e);
+const char* gtb_version(void);
+
+/* ---- problem upload (replaces Values / NonlinearFactorGraph containers) ----- */
+/* Values::insert for n variables of one type.  Calling again with the same n re-uploads the state only
+ * (the per-step host->device copy).                                                                      */
+gtb_status gtb_set_variables(gtb_engine* e, int vtype, int64_t n, const uint64_t* keys, const double* state);
+/* NonlinearFactorGraph::push_back of n factors of one bucket; keys is n x (2|1).                         */
+gtb_status gtb_set_factors(gtb_engine* e, int bucket, int64_t n, const uint64_t* keys, const double* z,
+                           const int32_t* noise_kind, const double* noise);
+/* Optional: position of every factor in the graph, rows of (bucket, index).  Default: bucket-major.      */
+gtb_status gtb_set_graph_order(gtb_engine* e, int64_t n, const int64_t* bucket_index_pairs);
+/* Finish set-up: key -> row tables, device upload.  Must precede everything below.                       */
+gtb_status gtb_finalize_problem(gtb_engine* e);
+
+/* ---- symbolic analysis, host, once per ordering -------------------------------- */
+/* Takes the elimination ordering (params.ordering, nonlinear/NonlinearOptimizerParams.h:107; the reference
+ * computes it once in the optimizer constructor, LevenbergMarquardtParams.h:112-117) and builds what
+ * eliminateMultifrontal rebuilds on every solve (inference/EliminateableFactorGraph-inst.h:131-137):
+ * VariableIndex -> EliminationTree (EliminationTree-inst.h:78-156) -> JunctionTree with the supernode
+ * merge rule (JunctionTree-inst.h:65-121, ClusterTree-inst.h:46-96) -> clique layout in Scatter order
+ * (linear/Scatter.cpp:39-73).  The result is bit-identical to the reference's Bayes-tree structure.      */
+gtb_status gtb_set_ordering(gtb_engine* e, int64_t n, const uint64_t* keys);
+/* Convenience orderings that need no graph algorithm: 0 = natural (sorted keys, Ordering::Natural),
+ * 1 = Schur (all POINT3 then all CAMERA, timing/timeSFMBAL.h:74-83).                                    */
+gtb_status gtb_set_ordering_builtin(gtb_engine* e, int which);
+gtb_status gtb_plan_sizes(const gtb_engine* e, int64_t* n_cliques, int64_t* n_clique_keys,
+                          int64_t* n_conditional_doubles, int64_t* n_scalars);
+/* Cliques in DFS post-order (children in stored order): frontal count, total key count, keys
+ * (frontals then separator sorted by key), parent index or -1.                                           */
+gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, uint64_t* keys,
+                        int64_t* parent);
+/* Plan statistics: out[0]=levels, [1]=max front dim, [2]=sum flops (POTRF+TRSM+SYRK), [3]=front arena
+ * doubles, [4]=small-front cliques, [5]=large-front cliques, [6]=flops in large fronts, [7]=assembly bytes */
+gtb_status gtb_plan_stats(const gtb_engine* e, double* out8);
+
+/* ---- per outer iteration ---------------------------------------------------------------------------- */
+/* NonlinearFactorGraph::linearize(values): whitened [A|b] of every factor into per-bucket device buffers. */
+gtb_status gtb_linearize(gtb_engine* e);
+/* Row-major m x (sum n_j + 1) per factor, as JacobianFactor::augmentedJacobian (parity dump).            */
+gtb_status gtb_get_jacobians(gtb_engine* e, int bucket, double* out);
+/* GaussianFactorGraph::hessianDiagonal (linear/GaussianFactorGraph.cpp:279-287); out may be NULL, layout
+ * = all variables concatenated in ascending key order.                                                   */
+gtb_status gtb_hessian_diagonal(gtb_engine* e, double* out);
+
+/* ---- per lambda trial --------------------------------------------------------------------------------- */
+/* buildDampedSystem + eliminateMultifrontal(EliminatePreferCholesky) (LevenbergMarquardtState.h:125-156,
+ * linear/HessianFactor.cpp:515-551, base/cholesky.cpp:108-159).  lambda <= 0: no damping (Gauss-Newton).
+ * diagonal_damping != 0: lambda * clamp(diag(H), min_diagonal, max_diagonal).
+ * Returns GTB_ERR_INDETERMINATE with *failed_key = first frontal key of the failing clique.              */
+gtb_status gtb_factorize(gtb_engine* e, double lambda, int diagonal_damping, double min_diagonal,
+                         double max_diagonal, uint64_t* failed_key);
+/* GaussianBayesTree::optimize (linear/linearAlgorithms-inst.h:50-155).                                   */
+gtb_status gtb_backsolve(gtb_engine* e);
+/* delta for all variables concatenated in ascending key order (VectorValues iteration order).            */
+gtb_status gtb_get_delta(gtb_engine* e, double* out);
+/* Conditionals [R S d], row-major F x (N+1) per clique, cliques in post-order, concatenated.             */
+gtb_status gtb_get_conditionals(gtb_engine* e, double* out);
+/* linear.error(zero), linear.error(delta) on the UNDAMPED system (LevenbergMarquardtOptimizer.cpp:170-171) */
+gtb_status gtb_linear_errors(gtb_engine* e, double* error_zero, double* error_delta);
+/* Values::retract(delta) into the scratch copy (nonlinear/Values.cpp:53-63,99).                          */
+gtb_status gtb_retract(gtb_engine* e);
+/* NonlinearFactorGraph::error (nonlinear/NonlinearFactorGraph.cpp:170-179); which: 0 current, 1 scratch. */
+gtb_status gtb_error(gtb_engine* e, int which, double* error);
+/* Accept the trial: scratch becomes current.                                                             */
+gtb_status gtb_accept(gtb_engine* e);
+/* Download variables (which: 0 current, 1 scratch); POSE2 rows come back as (cos, sin, x, y).            */
+gtb_status gtb_get_variables(gtb_engine* e, int vtype, int which, double* state);
+
+/* ---- optimizer drivers (host control flow identical to the reference) ------------------------------ */
+typedef struct {
+  int32_t max_iterations;         /* NonlinearOptimizerParams.h:44   default 100  */
+  double relative_error_tol;      /* 1e-5 */
+  double absolute_error_tol;      /* 1e-5 */
+  double error_tol;               /* 0    */
+  double lambda_initial;          /* LevenbergMarquardtParams.h:69-82: 1e-5 */
+  double lambda_factor;           /* 10   */
+  double lambda_upper_bound;      /* 1e5  */
+  double lambda_lower_bound;      /* 0    */
+  double min_model_fidelity;      /* 1e-3 */
+  int32_t diagonal_damping;       /* 0    */
+  int32_t use_fixed_lambda_factor;/* 1    */
+  double min_diagonal;            /* 1e-6 */
+  double max_diagonal;            /* 1e32 */
+} gtb_lm_params;
+
+typedef struct {
+  double initial_error, final_error, final_lambda;
+  int32_t iterations, inner_iterations;
+  int32_t log_rows;               /* rows written to the trace (see gtb_lm_optimize) */
+} gtb_lm_result;
+
+void gtb_lm_params_default(gtb_lm_params* p);        /* LevenbergMarquardtParams()                     */
+void gtb_lm_params_ceres(gtb_lm_params* p);          /* SetCeresDefaults, LevenbergMarquardtParams.h:85 */
+/* LevenbergMarquardtOptimizer::optimize() (NonlinearOptimizer.cpp:62-117, LevenbergMarquardtOptimizer.cpp:
+ * 121-304).  trace (may be NULL) receives up to trace_rows rows of [inner, 0, error, lambda, outer], the
+ * reference's logFile columns (LevenbergMarquardtOptimizer.cpp:104-118; time column left 0).            */
+gtb_status gtb_lm_optimize(gtb_engine* e, const gtb_lm_params* p, gtb_lm_result* result, double* trace,
+                           int64_t trace_rows);
+/* One LevenbergMarquardtOptimizer::iterate() (one linearize + lambda search).  State persists in the
+ * engine between calls; lambda is in/out.                                                                */
+gtb_status gtb_lm_iterate(gtb_engine* e, const gtb_lm_params* p, double* lambda_io, double* lambda_factor_io,
+                          double* error_io, int32_t* inner_iterations);
+/* GaussNewtonOptimizer::optimize() (nonlinear/GaussNewtonOptimizer.cpp:44-66).                          */
+gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double relative_error_tol,
+                           double absolute_error_tol, gtb_lm_result* result);
+
+/* ---- instrumentation ------------------------------------------------------------------------------- */
+/* Number of engine kernels launched since creation.                                                      */
+int64_t gtb_kernel_launches(const gtb_engine* e);
+/* Device time (ms, CUDA events on the engine stream) of the last call per stage:
+ * out[0]=linearize, [1]=assemble+factorize, [2]=backsolve, [3]=linear errors, [4]=retract, [5]=error,
+ * [6]=large-front factorisation share of [1], [7]=hessian diagonal                                       */
+gtb_status gtb_stage_ms(gtb_engine* e, double* out8);
+/* Per-stage event timing synchronises the stream after every stage; turn it off (on = 0) for throughput runs. */
+gtb_status gtb_set_stage_timing(gtb_engine* e, int on);
+/* Raw stream handle (cudaStream_t) for callers that time with their own events.                          */
+void* gtb_stream(gtb_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GTSAM_B200_H */
