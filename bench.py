@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py -- LM iterations/s of the batch nonlinear least-squares hot path (BASELINE.json metric).
+
+A "step" is one Levenberg-Marquardt inner iteration on one synthetic problem, exactly the stages the reference runs
+per lambda trial (nonlinear/LevenbergMarquardtOptimizer.cpp:121-304): linearize -> damped multifrontal Cholesky ->
+back-substitution -> linear.error(0), linear.error(delta) -> retract -> nonlinear error.  The trial is never accepted,
+so every step does identical work on identical inputs (the same loop as `ref_tool mode=time`, the CPU baseline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c2|c1] [--ordering metis|colamd|schur|natural]
+    python bench.py --impl reference ...     # the unmodified reference (oracle/_ref) on the host cores
+
+value     : device-resident throughput (inputs already in HBM), CUDA events on the engine stream, max over ranks
+e2e       : the same step driven through the C ABI with HOST buffers: variables re-uploaded every step, the new error
+            read back
+roofline  : the kernel class with the largest share of the step, measured live with per-launch CUDA events
+cpu_baseline : oracle/_ref/ref_tool (unmodified GTSAM 4.3a0, serial: TBB is not installed) on rank 0
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "c3": "C3 Ladybug-scale synthetic BA (1,723 cams, 156,000 points, 679,032 GeneralSFMFactor<Cal3Bundler> + 2 priors)",
+    "c2": "C2 sphere2500-shape Pose3 graph (2,500 Pose3, 4,949 BetweenFactor<Pose3> + prior)",
+    "c1": "C1 M3500-shape Pose2 graph (3,500 Pose2, 5,450 BetweenFactor<Pose2> + prior)",
+}
+DGEMM_FP64_TFLOPS = 35.46   # cuBLAS fp64 8192^3 measured on this pool's B200 (tools/probe_box.py, profiles/probe_r01.json)
+
+
+def make_problem(workload):
+    from gtsam_petercdev_b200 import datasets
+    if workload == "c3":
+        return datasets.ladybug_shape()
+    if workload == "c2":
+        return datasets.sphere_shape()
+    if workload == "c1":
+        return datasets.m3500_shape()
+    raise SystemExit(f"unknown workload {workload}")
+
+
+def ordering_for(problem, workload, name):
+    """Ordering keys, or a builtin name.  COLAMD / METIS orderings are the reference's own (computed once by
+    oracle/_ref/ref_tool, committed as permutations under tests/golden/): ordering is an input of the path."""
+    if name in ("schur", "natural"):
+        return name
+    f = os.path.join(ROOT, "tests", "golden", {"c3": "ladybug_shape", "c2": "sphere_shape", "c1": "m3500_shape"}[workload] + "_orderings.npz")
+    perm = np.load(f)[name]
+    return problem.variables()[0][perm]
+
+
+def clocks_start(path):
+    q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    try:
+        return subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                stdout=open(path, "w"), stderr=subprocess.DEVNULL)
+    except Exception:
+        return None
+
+
+def clocks_stop(proc, path, device):
+    out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+    if proc is None:
+        return out
+    proc.terminate()
+    try:
+        proc.wait(timeout=5)
+    except Exception:
+        proc.kill()
+    sm, mx, reasons = [], [], set()
+    try:
+        for line in open(path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9 or not f[0].isdigit() or int(f[0]) != device:
+                continue
+            sm.append(float(f[1]))
+            mx.append(float(f[2]))
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+    except Exception:
+        pass
+    if sm:
+        # "under load": the upper half of the samples (idle samples before/after the timed region pull the median down)
+        s = sorted(sm)
+        out["sm_mhz"] = float(np.median(s[len(s) // 2:]))
+        out["sm_max_mhz"] = float(max(mx))
+    out["reasons"] = sorted(reasons)
+    return out
+
+
+def run_reference(args, rank, world):
+    """The reference's own CPU implementation of the step (oracle/_ref/ref_tool mode=time: unmodified GTSAM 4.3a0
+    linked from oracle/_ref/libgtsam_ref.so), rank 0 only."""
+    if rank != 0:
+        return
+    tool = os.path.join(ROOT, "oracle", "_ref", "ref_tool")
+    base = {"impl": "reference", "metric": "LM iter/s (linearize+multifrontal Cholesky+backsub)", "unit": "iter/s",
+            "n_gpus": args.gpus, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": WORKLOADS[args.workload], "ordering": args.ordering,
+                                            "lambda": args.lam}}
+    if not os.path.exists(tool):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_tool not built (needs /root/reference)"}))
+        return
+    p = make_problem(args.workload)
+    o = ordering_for(p, args.workload, args.ordering)
+    tmp = tempfile.mkdtemp()
+    if not isinstance(o, str):
+        p.a["ordering"] = np.ascontiguousarray(o, dtype=np.uint64)
+    pf, of = os.path.join(tmp, "p.gtb"), os.path.join(tmp, "o.gtb")
+    p.save(pf)
+    # bounded sample: at ~10 s per C3 step the run is capped to what fits in a few minutes
+    est = {"c3": 11.0, "c2": 0.2, "c1": 0.1}[args.workload]
+    steps = max(1, min(args.steps, int(240 / est)))
+    warm = 1 if (args.warmup + steps) * est > 240 else args.warmup
+    sample = f"{steps} full LM inner iterations of the whole workload after {warm} warm-up (asked {args.steps}/{args.warmup})"
+    from gtsam_petercdev_b200 import gtbio
+    oname = o if isinstance(o, str) else "file"
+    t0 = time.time()
+    subprocess.run([tool, pf, of, "mode=time", f"ordering={oname}", f"iters={steps}", f"warm={warm}", f"lambda={args.lam!r}"],
+                   check=True)
+    wall = time.time() - t0
+    r = gtbio.load(of)
+    t_iter = float(np.mean(r["t_iter"]))
+    base.update({"value": 1.0 / t_iter, "steps": steps, "warmup": warm, "ms_per_step": 1e3 * t_iter,
+                 "cpu_baseline": {"value": 1.0 / t_iter, "unit": "iter/s", "cores": 1, "kind": "reference", "sample": sample,
+                                  "host_cores": os.cpu_count(), "threads_note": "TBB not installed: the reference runs serial",
+                                  "stage_ms": {k: 1e3 * float(np.mean(r[k])) for k in ("t_linearize", "t_eliminate", "t_backsub")},
+                                  "wall_s": wall},
+                 "e2e": {"value": 1.0 / t_iter, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0})
+    print(json.dumps(base))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--ordering", default="metis")
+    ap.add_argument("--lam", type=float, default=1e-5)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from gtsam_petercdev_b200.engine import Engine
+
+    # ---- set-up (untimed): problem, upload, symbolic plan ----------------------------------------------------
+    p = make_problem(args.workload)
+    t0 = time.time()
+    e = Engine(p, device=local)
+    t_upload = time.time() - t0
+    t0 = time.time()
+    e.set_ordering(ordering_for(p, args.workload, args.ordering))
+    t_plan = time.time() - t0
+    plan = e.plan()
+    st = plan["stats"]
+    stream = torch.cuda.ExternalStream(e.stream(), device=torch.device("cuda", local))
+    e.set_stage_timing(False)
+    lam = args.lam
+
+    def step():
+        e.linearize()
+        e.factorize(lam)
+        e.backsolve()
+        e0, e1 = e.linear_errors()
+        e.retract()
+        return e.error(1)
+
+    cam, pt = p.a.get("cam"), p.a.get("point")
+    host_state = [(t, np.ascontiguousarray(p.a[n])) for t, n in enumerate(["pose2", "pose3", "cam", "point"]) if n in p.a]
+    h2d = int(sum(a.nbytes for _, a in host_state))
+
+    def step_e2e():
+        for t, a in host_state:
+            e.set_state(t, a)       # host -> device copy of the step's inputs through the C ABI
+        return step()               # the new error comes back to the host (8 bytes) inside error()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        err1 = step()
+    clk_path = os.path.join(tempfile.gettempdir(), f"gtb_clocks_{rank}.csv")
+    clk = clocks_start(clk_path) if rank == 0 else None
+
+    def timed(fn, n):
+        barrier()
+        l0 = e.kernel_launches()
+        s, f = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record(stream)
+        for _ in range(n):
+            fn()
+        f.record(stream)
+        barrier()
+        ms = s.elapsed_time(f)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, e.kernel_launches() - l0
+
+    ms_dev, launches = timed(step, args.steps)
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    clocks = clocks_stop(clk, clk_path, local) if rank == 0 else None
+
+    # ---- per-kernel-class breakdown, measured live with per-launch CUDA events ---------------------------------
+    e.profile(True)
+    nprof = min(args.steps, 3)
+    for _ in range(nprof):
+        step()
+    prof = e.profile_read()
+    e.profile(False)
+    e.set_stage_timing(True)
+    step()
+    stage = e.stage_ms()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    per_step = {k: (v[0] / nprof, v[1] // nprof) for k, v in prof.items()}
+    total_k = sum(v[0] for v in per_step.values())
+    share = {k: v[0] / total_k for k, v in per_step.items()}
+    hbm = 6538.6
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm = float(peaks["hbm_gbs"])
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs; fp64 tensor peak = cuBLAS DGEMM measured by tools/probe_box.py)"
+    except Exception:
+        hbm, peak_src = 6650.0, "fallback"
+    # algorithmic work per step of each candidate class
+    work = {
+        "syrk_frontal": ("tensor", st["flops_syrk_frontal"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
+        "syrk_schur": ("tensor", st["flops_syrk_schur"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
+        "small_front": ("hbm", st["bytes_small"] / 1e9, hbm, "GB/s"),
+        "linearize": ("hbm", st["bytes_linearize"] / 1e9, hbm, "GB/s"),
+        "backsolve": ("hbm", st["bytes_backsolve"] / 1e9, hbm, "GB/s"),
+    }
+    dom = max((k for k in per_step if k in work), key=lambda k: per_step[k][0])
+    bound, amount, peak, unit = work[dom]
+    achieved = amount / (per_step[dom][0] / 1e3)
+    roofline = {"kernel": dom, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "share_of_step": share[dom],
+                "launches_per_step": per_step[dom][1], "ms_per_step": per_step[dom][0],
+                "all_classes_ms_per_step": {k: round(v[0], 4) for k, v in sorted(per_step.items(), key=lambda kv: -kv[1][0])},
+                "other": {k: {"achieved": work[k][1] / (per_step[k][0] / 1e3), "unit": work[k][3], "frac": work[k][1] / (per_step[k][0] / 1e3) / work[k][2]}
+                          for k in work if k in per_step and k != dom}}
+
+    line = {
+        "metric": "LM iter/s (linearize+multifrontal Cholesky+backsub)", "value": world * args.steps / (ms_dev / 1e3),
+        "unit": "iter/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload], "ordering": args.ordering + " (the reference's own, precomputed)",
+                   "lambda": lam, "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (one problem per GPU)",
+                   "l2": "inputs larger than L2 (fronts %.1f GB, Jacobians %.0f MB)" % (st["arena_doubles"] * 8 / 1e9, st["bytes_linearize"] / 1e6),
+                   "cliques": int(len(plan["clique_parent"])), "levels": int(st["levels"]), "max_front": int(st["max_front"]),
+                   "elimination_gflop": st["flops"] / 1e9, "setup_s": {"upload": t_upload, "symbolic_plan": t_plan}},
+        "e2e": {"value": world * args.steps / (ms_e2e / 1e3), "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8 * 3},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "stage_ms": stage,
+        "fp64_tflops_elimination": st["flops"] / 1e12 / (stage["factorize"] / 1e3),
+        "trial_error": err1,
+    }
+    # ---- CPU baseline: the unmodified reference on the host, bounded sample ------------------------------------
+    tool = os.path.join(ROOT, "oracle", "_ref", "ref_tool")
+    if not args.no_cpu_baseline and world == 1 and os.path.exists(tool):
+        from gtsam_petercdev_b200 import gtbio
+        tmp = tempfile.mkdtemp()
+        o = ordering_for(p, args.workload, args.ordering)
+        if not isinstance(o, str):
+            p.a["ordering"] = np.ascontiguousarray(o, dtype=np.uint64)
+        pf, of = os.path.join(tmp, "p.gtb"), os.path.join(tmp, "o.gtb")
+        p.save(pf)
+        iters = 1 if args.workload == "c3" else 5
+        subprocess.run([tool, pf, of, "mode=time", f"ordering={o if isinstance(o, str) else 'file'}", f"iters={iters}", "warm=1",
+                        f"lambda={lam!r}"], check=True)
+        r = gtbio.load(of)
+        t_iter = float(np.mean(r["t_iter"]))
+        line["cpu_baseline"] = {"value": 1.0 / t_iter, "unit": "iter/s", "cores": 1, "kind": "reference",
+                                "sample": f"{iters} full LM inner iteration(s) of the same workload after 1 warm-up, oracle/_ref/ref_tool mode=time",
+                                "host_cores": os.cpu_count(), "threads_note": "TBB not installed: the reference runs serial",
+                                "stage_ms": {k: 1e3 * float(np.mean(r[k])) for k in ("t_linearize", "t_eliminate", "t_backsub")},
+                                "trial_error": float(r["trial_error"][0]) if "trial_error" in r else None}
+    else:
+        line["cpu_baseline"] = {"value": None, "unit": "iter/s", "cores": 0, "kind": "reference",
+                                "sample": "skipped (multi-GPU run, --no-cpu-baseline, or oracle/_ref missing)"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

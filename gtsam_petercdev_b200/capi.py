@@ -60,6 +60,10 @@ _SIGS = {
     "gtb_kernel_launches": (C.c_int64, [_P]),
     "gtb_stage_ms": (C.c_int, [_P, _P]),
     "gtb_set_stage_timing": (C.c_int, [_P, C.c_int]),
+    "gtb_profile": (C.c_int, [_P, C.c_int]),
+    "gtb_profile_classes": (C.c_int, []),
+    "gtb_profile_class_name": (C.c_char_p, [C.c_int]),
+    "gtb_profile_read": (C.c_int, [_P, _P, _P]),
     "gtb_stream": (_P, [_P]),
 }
 

@@ -141,6 +141,11 @@ struct gtb_engine {
   DevBuf<ChildWork> d_child_work;
   bool linearized = false, factorized = false, solved = false, have_hdiag = false;
 
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_events;
+  std::vector<int> prof_class;
+  int64_t prof_used = 0;
+  int64_t class_launches[32] = {0};
   cudaEvent_t ev[2] = {nullptr, nullptr};
   double stage_ms[8] = {0};
   bool time_stages = true;
@@ -151,6 +156,7 @@ struct gtb_engine {
 
   ~gtb_engine() {
     if (h_scalars) cudaFreeHost(h_scalars);
+    for (auto ev_ : prof_events) cudaEventDestroy(ev_);
     if (ev[0]) cudaEventDestroy(ev[0]);
     if (ev[1]) cudaEventDestroy(ev[1]);
     if (stream) cudaStreamDestroy(stream);
@@ -273,11 +279,36 @@ struct StageTimer {
   }
 };
 
-static void check_launch(Engine* e) {
-  e->launches++;
-  cudaError_t err = cudaGetLastError();
-  if (err != cudaSuccess) throw CudaError(std::string("kernel launch: ") + cudaGetErrorString(err));
+// kernel classes for launch counting and optional per-launch event timing
+enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_ZERO, K_LFACT, K_LCHILD, K_POTRF,
+       K_TRSM, K_SYRK, K_SCHUR, K_BACKSOLVE, K_RETRACT, K_NUM };
+static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
+                                          "small_front", "large_zero", "large_factors", "large_children", "potrf",
+                                          "trsm", "syrk_frontal", "syrk_schur", "backsolve", "retract"};
+
+static void prof_begin(Engine* e, int k) {
+  if (!e->profiling) return;
+  if (e->prof_used + 2 > (int64_t)e->prof_events.size()) {
+    const size_t old = e->prof_events.size();
+    e->prof_events.resize(old + 8192);
+    for (size_t i = old; i < e->prof_events.size(); ++i) cudaEventCreate(&e->prof_events[i]);
+  }
+  e->prof_class.push_back(k);
+  cudaEventRecord(e->prof_events[e->prof_used++], e->stream);
 }
+static void check_launch(Engine* e, int k) {
+  e->launches++;
+  e->class_launches[k]++;
+  if (e->profiling) cudaEventRecord(e->prof_events[e->prof_used++], e->stream);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) throw CudaError(std::string("kernel launch (") + kKernelNames[k] + "): " + cudaGetErrorString(err));
+}
+#define LAUNCH(e, k, ...)   \
+  do {                      \
+    prof_begin(e, k);       \
+    __VA_ARGS__;            \
+    check_launch(e, k);     \
+  } while (0)
 
 // ------------------------------------------------------------------------------------------------------
 // problem set-up
@@ -623,8 +654,7 @@ template <int B> static void launch_linearize(Engine* e) {
   const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
   const double* s0 = e->d_state[e->cur][T::T0].p;
   const double* s1 = T::T1 >= 0 ? e->d_state[e->cur][T::T1 >= 0 ? T::T1 : 0].p : nullptr;
-  linearize_kernel<B><<<grid, kFactorThreads, smem, e->stream>>>(bk, s0, s1);
-  check_launch(e);
+  LAUNCH(e, K_LINEARIZE, linearize_kernel<B><<<grid, kFactorThreads, smem, e->stream>>>(bk, s0, s1));
 }
 static void linearize(Engine* e) {
   need_device(e);
@@ -644,8 +674,7 @@ template <int B> static void launch_error(Engine* e, int which) {
   const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
   const double* s0 = e->d_state[which][T::T0].p;
   const double* s1 = T::T1 >= 0 ? e->d_state[which][T::T1 >= 0 ? T::T1 : 0].p : nullptr;
-  error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(bk, s0, s1, e->d_partials.p + e->partial_off[B]);
-  check_launch(e);
+  LAUNCH(e, K_ERROR, error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(bk, s0, s1, e->d_partials.p + e->partial_off[B]));
 }
 static double nonlinear_error(Engine* e, int which) {
   need_device(e);
@@ -654,8 +683,7 @@ static double nonlinear_error(Engine* e, int which) {
   const int w = which ? (e->cur ^ 1) : e->cur;
   launch_error<0>(e, w); launch_error<1>(e, w); launch_error<2>(e, w); launch_error<3>(e, w);
   launch_error<4>(e, w); launch_error<5>(e, w); launch_error<6>(e, w);
-  sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p);
-  check_launch(e);
+  LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p));
   CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
   tm.stop();
@@ -666,9 +694,8 @@ template <int B> static void launch_linear_error(Engine* e) {
   const BucketDev& bk = e->bk[B];
   if (!bk.n) return;
   const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
-  linear_error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(
-      bk, e->d_delta.p, e->d_partials.p + e->partial_off[B], e->d_partials.p + e->n_partials + e->partial_off[B]);
-  check_launch(e);
+  LAUNCH(e, K_LINERR, linear_error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(
+      bk, e->d_delta.p, e->d_partials.p + e->partial_off[B], e->d_partials.p + e->n_partials + e->partial_off[B]));
 }
 static void linear_errors(Engine* e, double* e0, double* e1) {
   need_device(e);
@@ -676,10 +703,8 @@ static void linear_errors(Engine* e, double* e0, double* e1) {
   StageTimer tm(e, 3);
   launch_linear_error<0>(e); launch_linear_error<1>(e); launch_linear_error<2>(e); launch_linear_error<3>(e);
   launch_linear_error<4>(e); launch_linear_error<5>(e); launch_linear_error<6>(e);
-  sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p);
-  check_launch(e);
-  sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p + e->n_partials, (int)e->n_partials, e->d_scalars.p + 1);
-  check_launch(e);
+  LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p));
+  LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p + e->n_partials, (int)e->n_partials, e->d_scalars.p + 1));
   CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
   tm.stop();
@@ -696,8 +721,7 @@ static void hessian_diagonal(Engine* e) {
   AbTable tab;
   for (int b = 0; b < 7; ++b) tab.Ab[b] = e->d_Ab[b].p;
   const int grid = ((int)e->vkeys.size() + 3) / 4;
-  hessian_diag_kernel<<<grid, 128, 0, e->stream>>>(inc, tab, e->d_hdiag.p);
-  check_launch(e);
+  LAUNCH(e, K_HDIAG, hessian_diag_kernel<<<grid, 128, 0, e->stream>>>(inc, tab, e->d_hdiag.p));
   tm.stop();
   e->have_hdiag = true;
 }
@@ -729,8 +753,7 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     }
     const double s = 1.0 / (1.0 / std::sqrt(lambda));   // CachedModel sigma = 1/sqrt(lambda), whitened A = I / sigma
     const int n = (int)e->n_scalars;
-    damping_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, s, diag, lo, hi, e->d_hdiag.p, e->d_damp.p);
-    check_launch(e);
+    LAUNCH(e, K_DAMP, damping_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, s, diag, lo, hi, e->d_hdiag.p, e->d_damp.p));
   }
   const int32_t init = INT_MAX;
   CK(cudaMemcpyAsync(e->d_fail.p, &init, sizeof(int32_t), cudaMemcpyHostToDevice, st));
@@ -745,34 +768,27 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   for (int32_t l = 0; l < e->plan.n_levels; ++l) {
     const LevelSched& L = e->sched[l];
     for (const auto& c : L.small) {
-      small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin);
-      check_launch(e);
+      LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
     }
     if (!L.n_large) continue;
     const int32_t* ll = lists + L.large_begin;
-    large_zero_kernel<<<dim3((unsigned)L.zero_blocks, L.n_large), 256, 0, st>>>(E, ll);
-    check_launch(e);
-    large_factors_kernel<<<L.n_large, 256, 0, st>>>(E, ll);
-    check_launch(e);
+    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3((unsigned)L.zero_blocks, L.n_large), 256, 0, st>>>(E, ll));
+    LAUNCH(e, K_LFACT, large_factors_kernel<<<L.n_large, 256, 0, st>>>(E, ll));
     if (L.n_work) {
-      large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin);
-      check_launch(e);
+      LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
     }
     const int npanels = (L.max_F + NB - 1) / NB;
     for (int p = 0; p < npanels; ++p) {
-      potrf_kernel<<<L.n_large, 256, 0, st>>>(E, ll, p);
-      check_launch(e);
+      LAUNCH(e, K_POTRF, potrf_kernel<<<L.n_large, 256, 0, st>>>(E, ll, p));
       const int rb = std::min((p + 1) * NB, L.max_F);
       const int gx_trsm = (L.max_dim - std::min((p + 1) * NB, L.min_F) + 127) / 128;
       if (gx_trsm > 0) {
-        trsm_kernel<<<dim3(gx_trsm, L.n_large), 128, 0, st>>>(E, ll, p);
-        check_launch(e);
+        LAUNCH(e, K_TRSM, trsm_kernel<<<dim3(gx_trsm, L.n_large), 128, 0, st>>>(E, ll, p));
       }
       const int gy = (L.max_F - rb + TW - 1) / TW;
       const int gx = (L.max_dim - rb + TW - 1) / TW;
       if (gy > 0 && gx > 0) {
-        syrk_kernel<<<dim3(gx, gy, L.n_large), 256, 0, st>>>(E, ll, 0, p);
-        check_launch(e);
+        LAUNCH(e, K_SYRK, syrk_kernel<<<dim3(gx, gy, L.n_large), 256, 0, st>>>(E, ll, 0, p));
       }
     }
     {
@@ -783,8 +799,7 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
         maxS1 = std::max(maxS1, e->plan.S[c] + 1);
       }
       const int g = (maxS1 + TW - 1) / TW;
-      syrk_kernel<<<dim3(g, g, L.n_large), 256, 0, st>>>(E, ll, 1, 0);
-      check_launch(e);
+      LAUNCH(e, K_SCHUR, syrk_kernel<<<dim3(g, g, L.n_large), 256, 0, st>>>(E, ll, 1, 0));
     }
   }
   CK(cudaMemcpyAsync(e->h_scalars + 4, e->d_fail.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
@@ -804,9 +819,8 @@ static void backsolve(Engine* e) {
   const ElimDev E = elim_dev(e, false);
   for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
     const LevelSched& L = e->sched[l];
-    backsolve_kernel<<<L.n_all, L.bs_threads, L.bs_smem, e->stream>>>(E, e->d_level_cliques.p + e->plan.level_off[l],
-                                                                      e->d_delta.p);
-    check_launch(e);
+    LAUNCH(e, K_BACKSOLVE, backsolve_kernel<<<L.n_all, L.bs_threads, L.bs_smem, e->stream>>>(E, e->d_level_cliques.p + e->plan.level_off[l],
+                                                                      e->d_delta.p));
   }
   tm.stop();
   e->solved = true;
@@ -815,9 +829,8 @@ static void backsolve(Engine* e) {
 template <int VT> static void launch_retract(Engine* e) {
   const int n = (int)e->vars[VT].n;
   if (!n) return;
-  retract_kernel<VT><<<(n + 127) / 128, 128, 0, e->stream>>>(n, e->d_state[e->cur][VT].p, e->d_type_goff[VT].p,
-                                                             e->d_delta.p, e->d_state[e->cur ^ 1][VT].p);
-  check_launch(e);
+  LAUNCH(e, K_RETRACT, retract_kernel<VT><<<(n + 127) / 128, 128, 0, e->stream>>>(n, e->d_state[e->cur][VT].p, e->d_type_goff[VT].p,
+                                                             e->d_delta.p, e->d_state[e->cur ^ 1][VT].p));
 }
 static void retract(Engine* e) {
   need_device(e);
@@ -1031,6 +1044,26 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
   const Plan& p = e->plan;
   out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)p.arena_doubles;
   out[4] = (double)p.n_small; out[5] = (double)p.n_large; out[6] = p.flops_large; out[7] = p.assembly_bytes;
+  out[8] = p.flops_syrk_frontal; out[9] = p.flops_syrk_schur; out[10] = p.bytes_backsolve;
+  {
+    // small fronts also read the whitened rows of their own factors
+    static const int kMW[7] = {21, 78, 26, 12, 42, 90, 12};
+    double b = p.bytes_small;
+    for (int32_t c = 0; c < p.n_cliques; ++c)
+      if (p.F[c] + p.S[c] + 1 <= kSmallMax)
+        for (int64_t q = p.fac_off[c]; q < p.fac_off[c + 1]; ++q) b += 8.0 * kMW[e->g_bucket[p.slots[q].factor]];
+    out[11] = b;
+  }
+  // linearize: variables read once + per-factor indices, measurement, noise + whitened [A|b] written once
+  {
+    double b = 0;
+    for (int t = 0; t < 4; ++t) b += 8.0 * kStateDev[t] * e->vars[t].n;
+    for (int k = 0; k < 7; ++k)
+      b += (double)e->fac[k].n * (4.0 * kNKeys[k] + 8.0 * kZDev[k] + (e->fac[k].any_noise ? 8.0 * kM[k] * kM[k] + 1 : 0) +
+                                  8.0 * kM[k] * kW[k]);
+    out[12] = b;
+  }
+  out[13] = out[14] = out[15] = 0;
   return GTB_OK;
 }
 
@@ -1240,6 +1273,31 @@ gtb_status gtb_set_stage_timing(gtb_engine* e, int on) {
   if (!e) return GTB_ERR_INVALID;
   e->time_stages = on != 0;
   return GTB_OK;
+}
+gtb_status gtb_profile(gtb_engine* e, int on) {
+  if (!e) return GTB_ERR_INVALID;
+  e->profiling = on != 0;
+  e->prof_used = 0;
+  e->prof_class.clear();
+  return GTB_OK;
+}
+int gtb_profile_classes(void) { return K_NUM; }
+const char* gtb_profile_class_name(int k) { return (k >= 0 && k < K_NUM) ? kKernelNames[k] : ""; }
+gtb_status gtb_profile_read(gtb_engine* e, double* total_ms, int64_t* launches) {
+  if (!e || !total_ms || !launches) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  CK(cudaStreamSynchronize(e->stream));
+  for (int k = 0; k < K_NUM; ++k) { total_ms[k] = 0; launches[k] = 0; }
+  for (size_t i = 0; i < e->prof_class.size(); ++i) {
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, e->prof_events[2 * i], e->prof_events[2 * i + 1]));
+    total_ms[e->prof_class[i]] += ms;
+    launches[e->prof_class[i]]++;
+  }
+  e->prof_used = 0;
+  e->prof_class.clear();
+  GTB_CATCH(e)
 }
 void* gtb_stream(gtb_engine* e) { return e ? (void*)e->stream : nullptr; }
 

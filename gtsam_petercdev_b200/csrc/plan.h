@@ -56,6 +56,10 @@ struct Plan {
   std::vector<int32_t> level_n_small;   // number of small-front cliques at each level
   // statistics
   double flops = 0, flops_large = 0, assembly_bytes = 0;
+  double flops_syrk_frontal = 0;   // large fronts: trailing updates inside the frontal rows (syrk_kernel mode 0)
+  double flops_syrk_schur = 0;     // large fronts: C -= S^T S (syrk_kernel mode 1)
+  double bytes_small = 0;          // small fronts: factor rows read + child Schur complements read + front written
+  double bytes_backsolve = 0;      // [R S d] read once + delta written
   int32_t max_front = 0;
   int64_t n_small = 0, n_large = 0;
 };

@@ -233,6 +233,25 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P) {
     p.flops += fl;
     if (small) p.n_small++; else { p.n_large++; p.flops_large += fl; }
     p.assembly_bytes += 8.0 * (0.5 * dim * (dim + 1) + 0.5 * s1 * (s1 + 1));
+    p.bytes_backsolve += 8.0 * (0.5 * f * (f + 1) + f * s1 + f);
+    if (small) {
+      // own factor rows are added below once the slots are known; front written once, Schur block read by the parent
+      p.bytes_small += 8.0 * 0.5 * dim * (dim + 1);
+    } else {
+      p.flops_syrk_schur += f * s1 * (s1 + 1);
+      for (int32_t k0 = 0; k0 < F; k0 += 32) {
+        const int32_t kb = std::min(32, F - k0);
+        const double rb = k0 + kb, rows = F - rb;                       // rows [rb, F), columns [i, dim)
+        p.flops_syrk_frontal += 2.0 * kb * (rows * (dim - rb) - 0.5 * rows * (rows - 1));
+      }
+    }
+  }
+  for (int32_t c = 0; c < C; ++c) {
+    const int32_t par = p.parent[c];
+    if (par >= 0 && p.F[par] + p.S[par] + 1 <= small_max) {
+      const double s1 = p.S[c] + 1;
+      p.bytes_small += 8.0 * 0.5 * s1 * (s1 + 1);
+    }
   }
   p.arena_doubles = arena;
 

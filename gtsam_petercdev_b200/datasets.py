@@ -232,6 +232,16 @@ def ba_shape(n_cams=1723, n_points=156000, mean_obs=4.35, window=60, long_range=
     uv, z = _project(Rc[cam_idx], tc[cam_idx], cal[cam_idx], pts[pt_idx])
     ok = z > 0.5
     cam_idx, pt_idx, uv = cam_idx[ok], pt_idx[ok], uv[ok]
+    # every variable must appear in the graph (the reference's COLAMD ordering is built from the graph, and LM damping
+    # adds a prior per Values entry): drop points left with fewer than two observations and renumber
+    cnt = np.bincount(pt_idx, minlength=n_points)
+    keep_pt = cnt >= 2
+    sel = keep_pt[pt_idx]
+    cam_idx, pt_idx, uv = cam_idx[sel], pt_idx[sel], uv[sel]
+    remap = np.cumsum(keep_pt) - 1
+    pt_idx = remap[pt_idx]
+    pts = pts[keep_pt]
+    n_points = len(pts)
     uv = uv + rng.normal(size=uv.shape) * pixel_sigma
 
     # initial estimate: truth perturbed on the pose tangent and on the points

@@ -107,9 +107,10 @@ class Engine:
         keys = np.zeros(nk.value, dtype=np.uint64)
         parent = np.zeros(nc.value, dtype=np.int64)
         self._ck(self.lib.gtb_plan_get(self.h, _ptr(nfrontal), _ptr(nkeys), _ptr(keys), _ptr(parent)))
-        stats = np.zeros(8)
+        stats = np.zeros(16)
         self._ck(self.lib.gtb_plan_stats(self.h, _ptr(stats)))
-        names = ["levels", "max_front", "flops", "arena_doubles", "n_small", "n_large", "flops_large", "assembly_bytes"]
+        names = ["levels", "max_front", "flops", "arena_doubles", "n_small", "n_large", "flops_large", "assembly_bytes",
+                 "flops_syrk_frontal", "flops_syrk_schur", "bytes_backsolve", "bytes_small", "bytes_linearize"]
         return dict(clique_nfrontal=nfrontal, clique_nkeys=nkeys, clique_keys=keys, clique_parent=parent,
                     n_conditional_doubles=ncond.value, n_scalars=ns.value, stats=dict(zip(names, stats.tolist())))
 
@@ -214,6 +215,16 @@ class Engine:
 
     def set_stage_timing(self, on):
         self._ck(self.lib.gtb_set_stage_timing(self.h, int(bool(on))))
+
+    def profile(self, on=True):
+        self._ck(self.lib.gtb_profile(self.h, int(bool(on))))
+
+    def profile_read(self):
+        """{kernel class: (total ms, launches)} since the last read, from per-launch CUDA events on the engine stream."""
+        n = self.lib.gtb_profile_classes()
+        ms, cnt = np.zeros(n), np.zeros(n, dtype=np.int64)
+        self._ck(self.lib.gtb_profile_read(self.h, _ptr(ms), _ptr(cnt)))
+        return {self.lib.gtb_profile_class_name(k).decode(): (float(ms[k]), int(cnt[k])) for k in range(n) if cnt[k]}
 
     def stream(self):
         return self.lib.gtb_stream(self.h)

@@ -95,8 +95,11 @@ gtb_status gtb_plan_sizes(const gtb_engine* e, int64_t* n_cliques, int64_t* n_cl
 gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, uint64_t* keys,
                         int64_t* parent);
 /* Plan statistics: out[0]=levels, [1]=max front dim, [2]=sum flops (POTRF+TRSM+SYRK), [3]=front arena
- * doubles, [4]=small-front cliques, [5]=large-front cliques, [6]=flops in large fronts, [7]=assembly bytes */
-gtb_status gtb_plan_stats(const gtb_engine* e, double* out8);
+ * doubles, [4]=small-front cliques, [5]=large-front cliques, [6]=flops in large fronts, [7]=assembly bytes,
+ * [8]=flops of the frontal trailing updates of large fronts, [9]=flops of their Schur updates, [10]=algorithmic
+ * bytes of back-substitution, [11]=algorithmic bytes of small-front elimination, [12]=algorithmic bytes of
+ * linearize (SURVEY 8d formula), [13..15]=0                                                                */
+gtb_status gtb_plan_stats(const gtb_engine* e, double* out16);
 
 /* ---- per outer iteration ---------------------------------------------------------------------------- */
 /* NonlinearFactorGraph::linearize(values): whitened [A|b] of every factor into per-bucket device buffers. */
@@ -178,6 +181,13 @@ int64_t gtb_kernel_launches(const gtb_engine* e);
 gtb_status gtb_stage_ms(gtb_engine* e, double* out8);
 /* Per-stage event timing synchronises the stream after every stage; turn it off (on = 0) for throughput runs. */
 gtb_status gtb_set_stage_timing(gtb_engine* e, int on);
+/* Per-launch CUDA-event timing by kernel class (on the engine stream).  gtb_profile(e, 1) starts recording,
+ * gtb_profile_read sums elapsed ms and launch counts per class since the last read (arrays of
+ * gtb_profile_classes() entries) and clears the record.                                                   */
+gtb_status gtb_profile(gtb_engine* e, int on);
+int gtb_profile_classes(void);
+const char* gtb_profile_class_name(int k);
+gtb_status gtb_profile_read(gtb_engine* e, double* total_ms, int64_t* launches);
 /* Raw stream handle (cudaStream_t) for callers that time with their own events.                          */
 void* gtb_stream(gtb_engine* e);
 

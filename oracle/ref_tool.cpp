@@ -9,7 +9,7 @@
 // delta, errors, LM traces, and stage timings for the CPU baseline.
 //
 //   ref_tool <problem.gtb> <out.gtb> key=value ...
-//     mode=linearize | solve | lm | gn | time | symbolic
+//     mode=linearize | solve | lm | gn | time | symbolic | ordering
 //     ordering=colamd|metis|schur|natural|file   (file: array "ordering" in problem)
 //     lambda=<double> diag=0|1                    (solve: LM damping, 0 => none)
 //     ceres=0|1 maxiter=<n> lambda0=<d>           (lm)
@@ -315,7 +315,10 @@ int main(int argc, char** argv) {
     out.put_f64("error0", {B.graph.error(B.values)});
     out.put_i64("n_factors", {(int64_t)B.graph.size()});
 
-    if (mode == "linearize") {
+    if (mode == "ordering") {
+      Ordering ord = make_ordering(P, B);
+      dump_ordering(ord, out);
+    } else if (mode == "linearize") {
       auto gfg = B.graph.linearize(B.values);
       dump_jacobians(B, *gfg, out);
       VectorValues hd = gfg->hessianDiagonal();
@@ -404,8 +407,10 @@ int main(int argc, char** argv) {
       Ordering ord = make_ordering(P, B);
       int iters = (int)optd("iters", 3);
       double lambda = optd("lambda", 1e-5);
+      int warm = (int)optd("warm", 1);
+      double trial_error = 0, lin0 = 0, lin1 = 0;
       std::vector<double> tl, te, tb, tt;
-      for (int it = 0; it < iters + 1; ++it) {
+      for (int it = 0; it < iters + warm; ++it) {
         double a = now();
         auto gfg = B.graph.linearize(B.values);
         double b = now();
@@ -418,12 +423,13 @@ int main(int argc, char** argv) {
         Values nv = B.values.retract(delta);
         double en = B.graph.error(nv);
         double e = now();
-        (void)e0; (void)e1; (void)en;
-        if (it == 0) continue;  // warm-up
+        lin0 = e0; lin1 = e1; trial_error = en;
+        if (it < warm) continue;  // warm-up
         tl.push_back(b - a); te.push_back(c - b); tb.push_back(d - c); tt.push_back(e - a);
       }
       out.put_f64("t_linearize", tl); out.put_f64("t_eliminate", te);
       out.put_f64("t_backsub", tb); out.put_f64("t_iter", tt);
+      out.put_f64("trial_error", {trial_error}); out.put_f64("linear_error0", {lin0}); out.put_f64("linear_error1", {lin1});
     } else {
       throw std::runtime_error("unknown mode " + mode);
     }

@@ -1,0 +1,76 @@
+"""C-ABI surface and host-side behaviour that needs no GPU."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from gtsam_petercdev_b200 import capi, datasets
+from gtsam_petercdev_b200.engine import Engine, EngineError
+from gtsam_petercdev_b200.problem import Problem
+
+
+def test_library_exports_every_header_symbol():
+    lib = capi.lib()
+    names = capi.header_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/gtsam_b200.h but not exported"
+    assert set(names) == set(capi._SIGS), "ctypes signature table out of sync with the header"
+    assert b"sm_100a" in lib.gtb_version()
+
+
+def test_host_only_engine_refuses_numeric_calls():
+    p = datasets.m3500_shape(200, 10, seed=1)
+    e = Engine(p, device=-1)
+    e.set_ordering("natural")
+    assert e.plan()["stats"]["levels"] >= 1
+    for call in (e.linearize, e.backsolve, e.retract, lambda: e.error(0), lambda: e.factorize(0.0)):
+        with pytest.raises(EngineError) as ei:
+            call()
+        assert ei.value.status in (capi.ERR_NO_DEVICE, capi.ERR_INVALID)
+    with pytest.raises(EngineError) as ei:
+        e.linearize()
+    assert ei.value.status == capi.ERR_NO_DEVICE
+
+
+def test_missing_key_and_wrong_type_are_rejected():
+    p = datasets.m3500_shape(200, 5, seed=2)
+    a = dict(p.a)
+    a["between2_keys"] = a["between2_keys"].copy()
+    a["between2_keys"][3, 1] = 10 ** 6
+    with pytest.raises(EngineError) as ei:
+        Engine(Problem(a), device=-1)
+    assert ei.value.status == capi.ERR_KEY_MISSING
+
+
+def test_constrained_noise_is_rejected():
+    p = datasets.m3500_shape(200, 5, seed=2)
+    a = dict(p.a)
+    a["prior2_nk"] = np.array([2], dtype=np.int32)
+    a["prior2_noise"] = np.array([[1e-9, 1.0, 1.0, 0, 0, 0, 0, 0, 0]])
+    with pytest.raises(EngineError) as ei:
+        Engine(Problem(a), device=-1)
+    assert ei.value.status == capi.ERR_NOISE_MODEL
+
+
+def test_bad_ordering_is_rejected():
+    p = datasets.m3500_shape(200, 5, seed=2)
+    e = Engine(p, device=-1)
+    keys = p.a["pose2_keys"]
+    with pytest.raises(EngineError):
+        e.set_ordering(keys[:-1])
+    with pytest.raises(EngineError):
+        e.set_ordering(np.concatenate([keys[:-1], keys[:1]]))
+    with pytest.raises(EngineError):
+        e.set_ordering("schur")
+
+
+def test_unconnected_variable_is_inconsistent():
+    p = datasets.m3500_shape(200, 5, seed=2)
+    a = dict(p.a)
+    a["pose2_keys"] = np.concatenate([a["pose2_keys"], np.array([999], dtype=np.uint64)])
+    a["pose2"] = np.concatenate([a["pose2"], np.zeros((1, 3))])
+    e = Engine(Problem(a), device=-1)
+    with pytest.raises(EngineError) as ei:
+        e.set_ordering("natural")
+    assert ei.value.status == capi.ERR_INCONSISTENT
