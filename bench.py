@@ -256,8 +256,7 @@ def main():
         hbm, peak_src = 6650.0, "fallback"
     # algorithmic work per step of each candidate class
     work = {
-        "syrk_frontal": ("tensor", st["flops_syrk_frontal"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
-        "syrk_schur": ("tensor", st["flops_syrk_schur"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
+        "front_step": ("tensor", st["flops_large"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
         "small_front": ("hbm", st["bytes_small"] / 1e9, hbm, "GB/s"),
         "linearize": ("hbm", st["bytes_linearize"] / 1e9, hbm, "GB/s"),
         "backsolve": ("hbm", st["bytes_backsolve"] / 1e9, hbm, "GB/s"),

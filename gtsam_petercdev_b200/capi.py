@@ -64,6 +64,7 @@ _SIGS = {
     "gtb_profile_classes": (C.c_int, []),
     "gtb_profile_class_name": (C.c_char_p, [C.c_int]),
     "gtb_profile_read": (C.c_int, [_P, _P, _P]),
+    "gtb_profile_read_raw": (C.c_int64, [_P, _P, _P, C.c_int64]),
     "gtb_stream": (_P, [_P]),
 }
 

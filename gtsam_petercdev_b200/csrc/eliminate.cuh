@@ -26,7 +26,7 @@ struct CliqueDev {
   int32_t child_begin, child_end;
   int32_t pmap_off, gidx_off;
   int32_t first_key_var;  // variable id of the first frontal key (failure reporting)
-  int32_t pad;
+  int32_t dfac_off;       // large fronts: offset of the factored diagonal blocks' side buffer (doubles)
 };
 
 struct SlotDev { int32_t col0, col1, bucket, index; };
@@ -38,9 +38,13 @@ struct ElimDev {
   const int32_t* pmap;
   const int32_t* gidx;
   double* arena;
+  double* dfac;         // side buffer for the factored diagonal blocks of large fronts
   const double* Ab[7];
   const double* damp;   // per global scalar, or nullptr
   int32_t* fail;        // min failing clique id, initialised to INT_MAX
+  long long* dbg;       // optional cycle probe of role A (GTB_DEBUG & 8)
+  int32_t dbg_clique;
+  int32_t debug;        // experiment switches (GTB_DEBUG env): 1 skip tile tasks, 2 skip role-A column work, 4 skip role A
 };
 
 __constant__ int c_M[7] = {3, 6, 2, 3, 6, 9, 3};
@@ -188,107 +192,21 @@ __global__ void __launch_bounds__(256) large_children_kernel(ElimDev E, const Ch
 }
 
 // ---- blocked partial Cholesky ---------------------------------------------------------------------
-constexpr int NB = 32;    // panel height
-constexpr int TW = 64;    // tile width
+// Right-looking with one-panel look-ahead, ONE launch per panel step for all large fronts of a level:
+//   step p, role A (per clique, per 256-column slice): bring row panel p up to date with panel p-1, factor its
+//                   32 x 32 diagonal block (every slice redundantly, in shared memory), solve the slice
+//   step p, role B: trailing update by panel p-1 of the frontal rows below row panel p (64 x 64 DMMA tiles)
+//   step np (after the clique's last panel): Schur complement C -= S^T S with K = F, and the factored diagonal
+//                   blocks move from their side buffer into the front
+// Role A of step p and role B of step p touch disjoint rows, and both only read panel p-1, so no CTA waits on
+// another inside a launch.
+constexpr int NB = 32;       // panel height
+constexpr int TW = 64;       // tile width
 constexpr int LDT = NB + 4;  // shared leading dimension of a K x 64 operand tile (K contiguous), 36: conflict-free
-
-// Panel step p, part 1: factor the NB x NB diagonal block in place (one CTA per clique).
-__global__ void __launch_bounds__(256) potrf_kernel(ElimDev E, const int32_t* __restrict__ list, int p) {
-  const int c = list[blockIdx.x];
-  const CliqueDev ci = E.cliques[c];
-  const int k0 = p * NB;
-  if (k0 >= ci.F) return;
-  const int kb = min(NB, ci.F - k0);
-  double* A = E.arena + ci.front_off;
-  const int ld = ci.ld;
-  __shared__ double D[NB][NB + 1];
-  const int tid = threadIdx.x;
-  for (int idx = tid; idx < kb * kb; idx += blockDim.x) {
-    const int j = idx / kb, i = idx - j * kb;
-    D[i][j] = (i <= j) ? A[(k0 + i) + (int64_t)(k0 + j) * ld] : 0.0;
-  }
-  __syncthreads();
-  bool ok = true;
-  for (int k = 0; k < kb; ++k) {
-    const double piv = D[k][k];
-    if (!(piv > 0.0)) { ok = false; break; }  // Eigen LLT NumericalIssue
-    const double r = sqrt(piv);
-    __syncthreads();
-    if (tid > k && tid < kb) D[k][tid] /= r;
-    if (tid == k) D[k][k] = r;
-    __syncthreads();
-    const int cnt = kb - k - 1;
-    for (int idx = tid; idx < cnt * cnt; idx += blockDim.x) {
-      const int jj = idx / cnt, ii = idx - jj * cnt;
-      if (ii <= jj) D[k + 1 + ii][k + 1 + jj] -= D[k][k + 1 + ii] * D[k][k + 1 + jj];
-    }
-    __syncthreads();
-  }
-  if (!ok) {
-    // poison the block so dependants cannot look valid, and report
-    for (int idx = tid; idx < kb * kb; idx += blockDim.x) {
-      const int j = idx / kb, i = idx - j * kb;
-      if (i <= j) A[(k0 + i) + (int64_t)(k0 + j) * ld] = __longlong_as_double(0x7ff8000000000000LL);
-    }
-    if (tid == 0) atomicMin(E.fail, c);
-    return;
-  }
-  for (int idx = tid; idx < kb * kb; idx += blockDim.x) {
-    const int j = idx / kb, i = idx - j * kb;
-    if (i <= j) A[(k0 + i) + (int64_t)(k0 + j) * ld] = D[i][j];
-  }
-  if (k0 + kb == ci.F && tid == 0) {  // last panel: exponent test (base/cholesky.cpp:146-158)
-    bool good;
-    if (ci.F >= 2) {
-      const double r2 = (kb >= 2) ? D[kb - 2][kb - 2] : A[(ci.F - 2) + (int64_t)(ci.F - 2) * ld];
-      good = frexp_exp(r2) - frexp_exp(D[kb - 1][kb - 1]) < 12;
-    } else {
-      good = frexp_exp(D[0][0]) > -12;
-    }
-    if (!good) atomicMin(E.fail, c);
-  }
-}
-
-// Panel step p, part 2: row panel R12 = R11^-T A12; blockIdx.y = clique, blockIdx.x = 128-column slice, one
-// thread per column, R11 staged in shared memory.
-__global__ void __launch_bounds__(128) trsm_kernel(ElimDev E, const int32_t* __restrict__ list, int p) {
-  const int c = list[blockIdx.y];
-  const CliqueDev ci = E.cliques[c];
-  const int k0 = p * NB;
-  if (k0 >= ci.F) return;
-  const int kb = min(NB, ci.F - k0);
-  const int dim = ci.F + ci.S + 1;
-  const int j0 = k0 + kb + blockIdx.x * 128;
-  if (j0 >= dim) return;
-  double* A = E.arena + ci.front_off;
-  const int ld = ci.ld;
-  __shared__ double D[NB][NB + 1];
-  const int tid = threadIdx.x;
-  for (int idx = tid; idx < kb * kb; idx += blockDim.x) {
-    const int j = idx / kb, i = idx - j * kb;
-    D[i][j] = (i <= j) ? A[(k0 + i) + (int64_t)(k0 + j) * ld] : 0.0;
-  }
-  __syncthreads();
-  const int j = j0 + tid;
-  if (j >= dim) return;
-  double x[NB];
-  double* col = A + k0 + (int64_t)j * ld;
-#pragma unroll
-  for (int i = 0; i < NB; ++i) x[i] = (i < kb) ? col[i] : 0.0;
-#pragma unroll
-  for (int i = 0; i < NB; ++i) {
-    if (i < kb) {
-      double acc = x[i];
-#pragma unroll
-      for (int l = 0; l < NB; ++l)
-        if (l < i) acc -= D[l][i] * x[l];
-      x[i] = acc / D[i][i];
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < NB; ++i)
-    if (i < kb) col[i] = x[i];
-}
+constexpr int SLICE = 7 * 32;   // columns per role-A CTA: warp 0 factors the diagonal block, warps 1..7 own 32 columns
+constexpr int kStepSmemTile = 4 * TW * LDT * (int)sizeof(double);                       // two double-buffered operand tiles
+constexpr int kStepSmemA = (3 * NB * LDT + 2 * NB + 7 * (NB * LDT + NB * 12)) * (int)sizeof(double);
+constexpr int kStepSmem = kStepSmemA > kStepSmemTile ? kStepSmemA : kStepSmemTile;
 
 // FP64 tensor-core tile: m8n8k4 DMMA (mma.sync), D = A * B + C
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
@@ -297,70 +215,66 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                : "d"(a), "d"(b));
 }
 
-// Symmetric update of the upper triangle:  C[i, j] -= sum_{k in [ka, kb)} R[k, i] * R[k, j]
-// for i in [row_begin, row_end), j in [max(i, row_begin), dim), tiles of 64 x 64, operands staged through shared
-// memory in K-chunks of NB, products on the FP64 tensor pipe.
-//   mode 0 (frontal trailing update of panel p): ka = p*NB, kb = min(ka+NB, F), rows [kb, F)
-//   mode 1 (Schur complement):                   ka = 0,    kb = F,            rows [F, dim)
-// grid: x = column tile, y = row tile, z = clique in list.  256 threads = 8 warps as 2 (rows) x 4 (cols); each
-// warp owns a 32 x 16 sub-tile = 4 x 2 DMMA tiles.
-__global__ void __launch_bounds__(256) syrk_kernel(ElimDev E, const int32_t* __restrict__ list, int mode, int p) {
-  const int c = list[blockIdx.z];
-  const CliqueDev ci = E.cliques[c];
-  const int F = ci.F, dim = F + ci.S + 1, ld = ci.ld;
-  int ka, kb, rb, re;
-  if (mode == 0) {
-    ka = p * NB;
-    if (ka >= F) return;
-    kb = min(ka + NB, F);
-    rb = kb;
-    re = F;
-  } else {
-    ka = 0; kb = F; rb = F; re = dim;
-  }
-  const int r0 = rb + blockIdx.y * TW;
-  const int c0 = rb + blockIdx.x * TW;
-  if (blockIdx.x < blockIdx.y || r0 >= re || c0 >= dim) return;
-  double* A = E.arena + ci.front_off;
-
-  __shared__ __align__(16) double Xs[TW * LDT];
-  __shared__ __align__(16) double Ys[TW * LDT];
+// C[i, j] -= sum_{k in [ka, kend)} R[k, i] * R[k, j] for the 64 x 64 tile at (r0, c0), rows < re, upper triangle.
+// 256 threads = 8 warps as 2 (rows) x 4 (cols); each warp owns 32 x 16 = 4 x 2 DMMA tiles.  Operands are staged
+// through double-buffered shared memory in K-chunks of 32 (global loads of chunk n+1 overlap the DMMAs of chunk n).
+__device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int dim, int r0, int c0, int re, int ka,
+                                            int kend, double* sm) {
+  double* Xs = sm;                 // [2][TW * LDT]
+  double* Ys = sm + 2 * TW * LDT;  // [2][TW * LDT]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int wr = warp >> 2, wc = warp & 3;  // warp row (0..1) and column (0..3)
+  const int wr = warp >> 2, wc = warp & 3;
   const int g = lane >> 2, t = lane & 3;
   double acc[4][2][2];
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
     for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-
-  const int lk = tid & 31;          // k within the chunk: one warp reads 32 consecutive doubles of one column
-  const int lc0 = tid >> 5;        // first of 8 columns (stride 8) this thread loads
-  for (int kc = ka; kc < kb; kc += NB) {
-    const int kn = min(NB, kb - kc);
+  const int lc0 = tid >> 5;   // first of 8 operand columns (stride 8); lane = k within the chunk
+  double xr[8], yr[8];
+  auto fetch = [&](int kc) {
+    const int kn = min(NB, kend - kc);
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
       const int lcol = lc0 + 8 * q;
       const int xi = r0 + lcol, yj = c0 + lcol;
-      Xs[lcol * LDT + lk] = (xi < dim && lk < kn) ? A[kc + lk + (int64_t)xi * ld] : 0.0;
-      Ys[lcol * LDT + lk] = (yj < dim && lk < kn) ? A[kc + lk + (int64_t)yj * ld] : 0.0;
+      xr[q] = (xi < dim && lane < kn) ? A[kc + lane + (int64_t)xi * ld] : 0.0;
+      yr[q] = (yj < dim && lane < kn) ? A[kc + lane + (int64_t)yj * ld] : 0.0;
     }
-    __syncthreads();
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int lcol = lc0 + 8 * q;
+      Xs[buf * TW * LDT + lcol * LDT + lane] = xr[q];
+      Ys[buf * TW * LDT + lcol * LDT + lane] = yr[q];
+    }
+  };
+  fetch(ka);
+  stash(0);
+  __syncthreads();
+  int buf = 0;
+  for (int kc = ka; kc < kend; kc += NB) {
+    const bool more = kc + NB < kend;
+    if (more) fetch(kc + NB);
+    const double* X = Xs + buf * TW * LDT;
+    const double* Y = Ys + buf * TW * LDT;
 #pragma unroll
     for (int ks = 0; ks < NB; ks += 4) {
       double af[4], bf[2];
 #pragma unroll
-      for (int a = 0; a < 4; ++a) af[a] = Xs[(wr * 32 + a * 8 + g) * LDT + ks + t];
+      for (int a = 0; a < 4; ++a) af[a] = X[(wr * 32 + a * 8 + g) * LDT + ks + t];
 #pragma unroll
-      for (int b = 0; b < 2; ++b) bf[b] = Ys[(wc * 16 + b * 8 + g) * LDT + ks + t];
+      for (int b = 0; b < 2; ++b) bf[b] = Y[(wc * 16 + b * 8 + g) * LDT + ks + t];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 2; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
     }
+    if (more) stash(buf ^ 1);
     __syncthreads();
+    buf ^= 1;
   }
-  // epilogue: C -= acc on the upper triangle
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
@@ -374,36 +288,400 @@ __global__ void __launch_bounds__(256) syrk_kernel(ElimDev E, const int32_t* __r
     }
 }
 
-// ----------------------------------------------------------------------------------------------------
-// back-substitution: x_F = R^-1 (d - S x_S), one CTA per clique, levels from the roots down
-// (linear/linearAlgorithms-inst.h:54-116)
-// ----------------------------------------------------------------------------------------------------
-__global__ void backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, double* __restrict__ delta) {
-  extern __shared__ double sh[];
-  const int c = list[blockIdx.x];
+// number of tile tasks of a trapezoid: nrt tile rows, nct tile columns, only tiles with tx >= ty
+__host__ __device__ __forceinline__ int trapezoid_tiles(int nrt, int nct) {
+  if (nrt <= 0 || nct <= 0) return 0;
+  if (nrt > nct) nrt = nct;
+  return nrt * nct - nrt * (nrt - 1) / 2;
+}
+__device__ __forceinline__ void trapezoid_decode(int t, int nct, int& ty, int& tx) {
+  ty = 0;
+  while (t >= nct - ty) { t -= nct - ty; ++ty; }
+  tx = ty + t;
+}
+// tasks of clique (F, dim) at panel step p (host mirrors this to size the grid)
+__host__ __device__ __forceinline__ int step_tasks(int F, int dim, int p) {
+  const int np = (F + NB - 1) / NB;
+  if (p < np) {
+    const int k0 = p * NB, kb = (F - k0 < NB) ? F - k0 : NB, rest0 = k0 + kb;
+    int n = (dim - rest0 + SLICE - 1) / SLICE;
+    if (p >= 1) n += trapezoid_tiles((F - rest0 + TW - 1) / TW, (dim - rest0 + TW - 1) / TW);
+    return n;
+  }
+  if (p == np) {
+    const int nt = (dim - F + TW - 1) / TW;
+    return nt * (nt + 1) / 2;
+  }
+  return 0;
+}
+
+struct StepTask { int32_t clique; int32_t task; };
+
+__global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTask* __restrict__ tasks, int p) {
+  extern __shared__ __align__(16) double sm[];
+  const StepTask me = tasks[blockIdx.x];   // compact list: role-A slices (the critical path) first, no empty CTAs
+  const int c = me.clique;
   const CliqueDev ci = E.cliques[c];
+  const int F = ci.F, dim = F + ci.S + 1, ld = ci.ld;
+  const int np = (F + NB - 1) / NB;
+  if (p > np) return;
+  double* A = E.arena + ci.front_off;
+  double* dfac = E.dfac + ci.dfac_off;   // np blocks of NB x NB, row-major
+  int task = me.task;
+  const int tid = threadIdx.x;
+  if (p == np) {
+    const int nt = (dim - F + TW - 1) / TW;
+    if (task >= nt * (nt + 1) / 2) return;
+    int ty, tx;
+    trapezoid_decode(task, nt, ty, tx);
+    if (!(E.debug & 1)) tile_update(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
+    if (task == 0) {
+      // factored diagonal blocks: side buffer -> front (nothing in this launch reads them)
+      for (int idx = tid; idx < np * NB * NB; idx += blockDim.x) {
+        const int b = idx / (NB * NB), r = idx - b * NB * NB, i = r / NB, j = r - i * NB;
+        const int gi = b * NB + i, gj = b * NB + j;
+        if (i <= j && gj < F) A[gi + (int64_t)gj * ld] = dfac[idx];
+      }
+    }
+    return;
+  }
+  const int k0 = p * NB, kb = min(NB, F - k0), rest0 = k0 + kb;
+  const int nA = (dim - rest0 + SLICE - 1) / SLICE;
+  if (task >= nA) {
+    if (p == 0) return;
+    task -= nA;
+    const int nrt = (F - rest0 + TW - 1) / TW, nct = (dim - rest0 + TW - 1) / TW;
+    if (task >= trapezoid_tiles(nrt, nct)) return;
+    int ty, tx;
+    trapezoid_decode(task, nct, ty, tx);
+    if (!(E.debug & 1)) tile_update(A, ld, dim, rest0 + ty * TW, rest0 + tx * TW, F, k0 - NB, k0, sm);
+    return;
+  }
+  // ---- role A: slice `task` of row panel p ----
+  // warp 0 factors the diagonal block; warps 1..7 own 32 columns each.  All GEMM-shaped work (look-ahead update,
+  // blocked triangular solve with 8 x 8 diagonal inverses) runs on the FP64 tensor pipe.
+  if (E.debug & 4) return;
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  double* Ps = sm;                    // Ps[i * LDT + l] = R[k0-32+l, k0+i]            (panel p-1, columns of D)
+  double* Ds = Ps + NB * LDT;         // Ds[i * LDT + l] = D(l, i), l <= i             (column i of the block)
+  double* Ws = Ds + NB * LDT;         // Ws[i * LDT + l] = inv(D_bb)(l, i) for l, i in the same 8-block b
+  double* dinv = Ws + NB * LDT;       // 1 / D(i, i)
+  int* s_ok = reinterpret_cast<int*>(dinv + NB);
+  double* Xs = dinv + 2 * NB + (warp > 0 ? warp - 1 : 0) * (NB * LDT + NB * 12);   // Xs[c * LDT + i]
+  double* Ts = Xs + NB * LDT;                                                       // Ts[c * 12 + ii]
+  const bool probe = E.dbg && p == 1 && task == 0 && c == E.dbg_clique;
+  long long tq0 = 0, tq1 = 0, tq2 = 0, tq3 = 0, tq4 = 0, tq5 = 0;
+  if (probe) tq0 = clock64();
+  // column warps: issue every global load of the slice up front (fragment layout), they overlap the diagonal-block loads
+  const int jbase = rest0 + task * SLICE + (warp - 1) * 32;
+  const bool colwarp = warp > 0 && jbase < dim;
+  double qf[8][4], b0[4][4][2];
+  if (colwarp) {
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int j = jbase + nt * 8 + g;
+        qf[ks][nt] = (p >= 1 && j < dim) ? A[(k0 - NB + ks * 4 + t) + (int64_t)j * ld] : 0.0;
+      }
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int i = mt * 8 + g, j = jbase + nt * 8 + 2 * t + e;
+          b0[mt][nt][e] = (j < dim && i < kb) ? A[(k0 + i) + (int64_t)j * ld] : 0.0;
+        }
+  }
+  // diagonal block and the matching columns of panel p-1: one column (32 contiguous doubles) per warp instruction
+  for (int col = warp; col < NB; col += 8) {
+    Ps[col * LDT + lane] = (p >= 1 && col < kb) ? A[(k0 - NB + lane) + (int64_t)(k0 + col) * ld] : 0.0;
+    Ds[col * LDT + lane] = (lane <= col && col < kb) ? A[(k0 + lane) + (int64_t)(k0 + col) * ld] : ((lane == col) ? 1.0 : 0.0);
+    Ws[col * LDT + lane] = 0.0;
+  }
+  __syncthreads();
+  // column warps: X = B - P^T Q (needs only panel p-1)
+  if (colwarp) {
+    double acc[4][4][2];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+    if (p >= 1) {
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+        double af[4];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) af[mt] = Ps[(mt * 8 + g) * LDT + ks * 4 + t];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], af[mt], qf[ks][nt]);
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+          Xs[(nt * 8 + 2 * t + e) * LDT + mt * 8 + g] = b0[mt][nt][e] - acc[mt][nt][e];
+  }
+  if (probe) tq1 = clock64();
+  if (warp == 0) {
+    if (p >= 1) {
+      // look-ahead on the diagonal block: D -= P^T P (upper triangle; the lower one is never read)
+      double acc[4][4][2];
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+#pragma unroll
+      for (int ks = 0; ks < NB; ks += 4) {
+        double af[4];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) af[mt] = Ps[(mt * 8 + g) * LDT + ks + t];
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+          for (int nt = mt; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], af[mt], af[nt]);
+      }
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = mt; nt < 4; ++nt)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int i = mt * 8 + g, jj = nt * 8 + 2 * t + e;
+            if (i <= jj && jj < kb) Ds[jj * LDT + i] -= acc[mt][nt][e];
+          }
+      __syncwarp();
+    }
+    if (probe) tq2 = clock64();
+    // 32 x 32 Cholesky (upper) in registers: lane = column.  Rows >= kb are identity padding.
+    double d[NB];
+#pragma unroll
+    for (int i = 0; i < NB; ++i) d[i] = Ds[lane * LDT + i];
+    bool okw = true;
+    double myinv = 1.0;
+    // software-pipelined: the next pivot column is updated first so that its rsqrt overlaps the rest of the rank-1 update
+    double pk = __shfl_sync(0xffffffffu, d[0], 0);
+    double rinv = rsqrt(pk);
+#pragma unroll
+    for (int k = 0; k < NB; ++k) {
+      okw = okw && (pk > 0.0);               // Eigen LLT NumericalIssue (base/cholesky.cpp:126-128)
+      if (lane > k) d[k] *= rinv;
+      else if (lane == k) { d[k] = pk * rinv; myinv = rinv; }
+      const double ukl = d[k];
+      double pk_next = 1.0, rinv_next = 1.0;
+      if (k + 1 < NB) {
+        const double uki = __shfl_sync(0xffffffffu, d[k], k + 1);
+        if (k + 1 <= lane) d[k + 1] -= uki * ukl;
+        pk_next = __shfl_sync(0xffffffffu, d[k + 1], k + 1);
+        rinv_next = rsqrt(pk_next);
+      }
+#pragma unroll
+      for (int i = k + 2; i < NB; ++i) {
+        const double uki = __shfl_sync(0xffffffffu, d[k], i);
+        if (i <= lane) d[i] -= uki * ukl;
+      }
+      pk = pk_next;
+      rinv = rinv_next;
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i)
+      if (i <= lane) Ds[lane * LDT + i] = d[i];
+    dinv[lane] = myinv;
+    if (lane == 0) *s_ok = okw ? 1 : 0;
+    __syncwarp();
+    // inverses of the four 8 x 8 diagonal blocks: lane = column, back-substitution within its block
+    {
+      const int b8 = lane & ~7, jj = lane & 7;
+      double w[8];
+#pragma unroll
+      for (int i = 7; i >= 0; --i) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int k = i + 1; k < 8; ++k)
+          if (k <= jj) sacc += Ds[(b8 + k) * LDT + b8 + i] * w[k];
+        w[i] = (i == jj) ? myinv : ((i < jj) ? -sacc * dinv[b8 + i] : 0.0);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) Ws[lane * LDT + b8 + i] = w[i];
+    }
+    if (task == 0 && okw) {
+      double* db = dfac + p * NB * NB;
+#pragma unroll
+      for (int i = 0; i < NB; ++i) db[i * NB + lane] = (i <= lane) ? d[i] : 0.0;
+      if (k0 + kb == F) {   // last panel: exponent test (base/cholesky.cpp:146-158)
+        const double dlast = Ds[(kb - 1) * LDT + kb - 1];
+        const double dprev = (kb >= 2) ? Ds[(kb - 2) * LDT + kb - 2] : 1.0;
+        if (lane == 0) {
+          bool good;
+          if (F >= 2) {
+            const double r2 = (kb >= 2) ? dprev : dfac[(p - 1) * NB * NB + (NB - 1) * NB + (NB - 1)];
+            good = frexp_exp(r2) - frexp_exp(dlast) < 12;
+          } else {
+            good = frexp_exp(dlast) > -12;
+          }
+          if (!good) atomicMin(E.fail, c);
+        }
+      }
+    }
+    if (task == 0 && !okw && lane == 0) atomicMin(E.fail, c);
+  }
+  __syncthreads();
+  if (probe) tq3 = clock64();
+  if (!*s_ok || !colwarp) return;
+  // blocked forward substitution Y = R11^-T X in four 8-row stages
+#pragma unroll
+  for (int bi = 0; bi < 4; ++bi) {
+    double acc[4][2];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < bi * 8; ks += 4) {
+      const double a = Ds[(bi * 8 + g) * LDT + ks + t];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) dmma884(acc[nt][0], acc[nt][1], a, Xs[(nt * 8 + g) * LDT + ks + t]);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int cc = nt * 8 + 2 * t + e;
+        Ts[cc * 12 + g] = Xs[cc * LDT + bi * 8 + g] - acc[nt][e];
+      }
+    __syncwarp();
+    double y[4][2];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) y[nt][0] = y[nt][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 8; ks += 4) {
+      const double a = Ws[(bi * 8 + g) * LDT + bi * 8 + ks + t];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) dmma884(y[nt][0], y[nt][1], a, Ts[(nt * 8 + g) * 12 + ks + t]);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) Xs[(nt * 8 + 2 * t + e) * LDT + bi * 8 + g] = y[nt][e];
+    __syncwarp();
+  }
+  if (probe) tq4 = clock64();
+  for (int cc = 0; cc < 32; ++cc) {
+    const int j = jbase + cc;
+    if (j < dim && lane < kb) A[(k0 + lane) + (int64_t)j * ld] = Xs[cc * LDT + lane];
+  }
+  if (probe && lane == 0 && warp == 1) {
+    tq5 = clock64();
+    E.dbg[0] = tq1 - tq0; E.dbg[1] = tq2 - tq1; E.dbg[2] = tq3 - tq2; E.dbg[3] = tq4 - tq3; E.dbg[4] = tq5 - tq4;
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// back-substitution: x_F = R^-1 (d - S x_S), levels from the roots down (linear/linearAlgorithms-inst.h:54-116)
+// WARP = true : one warp per clique (F <= 32, F+S <= 160), kBsWarps cliques per CTA
+// WARP = false: one CTA per clique; blocked TRSV, 32 pivots per step, diagonal block solved by warp 0 in registers
+// ----------------------------------------------------------------------------------------------------
+constexpr int kBsWarps = 8;
+constexpr int kBsWarpDoubles = 32 + 160 + 32;   // rhs, xs, reduction scratch per warp
+
+template <bool WARP>
+__global__ void __launch_bounds__(WARP ? kBsWarps * 32 : 512)
+backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta) {
+  extern __shared__ double sh[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = WARP ? blockIdx.x * kBsWarps + warp : blockIdx.x;
+  if (slot >= count) return;   // WARP: whole warp exits together; CTA: never true
+  const int gsize = WARP ? 32 : (int)blockDim.x;
+  const int gtid = WARP ? lane : (int)threadIdx.x;
+  const CliqueDev ci = E.cliques[list[slot]];
   const int F = ci.F, S = ci.S, N = F + S, ld = ci.ld;
   const double* A = E.arena + ci.front_off;
   const int32_t* g = E.gidx + ci.gidx_off;
-  double* rhs = sh;       // F
-  double* xs = sh + F;    // S
-  const int T = blockDim.x, tid = threadIdx.x;
-  for (int j = tid; j < S; j += T) xs[j] = delta[g[F + j]];
-  __syncthreads();
-  for (int i = tid; i < F; i += T) {
-    double acc = A[i + (int64_t)N * ld];
-    for (int j = 0; j < S; ++j) acc -= A[i + (int64_t)(F + j) * ld] * xs[j];
-    rhs[i] = acc;
+  double* rhs = WARP ? sh + warp * kBsWarpDoubles : sh;     // F (WARP: 32)
+  double* xs = WARP ? rhs + 32 : sh + F;                    // S (WARP: 160)
+  double* red = WARP ? xs + 160 : sh + N;                   // gsize
+  double* xblk = WARP ? rhs : red + gsize;                  // 32 (CTA only; WARP has a single block)
+  auto gsync = [&]() { if (WARP) __syncwarp(); else __syncthreads(); };
+
+  for (int j = gtid; j < S; j += gsize) xs[j] = delta[g[F + j]];
+  gsync();
+  // rhs = d - S x_S
+  if (F >= gsize) {
+    for (int i = gtid; i < F; i += gsize) {
+      double a0 = A[i + (int64_t)N * ld], a1 = 0.0, a2 = 0.0, a3 = 0.0;
+      const double* row = A + i + (int64_t)F * ld;
+      int j = 0;
+      for (; j + 4 <= S; j += 4) {
+        a0 -= row[(int64_t)j * ld] * xs[j];
+        a1 -= row[(int64_t)(j + 1) * ld] * xs[j + 1];
+        a2 -= row[(int64_t)(j + 2) * ld] * xs[j + 2];
+        a3 -= row[(int64_t)(j + 3) * ld] * xs[j + 3];
+      }
+      for (; j < S; ++j) a0 -= row[(int64_t)j * ld] * xs[j];
+      rhs[i] = (a0 + a1) + (a2 + a3);
+    }
+  } else {
+    int Fp = 1;
+    while (Fp < F) Fp <<= 1;
+    const int G = gsize / Fp;
+    const int i = gtid & (Fp - 1), jg = gtid / Fp;
+    double acc = 0.0;
+    if (i < F) {
+      const double* row = A + i + (int64_t)F * ld;
+      for (int j = jg; j < S; j += G) acc -= row[(int64_t)j * ld] * xs[j];
+    }
+    red[gtid] = acc;
+    gsync();
+    if (gtid < F) {
+      double a = A[gtid + (int64_t)N * ld];
+      for (int q = 0; q < G; ++q) a += red[q * Fp + gtid];
+      rhs[gtid] = a;
+    }
   }
-  __syncthreads();
-  for (int k = F - 1; k >= 0; --k) {
-    const double xk = rhs[k] / A[k + (int64_t)k * ld];
+  gsync();
+  // blocked back-substitution with R (upper triangular), bottom block first
+  for (int b0 = ((F - 1) / 32) * 32; b0 >= 0; b0 -= 32) {
+    const int kb = min(32, F - b0);
+    if (WARP || warp == 0) {
+      double r[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k)
+        r[k] = (k < kb && lane <= k && lane < kb) ? A[(b0 + lane) + (int64_t)(b0 + k) * ld] : 1.0;
+      double my = (lane < kb) ? rhs[b0 + lane] : 0.0;
+#pragma unroll
+      for (int k = 31; k >= 0; --k) {
+        if (k < kb) {
+          const double dk = __shfl_sync(0xffffffffu, r[k], k);
+          const double xk = __shfl_sync(0xffffffffu, my, k) / dk;
+          if (lane == k) my = xk;
+          else if (lane < k) my -= r[k] * xk;
+        }
+      }
+      if (lane < kb) {
+        rhs[b0 + lane] = my;
+        if (!WARP) xblk[lane] = my;
+      }
+    }
+    if (WARP) break;   // F <= 32: single block
     __syncthreads();
-    if (tid == 0) rhs[k] = xk;
-    for (int i = tid; i < k; i += T) rhs[i] -= A[i + (int64_t)k * ld] * xk;
+    for (int i = gtid; i < b0; i += gsize) {
+      const double* row = A + i + (int64_t)b0 * ld;
+      double a0 = 0.0, a1 = 0.0;
+#pragma unroll 8
+      for (int k = 0; k < 32; k += 2) {
+        if (k < kb) a0 += row[(int64_t)k * ld] * xblk[k];
+        if (k + 1 < kb) a1 += row[(int64_t)(k + 1) * ld] * xblk[k + 1];
+      }
+      rhs[i] -= a0 + a1;
+    }
     __syncthreads();
   }
-  for (int i = tid; i < F; i += T) delta[g[i]] = rhs[i];
+  gsync();
+  for (int i = gtid; i < F; i += gsize) delta[g[i]] = rhs[i];
 }
 
 }  // namespace gtb

@@ -78,8 +78,11 @@ struct LevelSched {
   int64_t work_begin = 0;     // child extend-add work items for large parents
   int32_t n_work = 0;
   int32_t n_all = 0;          // all cliques at the level (back-substitution)
-  int32_t bs_smem = 0, bs_threads = 32;
+  int64_t bs_begin = 0;       // into the back-substitution list: warp-class cliques first, then CTA-class
+  int32_t n_bs_warp = 0, n_bs_cta = 0, bs_cta_smem = 0;
   int64_t zero_blocks = 0;
+  std::vector<int64_t> step_begin;  // per panel step 0..max_np: range of the compact task list
+  std::vector<int32_t> step_count;
 };
 
 }  // namespace gtb
@@ -120,6 +123,8 @@ struct gtb_engine {
   bool has_plan = false;
   std::vector<LevelSched> sched;
   std::vector<ChildWork> child_work;
+  std::vector<int32_t> bs_list;
+  std::vector<StepTask> step_tasks_list;
 
   // ---- device ----
   DevBuf<double> d_state[2][4];
@@ -129,7 +134,7 @@ struct gtb_engine {
   DevBuf<double> d_z[7], d_noise[7], d_Ab[7];
   DevBuf<int8_t> d_nk[7];
   BucketDev bk[7];
-  DevBuf<double> d_partials, d_scalars, d_delta, d_hdiag, d_damp, d_arena;
+  DevBuf<double> d_partials, d_scalars, d_delta, d_hdiag, d_damp, d_arena, d_dfac;
   int64_t partial_off[7] = {0};
   int64_t n_partials = 0;
   double* h_scalars = nullptr;   // pinned
@@ -137,8 +142,10 @@ struct gtb_engine {
   DevBuf<int32_t> d_inc_bucket, d_inc_index, d_inc_slot, d_var_goff, d_var_dim;
   DevBuf<CliqueDev> d_cliques;
   DevBuf<SlotDev> d_slots;
-  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail;
+  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list;
   DevBuf<ChildWork> d_child_work;
+  DevBuf<StepTask> d_step_tasks;
+  DevBuf<long long> d_dbg;
   bool linearized = false, factorized = false, solved = false, have_hdiag = false;
 
   bool profiling = false;
@@ -280,11 +287,11 @@ struct StageTimer {
 };
 
 // kernel classes for launch counting and optional per-launch event timing
-enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_ZERO, K_LFACT, K_LCHILD, K_POTRF,
-       K_TRSM, K_SYRK, K_SCHUR, K_BACKSOLVE, K_RETRACT, K_NUM };
+enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_ZERO, K_LFACT, K_LCHILD, K_STEP,
+       K_BACKSOLVE, K_RETRACT, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
-                                          "small_front", "large_zero", "large_factors", "large_children", "potrf",
-                                          "trsm", "syrk_frontal", "syrk_schur", "backsolve", "retract"};
+                                          "small_front", "large_zero", "large_factors", "large_children", "front_step",
+                                          "backsolve", "retract"};
 
 static void prof_begin(Engine* e, int k) {
   if (!e->profiling) return;
@@ -530,6 +537,8 @@ static void install_plan(Engine* e) {
   // level schedules
   e->sched.assign(p.n_levels, LevelSched());
   e->child_work.clear();
+  e->bs_list.clear();
+  e->step_tasks_list.clear();
   for (int32_t l = 0; l < p.n_levels; ++l) {
     LevelSched& L = e->sched[l];
     const int64_t b = p.level_off[l], ns = p.level_n_small[l], en = p.level_off[l + 1];
@@ -546,6 +555,28 @@ static void install_plan(Engine* e) {
       L.zero_blocks = std::max<int64_t>(L.zero_blocks, ((int64_t)p.ld[c] * (p.F[c] + p.S[c] + 1) / 2 + 255) / 256);
     }
     L.zero_blocks = std::min<int64_t>(L.zero_blocks, 64);
+    if (L.n_large) {
+      const int max_np = (L.max_F + NB - 1) / NB;
+      for (int sidx = 0; sidx <= max_np; ++sidx) {
+        L.step_begin.push_back((int64_t)e->step_tasks_list.size());
+        // role-A slices of every clique first (critical path), then the tile tasks
+        for (int pass = 0; pass < 2; ++pass)
+          for (int64_t q = L.large_begin; q < en; ++q) {
+            const int32_t c = p.level_cliques[q];
+            const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + NB - 1) / NB;
+            if (sidx > np_c) continue;
+            const int n = step_tasks(F, dim, sidx);
+            int nA = 0;
+            if (sidx < np_c) {
+              const int k0 = sidx * NB, kb = std::min(NB, F - k0);
+              nA = (dim - k0 - kb + SLICE - 1) / SLICE;
+            }
+            const int lo = pass == 0 ? 0 : nA, hi = pass == 0 ? nA : n;
+            for (int t = lo; t < hi; ++t) e->step_tasks_list.push_back(StepTask{c, t});
+          }
+        L.step_count.push_back((int32_t)(e->step_tasks_list.size() - L.step_begin.back()));
+      }
+    }
     L.work_begin = (int64_t)e->child_work.size();
     for (int64_t q = L.large_begin; q < en; ++q) {
       const int32_t c = p.level_cliques[q];
@@ -564,14 +595,18 @@ static void install_plan(Engine* e) {
       }
     }
     L.n_work = (int32_t)(e->child_work.size() - L.work_begin);
-    int32_t maxN = 0, maxFall = 0;
-    for (int64_t q = b; q < en; ++q) {
-      const int32_t c = p.level_cliques[q];
-      maxN = std::max(maxN, p.F[c] + p.S[c]);
-      maxFall = std::max(maxFall, p.F[c]);
-    }
-    L.bs_smem = maxN * (int32_t)sizeof(double);
-    L.bs_threads = maxFall <= 32 ? 32 : (maxFall <= 128 ? 128 : 256);
+    L.bs_begin = (int64_t)e->bs_list.size();
+    int32_t maxN = 0;
+    for (int pass = 0; pass < 2; ++pass)
+      for (int64_t q = b; q < en; ++q) {
+        const int32_t c = p.level_cliques[q];
+        const bool warp_class = p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kSmallMax;
+        if (warp_class != (pass == 0)) continue;
+        e->bs_list.push_back(c);
+        if (warp_class) L.n_bs_warp++;
+        else { L.n_bs_cta++; maxN = std::max(maxN, p.F[c] + p.S[c]); }
+      }
+    L.bs_cta_smem = (maxN + 512 + 32) * (int32_t)sizeof(double);
   }
   // re-sort the small part of every level by dimension and cut into thread classes
   std::vector<int32_t> lc = p.level_cliques;
@@ -595,6 +630,7 @@ static void install_plan(Engine* e) {
 
   cudaStream_t st = e->stream;
   std::vector<CliqueDev> cd(C);
+  int64_t dfac_total = 0;
   for (int32_t c = 0; c < C; ++c) {
     CliqueDev& d = cd[c];
     d.front_off = p.front_off[c];
@@ -604,7 +640,12 @@ static void install_plan(Engine* e) {
     need(p.pmap_off[c] < INT32_MAX && p.gidx_off[c] < INT32_MAX, "plan index overflow");
     d.pmap_off = (int32_t)p.pmap_off[c]; d.gidx_off = (int32_t)p.gidx_off[c];
     d.first_key_var = p.vars[p.vars_off[c]];
-    d.pad = 0;
+    d.dfac_off = 0;
+    if (p.F[c] + p.S[c] + 1 > kSmallMax) {
+      d.dfac_off = (int32_t)dfac_total;
+      dfac_total += (int64_t)((p.F[c] + NB - 1) / NB) * NB * NB;
+      need(dfac_total < INT32_MAX, "diagonal-block side buffer overflow");
+    }
   }
   std::vector<SlotDev> sd(p.slots.size());
   for (size_t i = 0; i < sd.size(); ++i) {
@@ -618,7 +659,11 @@ static void install_plan(Engine* e) {
   e->d_gidx.upload(p.gidx, st);
   e->d_level_cliques.upload(e->plan.level_cliques, st);
   e->d_child_work.upload(e->child_work, st);
+  e->d_bs_list.upload(e->bs_list, st);
+  e->d_step_tasks.upload(e->step_tasks_list, st);
+  e->d_dbg.alloc(8);
   e->d_fail.alloc(1);
+  e->d_dfac.alloc((size_t)dfac_total + NB * NB);
   e->d_arena.alloc((size_t)p.arena_doubles + 16);
   CK(cudaStreamSynchronize(st));
   e->factorized = e->solved = false;
@@ -729,10 +774,14 @@ static void hessian_diagonal(Engine* e) {
 static ElimDev elim_dev(Engine* e, bool damp) {
   ElimDev E;
   E.cliques = e->d_cliques.p; E.slots = e->d_slots.p; E.children = e->d_children.p;
-  E.pmap = e->d_pmap.p; E.gidx = e->d_gidx.p; E.arena = e->d_arena.p;
+  E.pmap = e->d_pmap.p; E.gidx = e->d_gidx.p; E.arena = e->d_arena.p; E.dfac = e->d_dfac.p;
   for (int b = 0; b < 7; ++b) E.Ab[b] = e->d_Ab[b].p;
   E.damp = damp ? e->d_damp.p : nullptr;
   E.fail = e->d_fail.p;
+  static const int dbg = getenv("GTB_DEBUG") ? atoi(getenv("GTB_DEBUG")) : 0;
+  E.debug = dbg;
+  E.dbg = (dbg & 8) ? e->d_dbg.p : nullptr;
+  E.dbg_clique = e->plan.n_cliques - 1;   // the root
   return E;
 }
 
@@ -761,7 +810,8 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   static bool attr = false;
   if (!attr) {
     CK(cudaFuncSetAttribute(small_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CK(cudaFuncSetAttribute(backsolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(front_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem));
+    CK(cudaFuncSetAttribute(backsolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr = true;
   }
   const int32_t* lists = e->d_level_cliques.p;
@@ -777,30 +827,9 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     if (L.n_work) {
       LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
     }
-    const int npanels = (L.max_F + NB - 1) / NB;
-    for (int p = 0; p < npanels; ++p) {
-      LAUNCH(e, K_POTRF, potrf_kernel<<<L.n_large, 256, 0, st>>>(E, ll, p));
-      const int rb = std::min((p + 1) * NB, L.max_F);
-      const int gx_trsm = (L.max_dim - std::min((p + 1) * NB, L.min_F) + 127) / 128;
-      if (gx_trsm > 0) {
-        LAUNCH(e, K_TRSM, trsm_kernel<<<dim3(gx_trsm, L.n_large), 128, 0, st>>>(E, ll, p));
-      }
-      const int gy = (L.max_F - rb + TW - 1) / TW;
-      const int gx = (L.max_dim - rb + TW - 1) / TW;
-      if (gy > 0 && gx > 0) {
-        LAUNCH(e, K_SYRK, syrk_kernel<<<dim3(gx, gy, L.n_large), 256, 0, st>>>(E, ll, 0, p));
-      }
-    }
-    {
-      // Schur complement update: rows [F, dim)
-      int maxS1 = 0;
-      for (int q = 0; q < L.n_large; ++q) {
-        const int32_t c = e->plan.level_cliques[L.large_begin + q];
-        maxS1 = std::max(maxS1, e->plan.S[c] + 1);
-      }
-      const int g = (maxS1 + TW - 1) / TW;
-      LAUNCH(e, K_SCHUR, syrk_kernel<<<dim3(g, g, L.n_large), 256, 0, st>>>(E, ll, 1, 0));
-    }
+    for (size_t s = 0; s < L.step_count.size(); ++s)
+      if (L.step_count[s] > 0)
+        LAUNCH(e, K_STEP, front_step_kernel<<<L.step_count[s], 256, kStepSmem, st>>>(E, e->d_step_tasks.p + L.step_begin[s], (int)s));
   }
   CK(cudaMemcpyAsync(e->h_scalars + 4, e->d_fail.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -819,8 +848,14 @@ static void backsolve(Engine* e) {
   const ElimDev E = elim_dev(e, false);
   for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
     const LevelSched& L = e->sched[l];
-    LAUNCH(e, K_BACKSOLVE, backsolve_kernel<<<L.n_all, L.bs_threads, L.bs_smem, e->stream>>>(E, e->d_level_cliques.p + e->plan.level_off[l],
-                                                                      e->d_delta.p));
+    const int32_t* bl = e->d_bs_list.p + L.bs_begin;
+    if (L.n_bs_warp)
+      LAUNCH(e, K_BACKSOLVE, backsolve_kernel<true><<<(L.n_bs_warp + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
+                                                      kBsWarps * kBsWarpDoubles * sizeof(double), e->stream>>>(
+                                 E, bl, L.n_bs_warp, e->d_delta.p));
+    if (L.n_bs_cta)
+      LAUNCH(e, K_BACKSOLVE, backsolve_kernel<false><<<L.n_bs_cta, 512, L.bs_cta_smem, e->stream>>>(
+                                 E, bl + L.n_bs_warp, L.n_bs_cta, e->d_delta.p));
   }
   tm.stop();
   e->solved = true;
@@ -1298,6 +1333,23 @@ gtb_status gtb_profile_read(gtb_engine* e, double* total_ms, int64_t* launches) 
   e->prof_used = 0;
   e->prof_class.clear();
   GTB_CATCH(e)
+}
+int64_t gtb_profile_read_raw(gtb_engine* e, int32_t* klass, float* ms, int64_t cap) {
+  if (!e || !e->has_device) return -1;
+  cudaStreamSynchronize(e->stream);
+  const int64_t n = std::min<int64_t>((int64_t)e->prof_class.size(), cap);
+  for (int64_t i = 0; i < n; ++i) {
+    klass[i] = e->prof_class[i];
+    cudaEventElapsedTime(&ms[i], e->prof_events[2 * i], e->prof_events[2 * i + 1]);
+  }
+  e->prof_used = 0;
+  e->prof_class.clear();
+  return n;
+}
+void gtb_debug_read(gtb_engine* e, long long* out8) {
+  if (!e || !e->has_device) return;
+  cudaStreamSynchronize(e->stream);
+  cudaMemcpy(out8, e->d_dbg.p, 8 * sizeof(long long), cudaMemcpyDeviceToHost);
 }
 void* gtb_stream(gtb_engine* e) { return e ? (void*)e->stream : nullptr; }
 

@@ -226,5 +226,13 @@ class Engine:
         self._ck(self.lib.gtb_profile_read(self.h, _ptr(ms), _ptr(cnt)))
         return {self.lib.gtb_profile_class_name(k).decode(): (float(ms[k]), int(cnt[k])) for k in range(n) if cnt[k]}
 
+    def profile_read_raw(self, cap=1 << 20):
+        """(class names per launch, ms per launch) in launch order since the last read."""
+        k = np.zeros(cap, dtype=np.int32)
+        ms = np.zeros(cap, dtype=np.float32)
+        n = self.lib.gtb_profile_read_raw(self.h, _ptr(k), _ptr(ms), cap)
+        names = [self.lib.gtb_profile_class_name(i).decode() for i in range(self.lib.gtb_profile_classes())]
+        return [names[i] for i in k[:n]], ms[:n].copy()
+
     def stream(self):
         return self.lib.gtb_stream(self.h)

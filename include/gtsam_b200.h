@@ -188,6 +188,8 @@ gtb_status gtb_profile(gtb_engine* e, int on);
 int gtb_profile_classes(void);
 const char* gtb_profile_class_name(int k);
 gtb_status gtb_profile_read(gtb_engine* e, double* total_ms, int64_t* launches);
+/* Every recorded launch in order: class id and elapsed ms; returns the number written (<= cap) and clears.  */
+int64_t gtb_profile_read_raw(gtb_engine* e, int32_t* klass, float* ms, int64_t cap);
 /* Raw stream handle (cudaStream_t) for callers that time with their own events.                          */
 void* gtb_stream(gtb_engine* e);
 

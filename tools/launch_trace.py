@@ -1,0 +1,37 @@
+"""Per-launch device times of one LM step (CUDA events around every launch), grouped for reading: which kernel
+class at which position of the level schedule costs what."""
+import sys, os, json
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench
+from gtsam_petercdev_b200.engine import Engine
+wl = sys.argv[1] if len(sys.argv) > 1 else "c3"
+ordn = sys.argv[2] if len(sys.argv) > 2 else "metis"
+p = bench.make_problem(wl)
+e = Engine(p, device=0)
+e.set_ordering(bench.ordering_for(p, wl, ordn))
+e.set_stage_timing(False)
+def step():
+    e.linearize(); e.factorize(1e-5); e.backsolve(); e.linear_errors(); e.retract(); return e.error(1)
+for _ in range(3): step()
+e.profile(True); step()
+names, ms = e.profile_read_raw()
+e.profile(False)
+# compress consecutive launches of the same class
+out, i = [], 0
+while i < len(names):
+    j = i
+    while j < len(names) and names[j] == names[i]: j += 1
+    seg = ms[i:j]
+    out.append((names[i], j - i, float(seg.sum()), float(seg.max())))
+    i = j
+for r in out: print("%-16s n=%4d total=%8.3f ms  max=%7.3f ms" % r)
+fs = ms[[k for k, n in enumerate(names) if n == "front_step"]]
+print("front_step launches", len(fs), "sum", fs.sum(), "sorted top", np.sort(fs)[::-1][:20])
+
+import ctypes
+if os.environ.get("GTB_DEBUG") and int(os.environ["GTB_DEBUG"]) & 8:
+    buf = (ctypes.c_longlong * 8)()
+    e.lib.gtb_debug_read.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    e.lib.gtb_debug_read(e.h, buf)
+    print("role A cycles (root, p=1, slice 0): load D/P %d, PtP %d, potrf %d, dfac+update %d, trsm+store %d" % tuple(buf[:5]))
