@@ -83,7 +83,7 @@ def test_solve_matches_reference(name, ordering, lam, diag, tag):
         if key in g:
             ours = e.variables(t, which=1)
             order = np.argsort(p.a[vt + "_keys"], kind="stable")  # golden dump is in key order
-            assert np.allclose(ours[order], g[key], rtol=0, atol=1e-9 * max(1.0, np.abs(g[key]).max())), vt
+            assert np.allclose(ours[order], g[key], rtol=0, atol=max(1e-9, 10 * sens) * max(1.0, np.abs(g[key]).max())), vt
 
 
 @pytest.mark.parametrize("name,mode,ordering,extra,tag", run_tags())
