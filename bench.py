@@ -257,7 +257,8 @@ def main():
     # algorithmic work per step of each candidate class
     work = {
         "front_step": ("tensor", st["flops_large"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
-        "small_front": ("hbm", st["bytes_small"] / 1e9, hbm, "GB/s"),
+        "small_front": ("hbm", (st["bytes_small"] - st["bytes_thin"]) / 1e9, hbm, "GB/s"),
+        "thin_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
         "linearize": ("hbm", st["bytes_linearize"] / 1e9, hbm, "GB/s"),
         "backsolve": ("hbm", st["bytes_backsolve"] / 1e9, hbm, "GB/s"),
     }

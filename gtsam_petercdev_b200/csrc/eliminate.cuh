@@ -151,6 +151,180 @@ __global__ void small_front_kernel(ElimDev E, const int32_t* __restrict__ list) 
 }
 
 // ----------------------------------------------------------------------------------------------------
+// thin fronts (F <= 12: a point, a pose, a camera): packed upper triangle in shared memory, column loops (no integer
+// division), reciprocal pivots.  WARP = true: one warp per clique, kThinWarps cliques per CTA; else one CTA per clique.
+// ----------------------------------------------------------------------------------------------------
+constexpr int kThinWarps = 8;
+__constant__ unsigned char c_pairA[91] = {
+    0, 0, 1, 0, 1, 2, 0, 1, 2, 3, 0, 1, 2, 3, 4, 0, 1, 2, 3, 4, 5, 0, 1, 2, 3, 4, 5, 6, 0, 1, 2, 3, 4, 5, 6, 7,
+    0, 1, 2, 3, 4, 5, 6, 7, 8, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10,
+    0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12};
+__constant__ unsigned char c_pairB[91] = {
+    0, 1, 1, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 4, 5, 5, 5, 5, 5, 5, 6, 6, 6, 6, 6, 6, 6, 7, 7, 7, 7, 7, 7, 7, 7,
+    8, 8, 8, 8, 8, 8, 8, 8, 8, 9, 9, 9, 9, 9, 9, 9, 9, 9, 9, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10,
+    11, 11, 11, 11, 11, 11, 11, 11, 11, 11, 11, 11, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12};
+
+__device__ __forceinline__ int tri(int i, int j) { return ((j * (j + 1)) >> 1) + i; }   // i <= j
+
+constexpr int kThinStage = 416;   // doubles of factor rows staged per group and pass (16 SFM factors)
+
+// packed index -> column j (largest j with j(j+1)/2 <= idx)
+__device__ __forceinline__ int tri_col(int idx) {
+  int j = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
+  while (((j + 1) * (j + 2)) >> 1 <= idx) ++j;
+  while ((j * (j + 1)) >> 1 > idx) --j;
+  return j;
+}
+
+template <bool WARP>
+__global__ void __launch_bounds__(WARP ? kThinWarps * 32 : 128)
+thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int group_doubles) {
+  extern __shared__ double sh[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = WARP ? blockIdx.x * kThinWarps + warp : blockIdx.x;
+  if (slot >= count) return;
+  const int gsize = WARP ? 32 : (int)blockDim.x;
+  const int gtid = WARP ? lane : (int)threadIdx.x;
+  auto gsync = [&]() { if (WARP) __syncwarp(); else __syncthreads(); };
+  double* P = sh + (WARP ? warp * (group_doubles + kThinStage) : 0);
+  double* stage = P + group_doubles;
+  const int c = list[slot];
+  const CliqueDev ci = E.cliques[c];
+  const int F = ci.F, N = F + ci.S, dim = N + 1;
+  const int plen = (dim * (dim + 1)) >> 1;
+  for (int i = gtid; i < plen; i += gsize) P[i] = 0.0;
+  // own factors, gather order.  The whitened rows of a batch of factors are staged into shared memory with one
+  // round of global loads, then accumulated factor by factor (fixed order: deterministic sums).
+  for (int s0 = ci.fac_begin; s0 < ci.fac_end;) {
+    int s1 = s0, used = 0;
+    while (s1 < ci.fac_end) {
+      const int b = E.slots[s1].bucket;
+      const int sz = c_M[b] * c_W[b];
+      if (used + sz > kThinStage) break;
+      used += sz;
+      ++s1;
+    }
+    gsync();   // previous batch fully consumed (and the zero fill done)
+    {
+      int off = 0;
+      for (int s = s0; s < s1; ++s) {
+        const SlotDev sl = E.slots[s];
+        const int sz = c_M[sl.bucket] * c_W[sl.bucket];
+        const double* ab = E.Ab[sl.bucket] + (int64_t)sl.index * sz;
+        for (int i = gtid; i < sz; i += gsize) stage[off + i] = ab[i];
+        off += sz;
+      }
+    }
+    gsync();
+    int off = 0;
+    for (int s = s0; s < s1; ++s) {
+      const SlotDev sl = E.slots[s];
+      const int M = c_M[sl.bucket], W = c_W[sl.bucket], n0 = c_N0[sl.bucket];
+      const double* ab = stage + off;
+      const int npairs = (W * (W + 1)) >> 1;
+      for (int pidx = gtid; pidx < npairs; pidx += gsize) {
+        const int a = c_pairA[pidx], b = c_pairB[pidx];
+        double acc = 0.0;
+        for (int r = 0; r < M; ++r) acc += ab[r * W + a] * ab[r * W + b];
+        int i = (a < n0) ? sl.col0 + a : (a < W - 1 ? sl.col1 + (a - n0) : N);
+        int j = (b < n0) ? sl.col0 + b : (b < W - 1 ? sl.col1 + (b - n0) : N);
+        if (i > j) { const int t = i; i = j; j = t; }
+        P[tri(i, j)] += acc;
+      }
+      off += M * W;
+      gsync();
+    }
+    s0 = s1;
+  }
+  gsync();
+  if (E.damp) {
+    const int32_t* g = E.gidx + ci.gidx_off;
+    for (int f = gtid; f < F; f += gsize) P[tri(f, f)] += E.damp[g[f]];
+    gsync();
+  }
+  // children's Schur complements, child order; one child column per pass, rows spread over the lanes
+  for (int q = ci.child_begin; q < ci.child_end; ++q) {
+    const CliqueDev cc = E.cliques[E.children[q]];
+    const int S1 = cc.S + 1;
+    const double* src = E.arena + cc.front_off + cc.F + (int64_t)cc.F * cc.ld;
+    const int32_t* pm = E.pmap + cc.pmap_off;
+    for (int j = WARP ? 0 : warp; j < S1; j += WARP ? 1 : (gsize >> 5)) {
+      const int pj = pm[j];
+      for (int i = lane; i <= j; i += 32) {
+        int a = pm[i], b = pj;
+        if (a > b) { const int t = a; a = b; b = t; }
+        P[tri(a, b)] += src[i + (int64_t)j * cc.ld];
+      }
+    }
+    gsync();
+  }
+  // (1) A_FF = R^T R on the small frontal block (base/cholesky.cpp:125)
+  bool ok = true;
+  for (int k = 0; k < F; ++k) {
+    const double piv = P[tri(k, k)];
+    if (!(piv > 0.0)) { ok = false; break; }   // Eigen LLT NumericalIssue
+    const double rinv = rsqrt(piv);
+    gsync();
+    for (int j = k + 1 + gtid; j < F; j += gsize) P[tri(k, j)] *= rinv;
+    if (gtid == 0) P[tri(k, k)] = piv * rinv;
+    gsync();
+    const int cnt = F - k - 1;
+    for (int idx = gtid; idx < cnt * cnt; idx += gsize) {
+      const int jj = idx / cnt, ii = idx - jj * cnt;
+      if (ii <= jj) P[tri(k + 1 + ii, k + 1 + jj)] -= P[tri(k, k + 1 + ii)] * P[tri(k, k + 1 + jj)];
+    }
+    gsync();
+  }
+  if (ok) {
+    if (F >= 2) ok = frexp_exp(P[tri(F - 2, F - 2)]) - frexp_exp(P[tri(F - 1, F - 1)]) < 12;
+    else if (F == 1) ok = frexp_exp(P[0]) > -12;
+  }
+  if (!ok) {
+    if (gtid == 0) atomicMin(E.fail, c);
+    return;
+  }
+  // (2) S = R^-T [A_FS | b]: one separator column per thread, forward substitution in place (:136)
+  double* rdiag = stage;   // the staging area is free by now
+  if (gtid < F) rdiag[gtid] = 1.0 / P[tri(gtid, gtid)];
+  gsync();
+  for (int j = F + gtid; j < dim; j += gsize) {
+    const int base = (j * (j + 1)) >> 1;
+    for (int r = 0; r < F; ++r) {
+      double x = P[base + r];
+      for (int l = 0; l < r; ++l) x -= P[tri(l, r)] * P[base + l];
+      P[base + r] = x * rdiag[r];
+    }
+  }
+  gsync();
+  // (3) C -= S^T S on the packed upper triangle, every element independent (:142); (i, j) advance incrementally
+  {
+    int idx = ((F * (F + 1)) >> 1) + gtid;
+    int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
+    for (; idx < plen; idx += gsize) {
+      if (i >= F) {
+        const int bi = (i * (i + 1)) >> 1, bj = (j * (j + 1)) >> 1;
+        double acc = 0.0;
+        for (int r = 0; r < F; ++r) acc += P[bi + r] * P[bj + r];
+        P[idx] -= acc;
+      }
+      i += gsize;
+      while (i > j) { i -= j + 1; ++j; }
+    }
+  }
+  gsync();
+  double* dst = E.arena + ci.front_off;
+  {
+    int idx = gtid;
+    int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
+    for (; idx < plen; idx += gsize) {
+      dst[i + (int64_t)j * ci.ld] = P[idx];
+      i += gsize;
+      while (i > j) { i -= j + 1; ++j; }
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
 // large fronts: front in global memory (L2-resident), several CTAs per front
 // ----------------------------------------------------------------------------------------------------
 // zeroing of very large fronts is spread over many CTAs
@@ -588,9 +762,47 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
 constexpr int kBsWarps = 8;
 constexpr int kBsWarpDoubles = 32 + 160 + 32;   // rhs, xs, reduction scratch per warp
 
+// S x_S for CTA-class cliques, spread over many CTAs: blockIdx.x = clique slot, y = 128-row block, z = 128-column
+// chunk.  Partial sums go to scratch[off + chunk * F + i]; backsolve_kernel<false> adds them in chunk order
+// (deterministic, no atomics).
+constexpr int kGemvRows = 128, kGemvCols = 128;
+__global__ void __launch_bounds__(kGemvRows)
+backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t* __restrict__ scratch_off,
+                      const double* __restrict__ delta, double* __restrict__ scratch) {
+  const CliqueDev ci = E.cliques[list[blockIdx.x]];
+  const int F = ci.F, S = ci.S, ld = ci.ld;
+  const int i0 = blockIdx.y * kGemvRows, j0 = blockIdx.z * kGemvCols;
+  if (i0 >= F || j0 >= S) return;
+  __shared__ double xs[kGemvCols];
+  const int nj = min(kGemvCols, S - j0);
+  const int32_t* g = E.gidx + ci.gidx_off + F + j0;
+  for (int j = threadIdx.x; j < nj; j += kGemvRows) xs[j] = delta[g[j]];
+  __syncthreads();
+  const int i = i0 + threadIdx.x;
+  if (i >= F) return;
+  const double* row = E.arena + ci.front_off + i + (int64_t)(F + j0) * ld;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  int j = 0;
+  for (; j + 16 <= nj; j += 16) {   // 16 independent loads in flight per thread
+    double v[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) v[u] = row[(int64_t)(j + u) * ld];
+#pragma unroll
+    for (int u = 0; u < 16; u += 4) {
+      a0 += v[u] * xs[j + u];
+      a1 += v[u + 1] * xs[j + u + 1];
+      a2 += v[u + 2] * xs[j + u + 2];
+      a3 += v[u + 3] * xs[j + u + 3];
+    }
+  }
+  for (; j < nj; ++j) a0 += row[(int64_t)j * ld] * xs[j];
+  scratch[scratch_off[blockIdx.x] + (int64_t)blockIdx.z * F + i] = (a0 + a1) + (a2 + a3);
+}
+
 template <bool WARP>
 __global__ void __launch_bounds__(WARP ? kBsWarps * 32 : 512)
-backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta) {
+backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta,
+                 const int32_t* __restrict__ scratch_off, const double* __restrict__ scratch) {
   extern __shared__ double sh[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = WARP ? blockIdx.x * kBsWarps + warp : blockIdx.x;
@@ -607,24 +819,18 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
   double* xblk = WARP ? rhs : red + gsize;                  // 32 (CTA only; WARP has a single block)
   auto gsync = [&]() { if (WARP) __syncwarp(); else __syncthreads(); };
 
-  for (int j = gtid; j < S; j += gsize) xs[j] = delta[g[F + j]];
-  gsync();
-  // rhs = d - S x_S
-  if (F >= gsize) {
+  if (!WARP) {
+    // rhs = d - (S x_S): partial products were computed by backsolve_gemv_kernel, summed here in chunk order
+    const int nchunk = (S + kGemvCols - 1) / kGemvCols;
+    const double* part = scratch + scratch_off[slot];
     for (int i = gtid; i < F; i += gsize) {
-      double a0 = A[i + (int64_t)N * ld], a1 = 0.0, a2 = 0.0, a3 = 0.0;
-      const double* row = A + i + (int64_t)F * ld;
-      int j = 0;
-      for (; j + 4 <= S; j += 4) {
-        a0 -= row[(int64_t)j * ld] * xs[j];
-        a1 -= row[(int64_t)(j + 1) * ld] * xs[j + 1];
-        a2 -= row[(int64_t)(j + 2) * ld] * xs[j + 2];
-        a3 -= row[(int64_t)(j + 3) * ld] * xs[j + 3];
-      }
-      for (; j < S; ++j) a0 -= row[(int64_t)j * ld] * xs[j];
-      rhs[i] = (a0 + a1) + (a2 + a3);
+      double a = A[i + (int64_t)N * ld];
+      for (int q = 0; q < nchunk; ++q) a -= part[(int64_t)q * F + i];
+      rhs[i] = a;
     }
   } else {
+    for (int j = gtid; j < S; j += gsize) xs[j] = delta[g[F + j]];
+    gsync();
     int Fp = 1;
     while (Fp < F) Fp <<= 1;
     const int G = gsize / Fp;
@@ -652,11 +858,16 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
       for (int k = 0; k < 32; ++k)
         r[k] = (k < kb && lane <= k && lane < kb) ? A[(b0 + lane) + (int64_t)(b0 + k) * ld] : 1.0;
       double my = (lane < kb) ? rhs[b0 + lane] : 0.0;
+      // reciprocal of this lane's diagonal entry: one division per lane instead of a chain of 32
+      double dg = 1.0;
+#pragma unroll
+      for (int k = 0; k < 32; ++k)
+        if (k == lane) dg = r[k];
+      const double rd = 1.0 / dg;
 #pragma unroll
       for (int k = 31; k >= 0; --k) {
         if (k < kb) {
-          const double dk = __shfl_sync(0xffffffffu, r[k], k);
-          const double xk = __shfl_sync(0xffffffffu, my, k) / dk;
+          const double xk = __shfl_sync(0xffffffffu, my, k) * __shfl_sync(0xffffffffu, rd, k);
           if (lane == k) my = xk;
           else if (lane < k) my -= r[k] * xk;
         }

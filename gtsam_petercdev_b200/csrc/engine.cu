@@ -33,7 +33,6 @@ static const int kVT[7][2] = {{0, 0}, {1, 1}, {2, 3}, {0, -1}, {1, -1}, {2, -1},
 static const int kStateIn[4] = {3, 12, 17, 3};
 static const int kStateDev[4] = {4, 12, 17, 3};
 static const int kDim[4] = {3, 6, 9, 3};
-static const int kSmallMax = 128;   // fronts with F+S+1 <= kSmallMax are eliminated in shared memory
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
 #define CK(call)                                                                                   \
@@ -70,7 +69,7 @@ template <class T> struct DevBuf {
 
 struct LevelSched {
   // small fronts split into thread classes; each class is a contiguous range of the level list
-  struct Cls { int64_t begin; int32_t count; int32_t threads; int32_t smem; };
+  struct Cls { int64_t begin; int32_t count; int32_t threads; int32_t smem; int32_t kind; int32_t group_doubles; };
   std::vector<Cls> small;
   int64_t large_begin = 0;
   int32_t n_large = 0;
@@ -80,6 +79,7 @@ struct LevelSched {
   int32_t n_all = 0;          // all cliques at the level (back-substitution)
   int64_t bs_begin = 0;       // into the back-substitution list: warp-class cliques first, then CTA-class
   int32_t n_bs_warp = 0, n_bs_cta = 0, bs_cta_smem = 0;
+  int32_t bs_max_F = 0, bs_max_S = 0;   // CTA class: grid of the partial-GEMV kernel
   int64_t zero_blocks = 0;
   std::vector<int64_t> step_begin;  // per panel step 0..max_np: range of the compact task list
   std::vector<int32_t> step_count;
@@ -123,7 +123,8 @@ struct gtb_engine {
   bool has_plan = false;
   std::vector<LevelSched> sched;
   std::vector<ChildWork> child_work;
-  std::vector<int32_t> bs_list;
+  std::vector<int32_t> bs_list, bs_scratch_off;
+  int64_t bs_scratch_doubles = 0;
   std::vector<StepTask> step_tasks_list;
 
   // ---- device ----
@@ -142,7 +143,8 @@ struct gtb_engine {
   DevBuf<int32_t> d_inc_bucket, d_inc_index, d_inc_slot, d_var_goff, d_var_dim;
   DevBuf<CliqueDev> d_cliques;
   DevBuf<SlotDev> d_slots;
-  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list;
+  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list, d_bs_scratch_off;
+  DevBuf<double> d_bs_scratch;
   DevBuf<ChildWork> d_child_work;
   DevBuf<StepTask> d_step_tasks;
   DevBuf<long long> d_dbg;
@@ -287,11 +289,11 @@ struct StageTimer {
 };
 
 // kernel classes for launch counting and optional per-launch event timing
-enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_ZERO, K_LFACT, K_LCHILD, K_STEP,
-       K_BACKSOLVE, K_RETRACT, K_NUM };
+enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_ZERO, K_LFACT, K_LCHILD, K_STEP,
+       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
-                                          "small_front", "large_zero", "large_factors", "large_children", "front_step",
-                                          "backsolve", "retract"};
+                                          "small_front", "thin_front", "large_zero", "large_factors", "large_children", "front_step",
+                                          "backsolve", "backsolve_gemv", "retract"};
 
 static void prof_begin(Engine* e, int k) {
   if (!e->profiling) return;
@@ -538,6 +540,8 @@ static void install_plan(Engine* e) {
   e->sched.assign(p.n_levels, LevelSched());
   e->child_work.clear();
   e->bs_list.clear();
+  e->bs_scratch_off.clear();
+  e->bs_scratch_doubles = 0;
   e->step_tasks_list.clear();
   for (int32_t l = 0; l < p.n_levels; ++l) {
     LevelSched& L = e->sched[l];
@@ -600,12 +604,29 @@ static void install_plan(Engine* e) {
     for (int pass = 0; pass < 2; ++pass)
       for (int64_t q = b; q < en; ++q) {
         const int32_t c = p.level_cliques[q];
-        const bool warp_class = p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kSmallMax;
+        const bool warp_class = p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kDenseMaxDim;
         if (warp_class != (pass == 0)) continue;
         e->bs_list.push_back(c);
         if (warp_class) L.n_bs_warp++;
-        else { L.n_bs_cta++; maxN = std::max(maxN, p.F[c] + p.S[c]); }
+        else {
+          L.n_bs_cta++;
+          maxN = std::max(maxN, p.F[c] + p.S[c]);
+          L.bs_max_F = std::max(L.bs_max_F, p.F[c]);
+          L.bs_max_S = std::max(L.bs_max_S, p.S[c]);
+        }
       }
+    // scratch offsets of the CTA-class cliques (same order as the list)
+    {
+      int64_t off = 0;
+      e->bs_scratch_off.resize(e->bs_list.size(), 0);
+      for (int64_t q = L.bs_begin + L.n_bs_warp; q < (int64_t)e->bs_list.size(); ++q) {
+        const int32_t c = e->bs_list[q];
+        e->bs_scratch_off[q] = (int32_t)off;
+        off += (int64_t)p.F[c] * ((p.S[c] + kGemvCols - 1) / kGemvCols);
+      }
+      need(off < INT32_MAX, "back-substitution scratch overflow");
+      e->bs_scratch_doubles = std::max(e->bs_scratch_doubles, off);
+    }
     L.bs_cta_smem = (maxN + 512 + 32) * (int32_t)sizeof(double);
   }
   // re-sort the small part of every level by dimension and cut into thread classes
@@ -614,15 +635,40 @@ static void install_plan(Engine* e) {
     LevelSched& L = e->sched[l];
     const int64_t b = p.level_off[l], ns = p.level_n_small[l];
     auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
-    std::stable_sort(lc.begin() + b, lc.begin() + b + ns, [&](int32_t a, int32_t c2) { return dim_of(a) < dim_of(c2); });
-    const int32_t bounds[4] = {32, 64, 96, kSmallMax};
-    const int32_t threads[4] = {32, 64, 128, 256};
+    // thin fronts first (sorted by dimension), then dense ones (sorted by dimension)
+    auto thin = [&](int32_t c) { return is_thin_front(p.F[c], dim_of(c)); };
+    std::stable_sort(lc.begin() + b, lc.begin() + b + ns, [&](int32_t a, int32_t c2) {
+      const int ka = thin(a) ? 0 : 1, kc = thin(c2) ? 0 : 1;
+      return ka != kc ? ka < kc : dim_of(a) < dim_of(c2);
+    });
     int64_t q = b;
+    // thin classes are cut adaptively so that the shared memory of a class (sized by its largest member) stays within
+    // ~20 % of what its smallest member needs: occupancy is limited by shared memory
+    while (q < b + ns && thin(lc[q])) {
+      const int64_t q0 = q;
+      const int d0 = dim_of(lc[q]);
+      const bool warp_kind = d0 <= 48;
+      const int hi = warp_kind ? (d0 <= 32 ? 32 : (d0 <= 40 ? 40 : 48)) : std::max(d0 + 8, d0 * 6 / 5);
+      int32_t md = 0;
+      while (q < b + ns && thin(lc[q]) && dim_of(lc[q]) <= hi) { md = std::max(md, dim_of(lc[q])); ++q; }
+      LevelSched::Cls cl;
+      cl.begin = q0; cl.count = (int32_t)(q - q0); cl.kind = warp_kind ? 0 : 1;
+      cl.threads = warp_kind ? kThinWarps * 32 : 128;
+      cl.group_doubles = ((md * (md + 1) / 2) + 1) & ~1;
+      cl.smem = (cl.group_doubles + kThinStage) * (int32_t)sizeof(double) * (warp_kind ? kThinWarps : 1);
+      L.small.push_back(cl);
+    }
+    const int32_t bounds[4] = {32, 64, 96, kDenseMaxDim};
+    const int32_t threads[4] = {32, 64, 128, 256};
     for (int k = 0; k < 4; ++k) {
-      int64_t q0 = q;
+      const int64_t q0 = q;
       int32_t md = 0;
       while (q < b + ns && dim_of(lc[q]) <= bounds[k]) { md = std::max(md, dim_of(lc[q])); ++q; }
-      if (q > q0) L.small.push_back({q0, (int32_t)(q - q0), threads[k], (md | 1) * md * (int32_t)sizeof(double)});
+      if (q == q0) continue;
+      LevelSched::Cls cl;
+      cl.begin = q0; cl.count = (int32_t)(q - q0); cl.threads = threads[k]; cl.kind = 2; cl.group_doubles = 0;
+      cl.smem = (md | 1) * md * (int32_t)sizeof(double);
+      L.small.push_back(cl);
     }
   }
   e->plan.level_cliques = lc;
@@ -641,7 +687,7 @@ static void install_plan(Engine* e) {
     d.pmap_off = (int32_t)p.pmap_off[c]; d.gidx_off = (int32_t)p.gidx_off[c];
     d.first_key_var = p.vars[p.vars_off[c]];
     d.dfac_off = 0;
-    if (p.F[c] + p.S[c] + 1 > kSmallMax) {
+    if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
       dfac_total += (int64_t)((p.F[c] + NB - 1) / NB) * NB * NB;
       need(dfac_total < INT32_MAX, "diagonal-block side buffer overflow");
@@ -660,6 +706,8 @@ static void install_plan(Engine* e) {
   e->d_level_cliques.upload(e->plan.level_cliques, st);
   e->d_child_work.upload(e->child_work, st);
   e->d_bs_list.upload(e->bs_list, st);
+  e->d_bs_scratch_off.upload(e->bs_scratch_off, st);
+  e->d_bs_scratch.alloc((size_t)e->bs_scratch_doubles + 1);
   e->d_step_tasks.upload(e->step_tasks_list, st);
   e->d_dbg.alloc(8);
   e->d_fail.alloc(1);
@@ -673,7 +721,7 @@ static void set_ordering_ids(Engine* e, const std::vector<int32_t>& order) {
   need(e->finalized, "gtb_finalize_problem must be called first");
   e->sym.order = order;
   try {
-    build_plan(e->sym, kSmallMax, &e->plan);
+    build_plan(e->sym, kDenseMaxDim, &e->plan);
   } catch (const std::runtime_error& ex) {
     throw StatusError(GTB_ERR_INCONSISTENT, ex.what());
   }
@@ -810,6 +858,8 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   static bool attr = false;
   if (!attr) {
     CK(cudaFuncSetAttribute(small_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(thin_front_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(thin_front_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(front_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem));
     CK(cudaFuncSetAttribute(backsolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr = true;
@@ -818,7 +868,14 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   for (int32_t l = 0; l < e->plan.n_levels; ++l) {
     const LevelSched& L = e->sched[l];
     for (const auto& c : L.small) {
-      LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
+      if (c.kind == 0)
+        LAUNCH(e, K_THIN, thin_front_kernel<true><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
+                              E, lists + c.begin, c.count, c.group_doubles));
+      else if (c.kind == 1)
+        LAUNCH(e, K_THIN, thin_front_kernel<false><<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin, c.count,
+                                                                                       c.group_doubles));
+      else
+        LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
     }
     if (!L.n_large) continue;
     const int32_t* ll = lists + L.large_begin;
@@ -849,13 +906,20 @@ static void backsolve(Engine* e) {
   for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
     const LevelSched& L = e->sched[l];
     const int32_t* bl = e->d_bs_list.p + L.bs_begin;
+    const int32_t* so = e->d_bs_scratch_off.p + L.bs_begin;
     if (L.n_bs_warp)
       LAUNCH(e, K_BACKSOLVE, backsolve_kernel<true><<<(L.n_bs_warp + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
                                                       kBsWarps * kBsWarpDoubles * sizeof(double), e->stream>>>(
-                                 E, bl, L.n_bs_warp, e->d_delta.p));
-    if (L.n_bs_cta)
+                                 E, bl, L.n_bs_warp, e->d_delta.p, so, e->d_bs_scratch.p));
+    if (L.n_bs_cta) {
+      if (L.bs_max_S > 0)
+        LAUNCH(e, K_BSGEMV, backsolve_gemv_kernel<<<dim3(L.n_bs_cta, (L.bs_max_F + kGemvRows - 1) / kGemvRows,
+                                                         (L.bs_max_S + kGemvCols - 1) / kGemvCols),
+                                                    kGemvRows, 0, e->stream>>>(E, bl + L.n_bs_warp, so + L.n_bs_warp,
+                                                                               e->d_delta.p, e->d_bs_scratch.p));
       LAUNCH(e, K_BACKSOLVE, backsolve_kernel<false><<<L.n_bs_cta, 512, L.bs_cta_smem, e->stream>>>(
-                                 E, bl + L.n_bs_warp, L.n_bs_cta, e->d_delta.p));
+                                 E, bl + L.n_bs_warp, L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, e->d_bs_scratch.p));
+    }
   }
   tm.stop();
   e->solved = true;
@@ -1079,15 +1143,29 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
   const Plan& p = e->plan;
   out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)p.arena_doubles;
   out[4] = (double)p.n_small; out[5] = (double)p.n_large; out[6] = p.flops_large; out[7] = p.assembly_bytes;
+  double thin_bytes = 0;
   out[8] = p.flops_syrk_frontal; out[9] = p.flops_syrk_schur; out[10] = p.bytes_backsolve;
   {
     // small fronts also read the whitened rows of their own factors
     static const int kMW[7] = {21, 78, 26, 12, 42, 90, 12};
     double b = p.bytes_small;
     for (int32_t c = 0; c < p.n_cliques; ++c)
-      if (p.F[c] + p.S[c] + 1 <= kSmallMax)
+      if (is_small_front(p.F[c], p.F[c] + p.S[c] + 1))
         for (int64_t q = p.fac_off[c]; q < p.fac_off[c + 1]; ++q) b += 8.0 * kMW[e->g_bucket[p.slots[q].factor]];
     out[11] = b;
+    // share of it in thin fronts (thin_front_kernel): own front written, own factor rows and child Schur blocks read
+    double bt = 0;
+    for (int32_t c = 0; c < p.n_cliques; ++c) {
+      const int dim = p.F[c] + p.S[c] + 1;
+      if (!is_thin_front(p.F[c], dim)) continue;
+      bt += 8.0 * 0.5 * dim * (dim + 1);
+      for (int64_t q = p.fac_off[c]; q < p.fac_off[c + 1]; ++q) bt += 8.0 * kMW[e->g_bucket[p.slots[q].factor]];
+      for (int64_t q = p.child_off[c]; q < p.child_off[c + 1]; ++q) {
+        const double s1 = p.S[p.children[q]] + 1;
+        bt += 8.0 * 0.5 * s1 * (s1 + 1);
+      }
+    }
+    thin_bytes = bt;
   }
   // linearize: variables read once + per-factor indices, measurement, noise + whitened [A|b] written once
   {
@@ -1098,7 +1176,7 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
                                   8.0 * kM[k] * kW[k]);
     out[12] = b;
   }
-  out[13] = out[14] = out[15] = 0;
+  out[13] = thin_bytes; out[14] = out[15] = 0;
   return GTB_OK;
 }
 

@@ -64,6 +64,14 @@ struct Plan {
   int64_t n_small = 0, n_large = 0;
 };
 
+// Front classes.  "Small" fronts are assembled and eliminated entirely in shared memory by one warp or CTA:
+//   thin  : few frontal scalars (a point or a pose), packed upper triangle in shared memory
+//   dense : any F, full square in shared memory
+// everything else is a "large" front that lives in global memory and is factored by the blocked panel kernels.
+constexpr int32_t kThinMaxF = 12, kThinMaxDim = 208, kDenseMaxDim = 128;
+inline bool is_thin_front(int32_t F, int32_t dim) { return F <= kThinMaxF && dim <= kThinMaxDim; }
+inline bool is_small_front(int32_t F, int32_t dim) { return dim <= kDenseMaxDim || is_thin_front(F, dim); }
+
 // Throws std::runtime_error with a message on inconsistent input.
 // small_max: fronts with F+S+1 <= small_max are handled by the shared-memory kernel.
 void build_plan(const SymbolicInput& in, int32_t small_max, Plan* out);

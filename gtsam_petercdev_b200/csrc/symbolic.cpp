@@ -210,7 +210,7 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P) {
     p.F[c] = F;
     p.S[c] = S;
     const int32_t dim = F + S + 1;
-    const bool small = dim <= small_max;
+    const bool small = is_small_front(F, dim);
     p.ld[c] = small ? dim : ((dim + 3) & ~3);
     arena = small ? ((arena + 1) & ~(int64_t)1) : ((arena + 15) & ~(int64_t)15);
     p.front_off[c] = arena;
@@ -248,7 +248,7 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P) {
   }
   for (int32_t c = 0; c < C; ++c) {
     const int32_t par = p.parent[c];
-    if (par >= 0 && p.F[par] + p.S[par] + 1 <= small_max) {
+    if (par >= 0 && is_small_front(p.F[par], p.F[par] + p.S[par] + 1)) {
       const double s1 = p.S[c] + 1;
       p.bytes_small += 8.0 * 0.5 * s1 * (s1 + 1);
     }
@@ -316,7 +316,7 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P) {
     std::vector<int64_t> fill(p.level_off.begin(), p.level_off.end() - 1);
     for (int pass = 0; pass < 2; ++pass)
       for (int32_t c = 0; c < C; ++c) {
-        const bool small = p.F[c] + p.S[c] + 1 <= small_max;
+        const bool small = is_small_front(p.F[c], p.F[c] + p.S[c] + 1);
         if (small == (pass == 0)) {
           p.level_cliques[fill[p.level[c]]++] = c;
           if (small) p.level_n_small[p.level[c]]++;
