@@ -66,7 +66,13 @@ _SIGS = {
     "gtb_profile_read": (C.c_int, [_P, _P, _P]),
     "gtb_profile_read_raw": (C.c_int64, [_P, _P, _P, C.c_int64]),
     "gtb_stream": (_P, [_P]),
+    "gtb_set_distributed": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P]),
+    "gtb_partition_get": (C.c_int, [_P, _P, _P]),
 }
+
+# int (*gtb_comm_fn)(void* user, int op, void* buf, int64_t count, void* stream)
+COMM_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p)
+COMM_REDUCE_SUM_TO_0, COMM_BROADCAST_FROM_0, COMM_ALLREDUCE_SUM, COMM_ALLREDUCE_MIN = 0, 1, 2, 3
 
 _lib = None
 

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <queue>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -121,8 +122,18 @@ struct gtb_engine {
   std::vector<int32_t> g_bucket, g_index;   // graph position -> (bucket, index)
   Plan plan;
   bool has_plan = false;
-  std::vector<LevelSched> sched;
+  std::vector<LevelSched> sched[2];   // phase 0: this rank's subtrees, phase 1: the shared top of the tree (rank 0)
+  std::vector<int32_t> sched_lists;   // clique lists of both phases, level by level
   std::vector<ChildWork> child_work;
+  // ---- distribution over ranks: one process per GPU ----
+  int rank = 0, world = 1;
+  gtb_comm_fn comm = nullptr;
+  void* comm_user = nullptr;
+  std::vector<int32_t> owner;         // per clique: owning rank, or -1 for the top of the tree
+  std::vector<int64_t> front_off;     // per clique: offset in this engine's arena (top fronts live in one tail region)
+  std::vector<int32_t> top_list;
+  int64_t top_off = 0, top_doubles = 0, arena_doubles = 0, top_work_begin = 0, top_zero_blocks = 0;
+  int32_t n_top_work = 0;
   std::vector<int32_t> bs_list, bs_scratch_off;
   int64_t bs_scratch_doubles = 0;
   std::vector<StepTask> step_tasks_list;
@@ -144,7 +155,9 @@ struct gtb_engine {
   DevBuf<CliqueDev> d_cliques;
   DevBuf<SlotDev> d_slots;
   DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list, d_bs_scratch_off;
-  DevBuf<double> d_bs_scratch;
+  DevBuf<double> d_bs_scratch, d_delta_own;
+  DevBuf<int32_t> d_top_list;
+  DevBuf<uint8_t> d_own_mask;
   DevBuf<ChildWork> d_child_work;
   DevBuf<StepTask> d_step_tasks;
   DevBuf<long long> d_dbg;
@@ -290,10 +303,10 @@ struct StageTimer {
 
 // kernel classes for launch counting and optional per-launch event timing
 enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_ZERO, K_LFACT, K_LCHILD, K_STEP,
-       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_NUM };
+       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
                                           "small_front", "thin_front", "large_zero", "large_factors", "large_children", "front_step",
-                                          "backsolve", "backsolve_gemv", "retract"};
+                                          "backsolve", "backsolve_gemv", "retract", "own_delta"};
 
 static void prof_begin(Engine* e, int k) {
   if (!e->profiling) return;
@@ -498,8 +511,8 @@ static void finalize_problem(Engine* e) {
     bk.z = e->d_z[b].p; bk.nk = e->d_nk[b].p; bk.noise = e->d_noise[b].p; bk.Ab = e->d_Ab[b].p;
   }
   e->d_partials.alloc(2 * std::max<int64_t>(e->n_partials, 1));
-  e->d_scalars.alloc(8);
-  CK(cudaMallocHost(&e->h_scalars, 8 * sizeof(double)));
+  e->d_scalars.alloc(16);
+  CK(cudaMallocHost(&e->h_scalars, 16 * sizeof(double)));
   e->d_delta.alloc(e->n_scalars);
   e->d_hdiag.alloc(e->n_scalars);
   e->d_damp.alloc(e->n_scalars);
@@ -533,26 +546,147 @@ static void finalize_problem(Engine* e) {
 // ------------------------------------------------------------------------------------------------------
 // symbolic plan -> device
 // ------------------------------------------------------------------------------------------------------
-static void install_plan(Engine* e) {
-  const Plan& p = e->plan;
+// extend-add work items of one child: column chunks of roughly equal triangle area
+static void push_child_work(Engine* e, int32_t ch) {
+  const int32_t S1 = e->plan.S[ch] + 1;
+  const int32_t nchunk = std::max(1, std::min(64, (int32_t)(((int64_t)S1 * S1 / 2) / 8192)));
+  int32_t c0 = 0;
+  for (int32_t k2 = 1; k2 <= nchunk; ++k2) {
+    int32_t c1 = (k2 == nchunk) ? S1 : (int32_t)std::lround(S1 * std::sqrt((double)k2 / nchunk));
+    c1 = std::max(c1, c0);
+    if (c1 > c0) e->child_work.push_back(ChildWork{ch, c0, c1, 0});
+    c0 = c1;
+  }
+}
+
+// Cost model of a front for the partitioner: elimination flops plus a fixed per-front term (launch / latency share).
+static double front_cost(const Plan& p, int32_t c) {
+  const double F = p.F[c], N1 = p.F[c] + p.S[c] + 1;
+  return F * N1 * N1 + 2e4;
+}
+
+// Modelled time of one factorisation under an ownership map: every rank walks its levels (a level costs the longest
+// chain of dependent panel steps in it or its flops at the sustained tile rate, whichever is larger, plus its small
+// fronts), then the top fronts are reduced and rank 0 walks the top.  Constants are the measured C3 figures
+// (DESIGN.md section 4); only the ranking of candidate cuts matters.
+static double modelled_time(const Plan& p, const std::vector<int32_t>& owner, int world) {
+  const double tau = 30e-6, rate = 6e12, t_small = 25e-9, bw = 3e11;
+  const int L = p.n_levels, G = world + 1;
+  std::vector<double> flops((size_t)G * L, 0.0), steps((size_t)G * L, 0.0), smalls((size_t)G * L, 0.0);
+  double reduce_bytes = 0;
+  for (int32_t c = 0; c < p.n_cliques; ++c) {
+    const int g = owner[c] < 0 ? world : owner[c];
+    const size_t k = (size_t)g * L + p.level[c];
+    const int dim = p.F[c] + p.S[c] + 1;
+    if (is_small_front(p.F[c], dim)) {
+      smalls[k] += 1;
+    } else {
+      flops[k] += (double)p.F[c] * dim * dim;
+      steps[k] = std::max(steps[k], (double)((p.F[c] + NB - 1) / NB + 1));
+    }
+    if (owner[c] < 0) reduce_bytes += 8.0 * p.ld[c] * dim;
+  }
+  double worst = 0, top = 0;
+  for (int g = 0; g < G; ++g) {
+    double t = 0;
+    for (int l = 0; l < L; ++l) {
+      const size_t k = (size_t)g * L + l;
+      t += std::max(steps[k] * tau, flops[k] / rate) + smalls[k] * t_small;
+    }
+    if (g < world) worst = std::max(worst, t);
+    else top = t;
+  }
+  return worst + top + (world > 1 ? reduce_bytes / bw : 0.0);
+}
+
+// Ownership of cliques for `world` ranks: the top of the tree (owner -1) is assembled by fan-in from all
+// ranks and factored on rank 0; every subtree hanging below it belongs to exactly one rank.  Candidate tops grow from
+// the roots by opening the heaviest remaining subtree (large fronts only); for each candidate the subtrees are assigned
+// heaviest-first to the least loaded rank and the cut with the smallest modelled time is kept (possibly the empty top:
+// a chain-like tree stays on one rank).  Deterministic: every rank computes the same map.
+static void compute_partition(const Plan& p, int world, std::vector<int32_t>& owner) {
   const int32_t C = p.n_cliques;
-  // level schedules
-  e->sched.assign(p.n_levels, LevelSched());
-  e->child_work.clear();
-  e->bs_list.clear();
-  e->bs_scratch_off.clear();
-  e->bs_scratch_doubles = 0;
-  e->step_tasks_list.clear();
+  owner.assign(C, 0);
+  if (world <= 1) return;
+  std::vector<double> sub(C);
+  for (int32_t c = 0; c < C; ++c) sub[c] = front_cost(p, c);
+  for (int32_t c = 0; c < C; ++c)   // post-order: children before parents
+    if (p.parent[c] >= 0) sub[p.parent[c]] += sub[c];
+  typedef std::pair<double, int32_t> Item;
+  // the opening sequence
+  std::vector<int32_t> seq;
+  {
+    std::priority_queue<Item> open;
+    for (int32_t c = 0; c < C; ++c)
+      if (p.parent[c] < 0) open.push(Item(sub[c], c));
+    while (!open.empty() && seq.size() < 48) {
+      const int32_t c = open.top().second;
+      open.pop();
+      const bool large = !is_small_front(p.F[c], p.F[c] + p.S[c] + 1);
+      if (!large || p.child_off[c + 1] == p.child_off[c]) continue;
+      seq.push_back(c);
+      for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k) open.push(Item(sub[p.children[k]], p.children[k]));
+    }
+  }
+  auto assign = [&](size_t n_open, std::vector<int32_t>& own) {
+    own.assign(C, -2);
+    for (size_t k = 0; k < n_open; ++k) own[seq[k]] = -1;
+    std::vector<Item> roots;
+    for (int32_t c = 0; c < C; ++c)
+      if (own[c] != -1 && (p.parent[c] < 0 || own[p.parent[c]] == -1)) roots.push_back(Item(sub[c], c));
+    std::sort(roots.begin(), roots.end(), [](const Item& a, const Item& b) {
+      return a.first != b.first ? a.first > b.first : a.second < b.second;
+    });
+    typedef std::pair<double, int> Load;   // (load, rank): least loaded first, ties to the lower rank
+    std::priority_queue<Load, std::vector<Load>, std::greater<Load>> ranks;
+    for (int r = 0; r < world; ++r) ranks.push(Load(0.0, r));
+    for (const Item& it : roots) {
+      Load l = ranks.top();
+      ranks.pop();
+      own[it.second] = l.second;
+      l.first += it.first;
+      ranks.push(l);
+    }
+    for (int32_t c = C - 1; c >= 0; --c)   // parents before children
+      if (own[c] == -2) own[c] = own[p.parent[c]];
+  };
+  double best = std::numeric_limits<double>::infinity();
+  std::vector<int32_t> cand;
+  // GTB_MIN_TOP=k (tests): consider only cuts with at least k top cliques, so that small problems exercise the fan-in
+  const char* mt = getenv("GTB_MIN_TOP");
+  const size_t min_top = std::min(seq.size(), (size_t)(mt ? std::max(0, atoi(mt)) : 0));
+  for (size_t n_open = min_top; n_open <= seq.size(); ++n_open) {
+    assign(n_open, cand);
+    const double t = modelled_time(p, cand, world);
+    if (t < best) { best = t; owner = cand; }
+  }
+}
+
+// Builds the level schedule of one phase: phase 0 = subtree cliques owned by this rank, phase 1 = the shared top of the
+// tree (factored on rank 0 after the fan-in reduction; empty when there is one rank).
+static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
+  const Plan& p = e->plan;
+  std::vector<LevelSched>& sched = e->sched[ph];
+  sched.assign(p.n_levels, LevelSched());
+  auto mine = [&](int32_t c) { return ph == 0 ? e->owner[c] == e->rank : e->owner[c] < 0; };
   for (int32_t l = 0; l < p.n_levels; ++l) {
-    LevelSched& L = e->sched[l];
-    const int64_t b = p.level_off[l], ns = p.level_n_small[l], en = p.level_off[l + 1];
+    LevelSched& L = sched[l];
+    // filtered copy of the level list: small fronts first, then large ones (the plan's order)
+    const int64_t pb = p.level_off[l], pns = p.level_n_small[l], pen = p.level_off[l + 1];
+    const int64_t b = (int64_t)lc.size();
+    int64_t ns = 0;
+    for (int64_t q = pb; q < pen; ++q)
+      if (mine(p.level_cliques[q])) {
+        lc.push_back(p.level_cliques[q]);
+        if (q < pb + pns) ++ns;
+      }
+    const int64_t en = (int64_t)lc.size();
     L.n_all = (int32_t)(en - b);
-    // small classes by front dimension; the list inside the level is re-sorted by dim so classes are contiguous
     L.large_begin = b + ns;
     L.n_large = (int32_t)(en - b - ns);
     L.min_F = INT_MAX;
     for (int64_t q = L.large_begin; q < en; ++q) {
-      const int32_t c = p.level_cliques[q];
+      const int32_t c = lc[q];
       L.max_F = std::max(L.max_F, p.F[c]);
       L.min_F = std::min(L.min_F, p.F[c]);
       L.max_dim = std::max(L.max_dim, p.F[c] + p.S[c] + 1);
@@ -566,7 +700,7 @@ static void install_plan(Engine* e) {
         // role-A slices of every clique first (critical path), then the tile tasks
         for (int pass = 0; pass < 2; ++pass)
           for (int64_t q = L.large_begin; q < en; ++q) {
-            const int32_t c = p.level_cliques[q];
+            const int32_t c = lc[q];
             const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + NB - 1) / NB;
             if (sidx > np_c) continue;
             const int n = step_tasks(F, dim, sidx);
@@ -581,29 +715,20 @@ static void install_plan(Engine* e) {
         L.step_count.push_back((int32_t)(e->step_tasks_list.size() - L.step_begin.back()));
       }
     }
+    // extend-add work of this level's large parents.  Phase 1 only adds the children that are top cliques themselves:
+    // subtree children were added before the reduction by whichever rank owns them (top_work).
     L.work_begin = (int64_t)e->child_work.size();
     for (int64_t q = L.large_begin; q < en; ++q) {
-      const int32_t c = p.level_cliques[q];
-      for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k) {
-        const int32_t ch = p.children[k];
-        const int32_t S1 = p.S[ch] + 1;
-        // chunks of roughly equal triangle area
-        const int32_t nchunk = std::max(1, std::min(64, (int32_t)(((int64_t)S1 * S1 / 2) / 8192)));
-        int32_t c0 = 0;
-        for (int32_t k2 = 1; k2 <= nchunk; ++k2) {
-          int32_t c1 = (k2 == nchunk) ? S1 : (int32_t)std::lround(S1 * std::sqrt((double)k2 / nchunk));
-          c1 = std::max(c1, c0);
-          if (c1 > c0) e->child_work.push_back(ChildWork{ch, c0, c1, 0});
-          c0 = c1;
-        }
-      }
+      const int32_t c = lc[q];
+      for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k)
+        if (ph == 0 || e->owner[p.children[k]] < 0) push_child_work(e, p.children[k]);
     }
     L.n_work = (int32_t)(e->child_work.size() - L.work_begin);
     L.bs_begin = (int64_t)e->bs_list.size();
     int32_t maxN = 0;
     for (int pass = 0; pass < 2; ++pass)
       for (int64_t q = b; q < en; ++q) {
-        const int32_t c = p.level_cliques[q];
+        const int32_t c = lc[q];
         const bool warp_class = p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kDenseMaxDim;
         if (warp_class != (pass == 0)) continue;
         e->bs_list.push_back(c);
@@ -628,12 +753,8 @@ static void install_plan(Engine* e) {
       e->bs_scratch_doubles = std::max(e->bs_scratch_doubles, off);
     }
     L.bs_cta_smem = (maxN + 512 + 32) * (int32_t)sizeof(double);
-  }
-  // re-sort the small part of every level by dimension and cut into thread classes
-  std::vector<int32_t> lc = p.level_cliques;
-  for (int32_t l = 0; l < p.n_levels; ++l) {
-    LevelSched& L = e->sched[l];
-    const int64_t b = p.level_off[l], ns = p.level_n_small[l];
+
+    // re-sort the small part of the level by dimension and cut into thread classes
     auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
     // thin fronts first (sorted by dimension), then dense ones (sorted by dimension)
     auto thin = [&](int32_t c) { return is_thin_front(p.F[c], dim_of(c)); };
@@ -671,7 +792,50 @@ static void install_plan(Engine* e) {
       L.small.push_back(cl);
     }
   }
-  e->plan.level_cliques = lc;
+}
+
+static void install_plan(Engine* e) {
+  const Plan& p = e->plan;
+  const int32_t C = p.n_cliques;
+  compute_partition(p, e->world, e->owner);
+  e->child_work.clear();
+  e->bs_list.clear();
+  e->bs_scratch_off.clear();
+  e->bs_scratch_doubles = 0;
+  e->step_tasks_list.clear();
+  std::vector<int32_t> lc;
+  lc.reserve(C);
+  build_phase(e, 0, lc);
+  build_phase(e, 1, lc);
+  e->sched_lists = lc;
+  // the shared top: fronts relocated to one contiguous tail of the arena (identical on every rank) so that the fan-in
+  // is a single reduction; assembled before it from own factors (rank 0) and from the subtree children each rank owns
+  e->front_off = p.front_off;
+  e->top_list.clear();
+  e->top_off = (p.arena_doubles + 15) & ~(int64_t)15;
+  int64_t tail = e->top_off;
+  e->top_zero_blocks = 0;
+  for (int32_t c = 0; c < C; ++c)
+    if (e->owner[c] < 0) {
+      e->top_list.push_back(c);
+      e->front_off[c] = tail;
+      const int64_t sz = (int64_t)p.ld[c] * (p.F[c] + p.S[c] + 1);
+      tail += (sz + 15) & ~(int64_t)15;
+      e->top_zero_blocks = std::max<int64_t>(e->top_zero_blocks, (sz / 2 + 255) / 256);
+    }
+  e->top_zero_blocks = std::min<int64_t>(e->top_zero_blocks, 64);
+  e->top_doubles = tail - e->top_off;
+  e->arena_doubles = e->top_list.empty() ? p.arena_doubles : tail;
+  e->top_work_begin = (int64_t)e->child_work.size();
+  for (int32_t c : e->top_list)
+    for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k)
+      if (e->owner[p.children[k]] == e->rank) push_child_work(e, p.children[k]);
+  e->n_top_work = (int32_t)(e->child_work.size() - e->top_work_begin);
+  // scalars whose solution this rank produces (frontals of its cliques; the top belongs to rank 0)
+  std::vector<uint8_t> own(e->n_scalars, 0);
+  for (int32_t c = 0; c < C; ++c)
+    if (e->owner[c] == e->rank || (e->owner[c] < 0 && e->rank == 0))
+      for (int32_t k = 0; k < p.F[c]; ++k) own[p.gidx[p.gidx_off[c] + k]] = 1;
   if (!e->has_device) return;
 
   cudaStream_t st = e->stream;
@@ -679,7 +843,7 @@ static void install_plan(Engine* e) {
   int64_t dfac_total = 0;
   for (int32_t c = 0; c < C; ++c) {
     CliqueDev& d = cd[c];
-    d.front_off = p.front_off[c];
+    d.front_off = e->front_off[c];
     d.F = p.F[c]; d.S = p.S[c]; d.ld = p.ld[c]; d.parent = p.parent[c];
     d.fac_begin = (int32_t)p.fac_off[c]; d.fac_end = (int32_t)p.fac_off[c + 1];
     d.child_begin = (int32_t)p.child_off[c]; d.child_end = (int32_t)p.child_off[c + 1];
@@ -703,7 +867,9 @@ static void install_plan(Engine* e) {
   e->d_children.upload(p.children, st);
   e->d_pmap.upload(p.pmap, st);
   e->d_gidx.upload(p.gidx, st);
-  e->d_level_cliques.upload(e->plan.level_cliques, st);
+  e->d_level_cliques.upload(e->sched_lists, st);
+  e->d_top_list.upload(e->top_list, st);
+  e->d_own_mask.upload(own, st);
   e->d_child_work.upload(e->child_work, st);
   e->d_bs_list.upload(e->bs_list, st);
   e->d_bs_scratch_off.upload(e->bs_scratch_off, st);
@@ -712,7 +878,8 @@ static void install_plan(Engine* e) {
   e->d_dbg.alloc(8);
   e->d_fail.alloc(1);
   e->d_dfac.alloc((size_t)dfac_total + NB * NB);
-  e->d_arena.alloc((size_t)p.arena_doubles + 16);
+  e->d_arena.alloc((size_t)e->arena_doubles + 16);
+  if (e->world > 1) e->d_delta_own.alloc((size_t)e->n_scalars + 2);
   CK(cudaStreamSynchronize(st));
   e->factorized = e->solved = false;
 }
@@ -833,6 +1000,44 @@ static ElimDev elim_dev(Engine* e, bool damp) {
   return E;
 }
 
+static void comm(Engine* e, int op, double* buf, int64_t count) {
+  if (e->world <= 1) return;
+  if (!e->comm) throw StatusError(GTB_ERR_INVALID, "gtb_set_distributed: world > 1 needs a communication callback");
+  if (e->comm(e->comm_user, op, buf, count, e->stream) != 0) throw StatusError(GTB_ERR_CUDA, "communication callback failed");
+}
+
+// Elimination of one phase, leaves to roots.  Phase 1 fronts were cleared and partly assembled before the fan-in; only
+// the children that are top cliques themselves are added here.
+static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
+  cudaStream_t st = e->stream;
+  const int32_t* lists = e->d_level_cliques.p;
+  for (int32_t l = 0; l < e->plan.n_levels; ++l) {
+    const LevelSched& L = e->sched[phase][l];
+    for (const auto& c : L.small) {
+      if (c.kind == 0)
+        LAUNCH(e, K_THIN, thin_front_kernel<true><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
+                              E, lists + c.begin, c.count, c.group_doubles));
+      else if (c.kind == 1)
+        LAUNCH(e, K_THIN, thin_front_kernel<false><<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin, c.count,
+                                                                                       c.group_doubles));
+      else
+        LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
+    }
+    if (!L.n_large) continue;
+    const int32_t* ll = lists + L.large_begin;
+    if (phase == 0) {
+      LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3((unsigned)L.zero_blocks, L.n_large), 256, 0, st>>>(E, ll));
+      LAUNCH(e, K_LFACT, large_factors_kernel<<<L.n_large, 256, 0, st>>>(E, ll));
+    }
+    if (L.n_work) {
+      LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
+    }
+    for (size_t s = 0; s < L.step_count.size(); ++s)
+      if (L.step_count[s] > 0)
+        LAUNCH(e, K_STEP, front_step_kernel<<<L.step_count[s], 256, kStepSmem, st>>>(E, e->d_step_tasks.p + L.step_begin[s], (int)s));
+  }
+}
+
 // returns failing clique id or -1
 static int32_t factorize(Engine* e, double lambda, int diag, double lo, double hi) {
   need_device(e);
@@ -864,47 +1069,39 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     CK(cudaFuncSetAttribute(backsolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr = true;
   }
-  const int32_t* lists = e->d_level_cliques.p;
-  for (int32_t l = 0; l < e->plan.n_levels; ++l) {
-    const LevelSched& L = e->sched[l];
-    for (const auto& c : L.small) {
-      if (c.kind == 0)
-        LAUNCH(e, K_THIN, thin_front_kernel<true><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
-                              E, lists + c.begin, c.count, c.group_doubles));
-      else if (c.kind == 1)
-        LAUNCH(e, K_THIN, thin_front_kernel<false><<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin, c.count,
-                                                                                       c.group_doubles));
-      else
-        LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
-    }
-    if (!L.n_large) continue;
-    const int32_t* ll = lists + L.large_begin;
-    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3((unsigned)L.zero_blocks, L.n_large), 256, 0, st>>>(E, ll));
-    LAUNCH(e, K_LFACT, large_factors_kernel<<<L.n_large, 256, 0, st>>>(E, ll));
-    if (L.n_work) {
-      LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
-    }
-    for (size_t s = 0; s < L.step_count.size(); ++s)
-      if (L.step_count[s] > 0)
-        LAUNCH(e, K_STEP, front_step_kernel<<<L.step_count[s], 256, kStepSmem, st>>>(E, e->d_step_tasks.p + L.step_begin[s], (int)s));
+  factorize_levels(e, E, 0);
+  if (!e->top_list.empty()) {
+    // fan-in: every rank adds what it owns into its copy of the top fronts, the copies are summed onto rank 0
+    const int nt = (int)e->top_list.size();
+    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3((unsigned)e->top_zero_blocks, nt), 256, 0, st>>>(E, e->d_top_list.p));
+    if (e->rank == 0) LAUNCH(e, K_LFACT, large_factors_kernel<<<nt, 256, 0, st>>>(E, e->d_top_list.p));
+    if (e->n_top_work)
+      LAUNCH(e, K_LCHILD, large_children_kernel<<<e->n_top_work, 256, 0, st>>>(E, e->d_child_work.p + e->top_work_begin));
+    comm(e, GTB_COMM_REDUCE_SUM_TO_0, e->d_arena.p + e->top_off, e->top_doubles);
+    if (e->rank == 0) factorize_levels(e, E, 1);
   }
   CK(cudaMemcpyAsync(e->h_scalars + 4, e->d_fail.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  tm.stop();
   int32_t fail;
   std::memcpy(&fail, e->h_scalars + 4, sizeof(int32_t));
+  if (e->world > 1) {
+    // every rank must take the same branch of the LM control flow: agree on the first failing clique
+    const double mine = (double)fail;
+    CK(cudaMemcpyAsync(e->d_scalars.p + 8, &mine, sizeof(double), cudaMemcpyHostToDevice, st));
+    comm(e, GTB_COMM_ALLREDUCE_MIN, e->d_scalars.p + 8, 1);
+    CK(cudaMemcpyAsync(e->h_scalars + 5, e->d_scalars.p + 8, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    fail = (int32_t)e->h_scalars[5];
+  }
+  tm.stop();
   e->factorized = (fail == INT_MAX);
   e->solved = false;
   return fail == INT_MAX ? -1 : fail;
 }
 
-static void backsolve(Engine* e) {
-  need_device(e);
-  need(e->factorized, "gtb_backsolve needs a successful gtb_factorize first");
-  StageTimer tm(e, 2);
-  const ElimDev E = elim_dev(e, false);
+static void backsolve_levels(Engine* e, const ElimDev& E, int phase) {
   for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
-    const LevelSched& L = e->sched[l];
+    const LevelSched& L = e->sched[phase][l];
     const int32_t* bl = e->d_bs_list.p + L.bs_begin;
     const int32_t* so = e->d_bs_scratch_off.p + L.bs_begin;
     if (L.n_bs_warp)
@@ -920,6 +1117,24 @@ static void backsolve(Engine* e) {
       LAUNCH(e, K_BACKSOLVE, backsolve_kernel<false><<<L.n_bs_cta, 512, L.bs_cta_smem, e->stream>>>(
                                  E, bl + L.n_bs_warp, L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, e->d_bs_scratch.p));
     }
+  }
+}
+
+static void backsolve(Engine* e) {
+  need_device(e);
+  need(e->factorized, "gtb_backsolve needs a successful gtb_factorize first");
+  StageTimer tm(e, 2);
+  const ElimDev E = elim_dev(e, false);
+  if (!e->top_list.empty()) {
+    if (e->rank == 0) backsolve_levels(e, E, 1);
+    comm(e, GTB_COMM_BROADCAST_FROM_0, e->d_delta.p, e->n_scalars);
+  }
+  backsolve_levels(e, E, 0);
+  if (e->world > 1) {
+    const int n = (int)e->n_scalars;
+    LAUNCH(e, K_OWNDELTA, own_delta_kernel<<<(n + 255) / 256, 256, 0, e->stream>>>(n, e->d_delta.p, e->d_own_mask.p, e->d_delta_own.p));
+    comm(e, GTB_COMM_ALLREDUCE_SUM, e->d_delta_own.p, e->n_scalars);
+    CK(cudaMemcpyAsync(e->d_delta.p, e->d_delta_own.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
   }
   tm.stop();
   e->solved = true;
@@ -1137,6 +1352,35 @@ gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, 
     for (size_t i = 0; i < p.vars.size(); ++i) keys[i] = e->vkeys[p.vars[i]];
   return GTB_OK;
 }
+gtb_status gtb_set_distributed(gtb_engine* e, int32_t rank, int32_t world, gtb_comm_fn fn, void* user) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need(world >= 1 && rank >= 0 && rank < world, "gtb_set_distributed: need 0 <= rank < world");
+  need(world == 1 || fn || !e->has_device, "gtb_set_distributed: world > 1 needs a communication callback");
+  e->rank = rank; e->world = world; e->comm = fn; e->comm_user = user;
+  if (e->has_plan) install_plan(e);
+  GTB_CATCH(e)
+}
+gtb_status gtb_partition_get(const gtb_engine* e, int32_t* owner, double* out) {
+  if (!e) return GTB_ERR_INVALID;
+  if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
+  const Plan& p = e->plan;
+  if (owner) std::memcpy(owner, e->owner.data(), sizeof(int32_t) * p.n_cliques);
+  if (out) {
+    for (int k = 0; k < 16; ++k) out[k] = 0;
+    double total = 0;
+    for (int32_t c = 0; c < p.n_cliques; ++c) {
+      const double w = front_cost(p, c);
+      total += w;
+      if (e->owner[c] < 0) out[2] += w;
+      else if (e->owner[c] < 13) out[3 + e->owner[c]] += w;
+    }
+    for (int k = 2; k < 16; ++k) out[k] /= total;
+    out[0] = (double)e->top_list.size();
+    out[1] = (double)e->top_doubles;
+  }
+  return GTB_OK;
+}
 gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
   if (!e || !out) return GTB_ERR_INVALID;
   if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
@@ -1235,12 +1479,13 @@ gtb_status gtb_get_conditionals(gtb_engine* e, double* out) {
   need(e->factorized && out, "gtb_get_conditionals needs a successful gtb_factorize first");
   const Plan& p = e->plan;
   // parity dump: not a hot path; stage the whole arena through the host
-  std::vector<double> arena((size_t)p.arena_doubles);
+  // (with several ranks only the cliques this rank factored hold conditionals; the others read back as assembled)
+  std::vector<double> arena((size_t)e->arena_doubles);
   CK(cudaMemcpyAsync(arena.data(), e->d_arena.p, arena.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
   for (int32_t c = 0; c < p.n_cliques; ++c) {
     const int F = p.F[c], dim = F + p.S[c] + 1, ld = p.ld[c];
-    const double* A = arena.data() + p.front_off[c];
+    const double* A = arena.data() + e->front_off[c];
     double* o = out + p.cond_off[c];
     for (int i = 0; i < F; ++i)
       for (int j = 0; j < dim; ++j) o[(int64_t)i * dim + j] = (j >= i) ? A[i + (int64_t)j * ld] : 0.0;

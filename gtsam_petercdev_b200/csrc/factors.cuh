@@ -628,6 +628,14 @@ __global__ void damping_kernel(int n, double s, int diag_mode, double lo, double
   }
 }
 
+// Several ranks: keep the entries of delta this rank solved for and clear the rest, so that a sum over ranks rebuilds
+// the whole vector exactly (every entry has one owner).
+__global__ void __launch_bounds__(256)
+own_delta_kernel(int n, const double* __restrict__ delta, const uint8_t* __restrict__ own, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = own[i] ? delta[i] : 0.0;
+}
+
 // Values::retract (nonlinear/Values.cpp:53-63): one thread per variable of one type.
 template <int VT>
 __global__ void __launch_bounds__(128)

@@ -99,6 +99,21 @@ class Engine:
         keys = np.ascontiguousarray(keys, dtype=np.uint64)
         self._ck(self.lib.gtb_set_ordering(self.h, len(keys), _ptr(keys)))
 
+    def set_distributed(self, rank, world, comm=None):
+        """One engine per process / GPU.  `comm` is a capi.COMM_FN (see distributed.py); keep it alive with the engine."""
+        self._comm = comm
+        fn = C.cast(comm, C.c_void_p) if comm is not None else None
+        self._ck(self.lib.gtb_set_distributed(self.h, int(rank), int(world), fn, None))
+
+    def partition(self):
+        nc = C.c_int64()
+        self._ck(self.lib.gtb_plan_sizes(self.h, C.byref(nc), None, None, None))
+        owner = np.zeros(nc.value, dtype=np.int32)
+        st = np.zeros(16)
+        self._ck(self.lib.gtb_partition_get(self.h, _ptr(owner), _ptr(st)))
+        return dict(owner=owner, n_top=int(st[0]), reduced_doubles=int(st[1]), top_share=float(st[2]),
+                    rank_share=st[3:].copy())
+
     def plan(self):
         nc, nk, ncond, ns = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
         self._ck(self.lib.gtb_plan_sizes(self.h, C.byref(nc), C.byref(nk), C.byref(ncond), C.byref(ns)))

@@ -172,6 +172,30 @@ gtb_status gtb_lm_iterate(gtb_engine* e, const gtb_lm_params* p, double* lambda_
 gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double relative_error_tol,
                            double absolute_error_tol, gtb_lm_result* result);
 
+/* ---- several GPUs: one engine per process / GPU ---------------------------------------------
+ * The reference parallelises elimination over the children of a clique with TBB tasks
+ * (inference/ClusterTree-inst.h:286-318).  Across GPUs the same tree is cut instead: every rank holds the whole
+ * problem and the whole plan, eliminates the subtrees it owns, adds their Schur complements into its copy of the
+ * fronts at the top of the tree, and the top fronts are summed onto rank 0 (fan-in), which factors them.
+ * Back-substitution runs the other way: rank 0 solves the top, the solution is broadcast, every rank solves its
+ * subtrees and the owned pieces of delta are summed so that each replica can retract.
+ * The library does not link a communication library: the caller supplies the three collectives below
+ * (ncclReduce / ncclBroadcast / ncclAllReduce on `stream` in a GTSAM build; torch.distributed in bench.py).
+ * `buf` is a device pointer to `count` doubles; the call must be ordered on `stream` (a cudaStream_t) or complete
+ * before it returns.  Return 0 on success.                                                               */
+#define GTB_COMM_REDUCE_SUM_TO_0 0
+#define GTB_COMM_BROADCAST_FROM_0 1
+#define GTB_COMM_ALLREDUCE_SUM 2
+#define GTB_COMM_ALLREDUCE_MIN 3
+typedef int (*gtb_comm_fn)(void* user, int op, void* buf, int64_t count, void* stream);
+/* Call after gtb_finalize_problem and before gtb_set_ordering*.  world = 1 restores the single-GPU schedule.
+ * comm may be NULL on an engine without a device (host-side partition tests).                            */
+gtb_status gtb_set_distributed(gtb_engine* e, int32_t rank, int32_t world, gtb_comm_fn comm, void* user);
+/* Owner rank of every clique (post-order ids as in gtb_plan_get); -1 = top of the tree (fan-in, rank 0).
+ * stats: out[0] = number of top cliques, out[1] = doubles reduced per factorisation, out[2] = cost share of the top
+ * (model), out[3 + r] for r < world (at most 13) = cost share of rank r's subtrees.                            */
+gtb_status gtb_partition_get(const gtb_engine* e, int32_t* owner, double* out16);
+
 /* ---- instrumentation ------------------------------------------------------------------------------- */
 /* Number of engine kernels launched since creation.                                                      */
 int64_t gtb_kernel_launches(const gtb_engine* e);
