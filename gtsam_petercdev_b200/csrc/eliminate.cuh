@@ -374,12 +374,18 @@ __global__ void __launch_bounds__(256) large_children_kernel(ElimDev E, const Ch
 //                   blocks move from their side buffer into the front
 // Role A of step p and role B of step p touch disjoint rows, and both only read panel p-1, so no CTA waits on
 // another inside a launch.
-constexpr int NB = 32;       // panel height
+constexpr int NB = 32;       // K-chunk of the tile update and side of the in-register Cholesky block
+constexpr int PW = 2 * NB;   // panel height: 64 pivots per launch (two NB blocks factored back to back inside role A)
 constexpr int TW = 64;       // tile width
 constexpr int LDT = NB + 4;  // shared leading dimension of a K x 64 operand tile (K contiguous), 36: conflict-free
-constexpr int SLICE = 7 * 32;   // columns per role-A CTA: warp 0 factors the diagonal block, warps 1..7 own 32 columns
+constexpr int LDP = PW + 4;  // shared leading dimension of the role-A operands (68: conflict-free for the DMMA fragments)
+constexpr int CWID = 8;      // columns per role-A column warp (one DMMA n-tile)
+constexpr int SLICE = 7 * CWID;   // columns per role-A CTA: warp 0 factors the diagonal block, warps 1..7 own 8 columns each
 constexpr int kStepSmemTile = 4 * TW * LDT * (int)sizeof(double);                       // two double-buffered operand tiles
-constexpr int kStepSmemA = (3 * NB * LDT + 2 * NB + 7 * (NB * LDT + NB * 12)) * (int)sizeof(double);
+// role A: Ps, Ds, Ws (8 x 8 inverses), dinv, flag, warp 0's scratch, then Xs + Ts per column warp
+constexpr int kRoleAWarp0 = 2 * PW * LDP + PW * 12 + PW + 2 + NB * 12;
+constexpr int kRoleAColWarp = CWID * LDP + CWID * 12;
+constexpr int kStepSmemA = (kRoleAWarp0 + 7 * kRoleAColWarp) * (int)sizeof(double);
 constexpr int kStepSmem = kStepSmemA > kStepSmemTile ? kStepSmemA : kStepSmemTile;
 
 // FP64 tensor-core tile: m8n8k4 DMMA (mma.sync), D = A * B + C
@@ -475,9 +481,9 @@ __device__ __forceinline__ void trapezoid_decode(int t, int nct, int& ty, int& t
 }
 // tasks of clique (F, dim) at panel step p (host mirrors this to size the grid)
 __host__ __device__ __forceinline__ int step_tasks(int F, int dim, int p) {
-  const int np = (F + NB - 1) / NB;
+  const int np = (F + PW - 1) / PW;
   if (p < np) {
-    const int k0 = p * NB, kb = (F - k0 < NB) ? F - k0 : NB, rest0 = k0 + kb;
+    const int k0 = p * PW, kb = (F - k0 < PW) ? F - k0 : PW, rest0 = k0 + kb;
     int n = (dim - rest0 + SLICE - 1) / SLICE;
     if (p >= 1) n += trapezoid_tiles((F - rest0 + TW - 1) / TW, (dim - rest0 + TW - 1) / TW);
     return n;
@@ -491,16 +497,114 @@ __host__ __device__ __forceinline__ int step_tasks(int F, int dim, int p) {
 
 struct StepTask { int32_t clique; int32_t task; };
 
+// One warp: Cholesky (upper) of the 32 x 32 block Dh[i * LDP + l] = D(l, i) held in shared memory, in registers with
+// lane = column; rows / columns beyond the front are identity padding.  Also leaves 1 / R(i, i) in dinv_h and the inverses
+// of the four 8 x 8 diagonal blocks in Ws_h[i * 12 + r].  Returns false on a non-positive pivot (Eigen LLT
+// NumericalIssue, base/cholesky.cpp:126-128).  Not inlined: the unrolled body is ~4.5k instructions and is used twice.
+__device__ __noinline__ bool potrf32_warp(double* Dh, double* dinv_h, double* Ws_h, int lane) {
+  bool okw = true;
+  double d[NB];
+#pragma unroll
+  for (int i = 0; i < NB; ++i) d[i] = Dh[lane * LDP + i];
+  double myinv = 1.0;
+  // software-pipelined: the next pivot column is updated first so that its rsqrt overlaps the rest of the rank-1 update
+  double pk = __shfl_sync(0xffffffffu, d[0], 0);
+  double rinv = rsqrt(pk);
+#pragma unroll
+  for (int k = 0; k < NB; ++k) {
+    okw = okw && (pk > 0.0);
+    if (lane > k) d[k] *= rinv;
+    else if (lane == k) { d[k] = pk * rinv; myinv = rinv; }
+    const double ukl = d[k];
+    double pk_next = 1.0, rinv_next = 1.0;
+    if (k + 1 < NB) {
+      const double uki = __shfl_sync(0xffffffffu, d[k], k + 1);
+      if (k + 1 <= lane) d[k + 1] -= uki * ukl;
+      pk_next = __shfl_sync(0xffffffffu, d[k + 1], k + 1);
+      rinv_next = rsqrt(pk_next);
+    }
+#pragma unroll
+    for (int i = k + 2; i < NB; ++i) {
+      const double uki = __shfl_sync(0xffffffffu, d[k], i);
+      if (i <= lane) d[i] -= uki * ukl;
+    }
+    pk = pk_next;
+    rinv = rinv_next;
+  }
+#pragma unroll
+  for (int i = 0; i < NB; ++i)
+    if (i <= lane) Dh[lane * LDP + i] = d[i];
+  dinv_h[lane] = myinv;
+  __syncwarp();
+  // inverses of the four 8 x 8 diagonal blocks: lane = column, back-substitution within its block
+  const int b8 = lane & ~7, jj = lane & 7;
+  double w[8];
+#pragma unroll
+  for (int i = 7; i >= 0; --i) {
+    double sacc = 0.0;
+#pragma unroll
+    for (int k = i + 1; k < 8; ++k)
+      if (k <= jj) sacc += Dh[(b8 + k) * LDP + b8 + i] * w[k];
+    w[i] = (i == jj) ? myinv : ((i < jj) ? -sacc * dinv_h[b8 + i] : 0.0);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) Ws_h[lane * 12 + i] = w[i];
+  __syncwarp();
+  return okw;
+}
+
+// Blocked forward substitution Y = R^-T X on NT*8 columns held as X[c * LDP + i] (i = row), one warp, stages
+// [b_begin, b_end) of 8 rows each.  R is the upper factor in Ds (Ds[i * LDP + l] = R(l, i)); Ws holds the inverses of
+// its 8 x 8 diagonal blocks (Ws[i * 12 + r] = inv(R_bb)(r, i % 8)).  Rows of earlier stages must already be solved.
+template <int NT>
+__device__ __forceinline__ void trsm_stages(const double* __restrict__ Ds, const double* __restrict__ Ws, double* X,
+                                            double* Ts, int b_begin, int b_end, int g, int t) {
+#pragma unroll 1
+  for (int bi = b_begin; bi < b_end; ++bi) {
+    double acc[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) acc[nt][0] = acc[nt][1] = 0.0;
+    for (int ks = 0; ks < bi * 8; ks += 4) {
+      const double a = Ds[(bi * 8 + g) * LDP + ks + t];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) dmma884(acc[nt][0], acc[nt][1], a, X[(nt * 8 + g) * LDP + ks + t]);
+    }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int cc = nt * 8 + 2 * t + e;
+        Ts[cc * 12 + g] = X[cc * LDP + bi * 8 + g] - acc[nt][e];
+      }
+    __syncwarp();
+    double y[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) y[nt][0] = y[nt][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 8; ks += 4) {
+      // A operand = inv(R_bb)^T: element [g][ks + t] = inv(R_bb)(ks + t, g)
+      const double a = Ws[(bi * 8 + g) * 12 + ks + t];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) dmma884(y[nt][0], y[nt][1], a, Ts[(nt * 8 + g) * 12 + ks + t]);
+    }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) X[(nt * 8 + 2 * t + e) * LDP + bi * 8 + g] = y[nt][e];
+    __syncwarp();
+  }
+}
+
 __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTask* __restrict__ tasks, int p) {
   extern __shared__ __align__(16) double sm[];
   const StepTask me = tasks[blockIdx.x];   // compact list: role-A slices (the critical path) first, no empty CTAs
   const int c = me.clique;
   const CliqueDev ci = E.cliques[c];
   const int F = ci.F, dim = F + ci.S + 1, ld = ci.ld;
-  const int np = (F + NB - 1) / NB;
+  const int np = (F + PW - 1) / PW;
   if (p > np) return;
   double* A = E.arena + ci.front_off;
-  double* dfac = E.dfac + ci.dfac_off;   // np blocks of NB x NB, row-major
+  double* dfac = E.dfac + ci.dfac_off;   // np blocks of PW x PW, row-major
   int task = me.task;
   const int tid = threadIdx.x;
   if (p == np) {
@@ -511,15 +615,15 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     if (!(E.debug & 1)) tile_update(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
     if (task == 0) {
       // factored diagonal blocks: side buffer -> front (nothing in this launch reads them)
-      for (int idx = tid; idx < np * NB * NB; idx += blockDim.x) {
-        const int b = idx / (NB * NB), r = idx - b * NB * NB, i = r / NB, j = r - i * NB;
-        const int gi = b * NB + i, gj = b * NB + j;
+      for (int idx = tid; idx < np * PW * PW; idx += blockDim.x) {
+        const int b = idx / (PW * PW), r = idx - b * PW * PW, i = r / PW, j = r - i * PW;
+        const int gi = b * PW + i, gj = b * PW + j;
         if (i <= j && gj < F) A[gi + (int64_t)gj * ld] = dfac[idx];
       }
     }
     return;
   }
-  const int k0 = p * NB, kb = min(NB, F - k0), rest0 = k0 + kb;
+  const int k0 = p * PW, kb = min(PW, F - k0), rest0 = k0 + kb;
   const int nA = (dim - rest0 + SLICE - 1) / SLICE;
   if (task >= nA) {
     if (p == 0) return;
@@ -528,229 +632,182 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     if (task >= trapezoid_tiles(nrt, nct)) return;
     int ty, tx;
     trapezoid_decode(task, nct, ty, tx);
-    if (!(E.debug & 1)) tile_update(A, ld, dim, rest0 + ty * TW, rest0 + tx * TW, F, k0 - NB, k0, sm);
+    if (!(E.debug & 1)) tile_update(A, ld, dim, rest0 + ty * TW, rest0 + tx * TW, F, k0 - PW, k0, sm);
     return;
   }
-  // ---- role A: slice `task` of row panel p ----
-  // warp 0 factors the diagonal block; warps 1..7 own 32 columns each.  All GEMM-shaped work (look-ahead update,
-  // blocked triangular solve with 8 x 8 diagonal inverses) runs on the FP64 tensor pipe.
+  // ---- role A: slice `task` of row panel p (64 pivots) ----
+  // Every role-A CTA factors the 64 x 64 diagonal block redundantly (warp 0: two 32 x 32 in-register Choleskys with a
+  // 32 x 32 triangular solve and a rank-32 update between them), so no CTA waits on another inside a launch.  Warps 1..7
+  // own 8 columns each: look-ahead update by panel p-1 while warp 0 factors, then the blocked triangular solve.
+  // All GEMM-shaped work runs on the FP64 tensor pipe.
   if (E.debug & 4) return;
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-  double* Ps = sm;                    // Ps[i * LDT + l] = R[k0-32+l, k0+i]            (panel p-1, columns of D)
-  double* Ds = Ps + NB * LDT;         // Ds[i * LDT + l] = D(l, i), l <= i             (column i of the block)
-  double* Ws = Ds + NB * LDT;         // Ws[i * LDT + l] = inv(D_bb)(l, i) for l, i in the same 8-block b
-  double* dinv = Ws + NB * LDT;       // 1 / D(i, i)
-  int* s_ok = reinterpret_cast<int*>(dinv + NB);
-  double* Xs = dinv + 2 * NB + (warp > 0 ? warp - 1 : 0) * (NB * LDT + NB * 12);   // Xs[c * LDT + i]
-  double* Ts = Xs + NB * LDT;                                                       // Ts[c * 12 + ii]
-  const bool probe = E.dbg && p == 1 && task == 0 && c == E.dbg_clique;
-  long long tq0 = 0, tq1 = 0, tq2 = 0, tq3 = 0, tq4 = 0, tq5 = 0;
-  if (probe) tq0 = clock64();
+  double* Ps = sm;                    // Ps[i * LDP + k] = R[k0-64+k, k0+i]           (panel p-1, columns of D)
+  double* Ds = Ps + PW * LDP;         // Ds[i * LDP + l] = D(l, i), l <= i            (column i of the block)
+  double* Ws = Ds + PW * LDP;         // Ws[i * 12 + r] = inv(D_bb)(r, i % 8), b = i / 8
+  double* dinv = Ws + PW * 12;        // 1 / D(i, i)
+  int* s_ok = reinterpret_cast<int*>(dinv + PW);
+  double* T0 = dinv + PW + 2;         // warp 0's scratch for the solve of the off-diagonal block
+  double* Xs = sm + kRoleAWarp0 + (warp > 0 ? warp - 1 : 0) * kRoleAColWarp;   // Xs[c * LDP + i]
+  double* Ts = Xs + CWID * LDP;                                                 // Ts[c * 12 + ii]
   // column warps: issue every global load of the slice up front (fragment layout), they overlap the diagonal-block loads
-  const int jbase = rest0 + task * SLICE + (warp - 1) * 32;
+  const int jbase = rest0 + task * SLICE + (warp - 1) * CWID;
   const bool colwarp = warp > 0 && jbase < dim;
-  double qf[8][4], b0[4][4][2];
+  double qf[16], b0[8][2];
   if (colwarp) {
+    const int j = jbase + g;
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks)
+    for (int ks = 0; ks < 16; ++ks) qf[ks] = (p >= 1 && j < dim) ? A[(k0 - PW + ks * 4 + t) + (int64_t)j * ld] : 0.0;
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        const int j = jbase + nt * 8 + g;
-        qf[ks][nt] = (p >= 1 && j < dim) ? A[(k0 - NB + ks * 4 + t) + (int64_t)j * ld] : 0.0;
+    for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int i = mt * 8 + g, jj = jbase + 2 * t + e;
+        b0[mt][e] = (jj < dim && i < kb) ? A[(k0 + i) + (int64_t)jj * ld] : 0.0;
       }
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int i = mt * 8 + g, j = jbase + nt * 8 + 2 * t + e;
-          b0[mt][nt][e] = (j < dim && i < kb) ? A[(k0 + i) + (int64_t)j * ld] : 0.0;
-        }
   }
-  // diagonal block and the matching columns of panel p-1: one column (32 contiguous doubles) per warp instruction
-  for (int col = warp; col < NB; col += 8) {
-    Ps[col * LDT + lane] = (p >= 1 && col < kb) ? A[(k0 - NB + lane) + (int64_t)(k0 + col) * ld] : 0.0;
-    Ds[col * LDT + lane] = (lane <= col && col < kb) ? A[(k0 + lane) + (int64_t)(k0 + col) * ld] : ((lane == col) ? 1.0 : 0.0);
-    Ws[col * LDT + lane] = 0.0;
+  // diagonal block and the matching columns of panel p-1: one column (64 contiguous doubles) per two warp instructions
+  {
+    double vp[8][2], vd[8][2];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int col = warp + 8 * q;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int l = lane + 32 * h;
+        vp[q][h] = (p >= 1 && col < kb) ? A[(k0 - PW + l) + (int64_t)(k0 + col) * ld] : 0.0;
+        vd[q][h] = (l <= col && col < kb) ? A[(k0 + l) + (int64_t)(k0 + col) * ld] : ((l == col) ? 1.0 : 0.0);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int col = warp + 8 * q;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        Ps[col * LDP + lane + 32 * h] = vp[q][h];
+        Ds[col * LDP + lane + 32 * h] = vd[q][h];
+      }
+    }
   }
   __syncthreads();
-  // column warps: X = B - P^T Q (needs only panel p-1)
-  if (colwarp) {
-    double acc[4][4][2];
+  // look-ahead on the diagonal block, shared by the 8 warps: D -= P^T P on the 36 upper 8 x 8 tile pairs
+  if (p >= 1) {
+    double acc[5][2];
+    int pm[5], pn[5];
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
+    for (int q = 0; q < 5; ++q) {
+      acc[q][0] = acc[q][1] = 0.0;
+      // pair index -> (mt, nt), mt <= nt < 8, row-major over the upper triangle
+      int idx = warp + 8 * q, mt = 0;
+      while (mt < 7 && idx >= 8 - mt) { idx -= 8 - mt; ++mt; }   // (indices >= 36 are masked below)
+      pm[q] = mt;
+      pn[q] = mt + idx;
+    }
+#pragma unroll 4
+    for (int ks = 0; ks < PW; ks += 4) {
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
-    if (p >= 1) {
-#pragma unroll
-      for (int ks = 0; ks < 8; ++ks) {
-        double af[4];
-#pragma unroll
-        for (int mt = 0; mt < 4; ++mt) af[mt] = Ps[(mt * 8 + g) * LDT + ks * 4 + t];
-#pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-          for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], af[mt], qf[ks][nt]);
-      }
+      for (int q = 0; q < 5; ++q)
+        if (warp + 8 * q < 36)
+          dmma884(acc[q][0], acc[q][1], Ps[(pm[q] * 8 + g) * LDP + ks + t], Ps[(pn[q] * 8 + g) * LDP + ks + t]);
     }
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
+    for (int q = 0; q < 5; ++q)
+      if (warp + 8 * q < 36) {
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-          Xs[(nt * 8 + 2 * t + e) * LDT + mt * 8 + g] = b0[mt][nt][e] - acc[mt][nt][e];
-  }
-  if (probe) tq1 = clock64();
-  if (warp == 0) {
-    if (p >= 1) {
-      // look-ahead on the diagonal block: D -= P^T P (upper triangle; the lower one is never read)
-      double acc[4][4][2];
-#pragma unroll
-      for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
-#pragma unroll
-      for (int ks = 0; ks < NB; ks += 4) {
-        double af[4];
-#pragma unroll
-        for (int mt = 0; mt < 4; ++mt) af[mt] = Ps[(mt * 8 + g) * LDT + ks + t];
-#pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-          for (int nt = mt; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], af[mt], af[nt]);
-      }
-#pragma unroll
-      for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-        for (int nt = mt; nt < 4; ++nt)
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int i = mt * 8 + g, jj = nt * 8 + 2 * t + e;
-            if (i <= jj && jj < kb) Ds[jj * LDT + i] -= acc[mt][nt][e];
-          }
-      __syncwarp();
-    }
-    if (probe) tq2 = clock64();
-    // 32 x 32 Cholesky (upper) in registers: lane = column.  Rows >= kb are identity padding.
-    double d[NB];
-#pragma unroll
-    for (int i = 0; i < NB; ++i) d[i] = Ds[lane * LDT + i];
-    bool okw = true;
-    double myinv = 1.0;
-    // software-pipelined: the next pivot column is updated first so that its rsqrt overlaps the rest of the rank-1 update
-    double pk = __shfl_sync(0xffffffffu, d[0], 0);
-    double rinv = rsqrt(pk);
-#pragma unroll
-    for (int k = 0; k < NB; ++k) {
-      okw = okw && (pk > 0.0);               // Eigen LLT NumericalIssue (base/cholesky.cpp:126-128)
-      if (lane > k) d[k] *= rinv;
-      else if (lane == k) { d[k] = pk * rinv; myinv = rinv; }
-      const double ukl = d[k];
-      double pk_next = 1.0, rinv_next = 1.0;
-      if (k + 1 < NB) {
-        const double uki = __shfl_sync(0xffffffffu, d[k], k + 1);
-        if (k + 1 <= lane) d[k + 1] -= uki * ukl;
-        pk_next = __shfl_sync(0xffffffffu, d[k + 1], k + 1);
-        rinv_next = rsqrt(pk_next);
-      }
-#pragma unroll
-      for (int i = k + 2; i < NB; ++i) {
-        const double uki = __shfl_sync(0xffffffffu, d[k], i);
-        if (i <= lane) d[i] -= uki * ukl;
-      }
-      pk = pk_next;
-      rinv = rinv_next;
-    }
-#pragma unroll
-    for (int i = 0; i < NB; ++i)
-      if (i <= lane) Ds[lane * LDT + i] = d[i];
-    dinv[lane] = myinv;
-    if (lane == 0) *s_ok = okw ? 1 : 0;
-    __syncwarp();
-    // inverses of the four 8 x 8 diagonal blocks: lane = column, back-substitution within its block
-    {
-      const int b8 = lane & ~7, jj = lane & 7;
-      double w[8];
-#pragma unroll
-      for (int i = 7; i >= 0; --i) {
-        double sacc = 0.0;
-#pragma unroll
-        for (int k = i + 1; k < 8; ++k)
-          if (k <= jj) sacc += Ds[(b8 + k) * LDT + b8 + i] * w[k];
-        w[i] = (i == jj) ? myinv : ((i < jj) ? -sacc * dinv[b8 + i] : 0.0);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) Ws[lane * LDT + b8 + i] = w[i];
-    }
-    if (task == 0 && okw) {
-      double* db = dfac + p * NB * NB;
-#pragma unroll
-      for (int i = 0; i < NB; ++i) db[i * NB + lane] = (i <= lane) ? d[i] : 0.0;
-      if (k0 + kb == F) {   // last panel: exponent test (base/cholesky.cpp:146-158)
-        const double dlast = Ds[(kb - 1) * LDT + kb - 1];
-        const double dprev = (kb >= 2) ? Ds[(kb - 2) * LDT + kb - 2] : 1.0;
-        if (lane == 0) {
-          bool good;
-          if (F >= 2) {
-            const double r2 = (kb >= 2) ? dprev : dfac[(p - 1) * NB * NB + (NB - 1) * NB + (NB - 1)];
-            good = frexp_exp(r2) - frexp_exp(dlast) < 12;
-          } else {
-            good = frexp_exp(dlast) > -12;
-          }
-          if (!good) atomicMin(E.fail, c);
+        for (int e = 0; e < 2; ++e) {
+          const int i = pm[q] * 8 + g, jj = pn[q] * 8 + 2 * t + e;
+          if (i <= jj && jj < kb) Ds[jj * LDP + i] -= acc[q][e];
         }
       }
+    __syncthreads();
+  }
+  // column warps: X = B - P^T Q (needs only panel p-1), while warp 0 factors
+  if (colwarp) {
+    double acc[8][2];
+#pragma unroll
+    for (int mt = 0; mt < 8; ++mt) acc[mt][0] = acc[mt][1] = 0.0;
+    if (p >= 1) {
+#pragma unroll
+      for (int ks = 0; ks < 16; ++ks) {
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt) dmma884(acc[mt][0], acc[mt][1], Ps[(mt * 8 + g) * LDP + ks * 4 + t], qf[ks]);
+      }
     }
+#pragma unroll
+    for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) Xs[(2 * t + e) * LDP + mt * 8 + g] = b0[mt][e] - acc[mt][e];
+  }
+  if (warp == 0) {
+    bool okw = true;
+    const int nh = kb > NB ? 2 : 1;
+#pragma unroll 1
+    for (int h = 0; h < nh; ++h) {
+      okw = potrf32_warp(Ds + h * NB * LDP + h * NB, dinv + h * NB, Ws + h * NB * 12, lane);
+      if (!okw) break;
+      if (h == 0 && nh == 2) {
+        // off-diagonal block T = D00^-T D01 (columns 32..63, rows 0..31), then D11 -= T^T T on its 10 upper tile pairs
+        trsm_stages<4>(Ds, Ws, Ds + NB * LDP, T0, 0, 4, g, t);
+        double acc[10][2];
+#pragma unroll
+        for (int q = 0; q < 10; ++q) acc[q][0] = acc[q][1] = 0.0;
+#pragma unroll 2
+        for (int ks = 0; ks < NB; ks += 4) {
+          double f[4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) f[a] = Ds[(NB + a * 8 + g) * LDP + ks + t];
+          int q = 0;
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+            for (int nt = mt; nt < 4; ++nt, ++q) dmma884(acc[q][0], acc[q][1], f[mt], f[nt]);
+        }
+        int q = 0;
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+          for (int nt = mt; nt < 4; ++nt, ++q)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int i = mt * 8 + g, jj = nt * 8 + 2 * t + e;
+              if (i <= jj && NB + jj < kb) Ds[(NB + jj) * LDP + NB + i] -= acc[q][e];
+            }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) *s_ok = okw ? 1 : 0;
     if (task == 0 && !okw && lane == 0) atomicMin(E.fail, c);
   }
   __syncthreads();
-  if (probe) tq3 = clock64();
-  if (!*s_ok || !colwarp) return;
-  // blocked forward substitution Y = R11^-T X in four 8-row stages
-#pragma unroll
-  for (int bi = 0; bi < 4; ++bi) {
-    double acc[4][2];
-#pragma unroll
-    for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = 0.0;
-#pragma unroll
-    for (int ks = 0; ks < bi * 8; ks += 4) {
-      const double a = Ds[(bi * 8 + g) * LDT + ks + t];
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) dmma884(acc[nt][0], acc[nt][1], a, Xs[(nt * 8 + g) * LDT + ks + t]);
+  if (!*s_ok) return;
+  if (task == 0) {
+    // factored diagonal block -> side buffer (other CTAs of this launch still read the unfactored block from the front)
+    double* db = dfac + p * PW * PW;
+    for (int idx = tid; idx < PW * PW; idx += blockDim.x) {
+      const int i = idx / PW, j = idx - i * PW;
+      db[idx] = (i <= j) ? Ds[j * LDP + i] : 0.0;
     }
-#pragma unroll
-    for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int cc = nt * 8 + 2 * t + e;
-        Ts[cc * 12 + g] = Xs[cc * LDT + bi * 8 + g] - acc[nt][e];
+    if (k0 + kb == F && tid == 0) {   // last panel: exponent test (base/cholesky.cpp:146-158)
+      const double dlast = Ds[(kb - 1) * LDP + kb - 1];
+      bool good;
+      if (F >= 2) {
+        const double r2 = (kb >= 2) ? Ds[(kb - 2) * LDP + kb - 2] : dfac[(p - 1) * PW * PW + (PW - 1) * PW + (PW - 1)];
+        good = frexp_exp(r2) - frexp_exp(dlast) < 12;
+      } else {
+        good = frexp_exp(dlast) > -12;
       }
-    __syncwarp();
-    double y[4][2];
-#pragma unroll
-    for (int nt = 0; nt < 4; ++nt) y[nt][0] = y[nt][1] = 0.0;
-#pragma unroll
-    for (int ks = 0; ks < 8; ks += 4) {
-      const double a = Ws[(bi * 8 + g) * LDT + bi * 8 + ks + t];
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) dmma884(y[nt][0], y[nt][1], a, Ts[(nt * 8 + g) * 12 + ks + t]);
+      if (!good) atomicMin(E.fail, c);
     }
-#pragma unroll
-    for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) Xs[(nt * 8 + 2 * t + e) * LDT + bi * 8 + g] = y[nt][e];
-    __syncwarp();
   }
-  if (probe) tq4 = clock64();
-  for (int cc = 0; cc < 32; ++cc) {
+  if (!colwarp) return;
+  // blocked forward substitution Y = R^-T X in 8-row stages
+  trsm_stages<1>(Ds, Ws, Xs, Ts, 0, (kb + 7) / 8, g, t);
+  for (int cc = 0; cc < CWID; ++cc) {
     const int j = jbase + cc;
-    if (j < dim && lane < kb) A[(k0 + lane) + (int64_t)j * ld] = Xs[cc * LDT + lane];
-  }
-  if (probe && lane == 0 && warp == 1) {
-    tq5 = clock64();
-    E.dbg[0] = tq1 - tq0; E.dbg[1] = tq2 - tq1; E.dbg[2] = tq3 - tq2; E.dbg[3] = tq4 - tq3; E.dbg[4] = tq5 - tq4;
+    if (j < dim) {
+      if (lane < kb) A[(k0 + lane) + (int64_t)j * ld] = Xs[cc * LDP + lane];
+      if (lane + NB < kb) A[(k0 + lane + NB) + (int64_t)j * ld] = Xs[cc * LDP + lane + NB];
+    }
   }
 }
 

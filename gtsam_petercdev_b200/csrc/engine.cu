@@ -582,7 +582,7 @@ static double modelled_time(const Plan& p, const std::vector<int32_t>& owner, in
       smalls[k] += 1;
     } else {
       flops[k] += (double)p.F[c] * dim * dim;
-      steps[k] = std::max(steps[k], (double)((p.F[c] + NB - 1) / NB + 1));
+      steps[k] = std::max(steps[k], (double)((p.F[c] + PW - 1) / PW + 1));
     }
     if (owner[c] < 0) reduce_bytes += 8.0 * p.ld[c] * dim;
   }
@@ -694,19 +694,19 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
     }
     L.zero_blocks = std::min<int64_t>(L.zero_blocks, 64);
     if (L.n_large) {
-      const int max_np = (L.max_F + NB - 1) / NB;
+      const int max_np = (L.max_F + PW - 1) / PW;
       for (int sidx = 0; sidx <= max_np; ++sidx) {
         L.step_begin.push_back((int64_t)e->step_tasks_list.size());
         // role-A slices of every clique first (critical path), then the tile tasks
         for (int pass = 0; pass < 2; ++pass)
           for (int64_t q = L.large_begin; q < en; ++q) {
             const int32_t c = lc[q];
-            const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + NB - 1) / NB;
+            const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
             if (sidx > np_c) continue;
             const int n = step_tasks(F, dim, sidx);
             int nA = 0;
             if (sidx < np_c) {
-              const int k0 = sidx * NB, kb = std::min(NB, F - k0);
+              const int k0 = sidx * PW, kb = std::min(PW, F - k0);
               nA = (dim - k0 - kb + SLICE - 1) / SLICE;
             }
             const int lo = pass == 0 ? 0 : nA, hi = pass == 0 ? nA : n;
@@ -853,7 +853,7 @@ static void install_plan(Engine* e) {
     d.dfac_off = 0;
     if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
-      dfac_total += (int64_t)((p.F[c] + NB - 1) / NB) * NB * NB;
+      dfac_total += (int64_t)((p.F[c] + PW - 1) / PW) * PW * PW;
       need(dfac_total < INT32_MAX, "diagonal-block side buffer overflow");
     }
   }
@@ -877,7 +877,7 @@ static void install_plan(Engine* e) {
   e->d_step_tasks.upload(e->step_tasks_list, st);
   e->d_dbg.alloc(8);
   e->d_fail.alloc(1);
-  e->d_dfac.alloc((size_t)dfac_total + NB * NB);
+  e->d_dfac.alloc((size_t)dfac_total + PW * PW);
   e->d_arena.alloc((size_t)e->arena_doubles + 16);
   if (e->world > 1) e->d_delta_own.alloc((size_t)e->n_scalars + 2);
   CK(cudaStreamSynchronize(st));
