@@ -556,14 +556,16 @@ __device__ __noinline__ bool potrf32_warp(double* Dh, double* dinv_h, double* Ws
 // Blocked forward substitution Y = R^-T X on NT*8 columns held as X[c * LDP + i] (i = row), one warp, stages
 // [b_begin, b_end) of 8 rows each.  R is the upper factor in Ds (Ds[i * LDP + l] = R(l, i)); Ws holds the inverses of
 // its 8 x 8 diagonal blocks (Ws[i * 12 + r] = inv(R_bb)(r, i % 8)).  Rows of earlier stages must already be solved.
-template <int NT>
+template <int NT, int NSTAGE>
 __device__ __forceinline__ void trsm_stages(const double* __restrict__ Ds, const double* __restrict__ Ws, double* X,
-                                            double* Ts, int b_begin, int b_end, int g, int t) {
-#pragma unroll 1
-  for (int bi = b_begin; bi < b_end; ++bi) {
+                                            double* Ts, int b_end, int g, int t) {
+#pragma unroll
+  for (int bi = 0; bi < NSTAGE; ++bi) {
+    if (bi >= b_end) break;
     double acc[NT][2];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) acc[nt][0] = acc[nt][1] = 0.0;
+#pragma unroll
     for (int ks = 0; ks < bi * 8; ks += 4) {
       const double a = Ds[(bi * 8 + g) * LDP + ks + t];
 #pragma unroll
@@ -595,6 +597,22 @@ __device__ __forceinline__ void trsm_stages(const double* __restrict__ Ds, const
   }
 }
 
+// Factored diagonal block b: side buffer (column-major PW x PW) -> front.  Runs one launch after the block was factored,
+// when no CTA reads the unfactored block from the front any more.  256 threads, 16 independent copies each.
+__device__ __forceinline__ void copy_diag_block(double* __restrict__ A, int ld, int F, const double* __restrict__ dfac, int b,
+                                                int tid) {
+  const double* src = dfac + (int64_t)b * PW * PW;
+  double v[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) v[q] = src[tid + 256 * q];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) {
+    const int idx = tid + 256 * q, j = idx / PW, i = idx - j * PW;
+    const int gi = b * PW + i, gj = b * PW + j;
+    if (i <= j && gj < F) A[gi + (int64_t)gj * ld] = v[q];
+  }
+}
+
 __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTask* __restrict__ tasks, int p) {
   extern __shared__ __align__(16) double sm[];
   const StepTask me = tasks[blockIdx.x];   // compact list: role-A slices (the critical path) first, no empty CTAs
@@ -613,14 +631,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     int ty, tx;
     trapezoid_decode(task, nt, ty, tx);
     if (!(E.debug & 1)) tile_update(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
-    if (task == 0) {
-      // factored diagonal blocks: side buffer -> front (nothing in this launch reads them)
-      for (int idx = tid; idx < np * PW * PW; idx += blockDim.x) {
-        const int b = idx / (PW * PW), r = idx - b * PW * PW, i = r / PW, j = r - i * PW;
-        const int gi = b * PW + i, gj = b * PW + j;
-        if (i <= j && gj < F) A[gi + (int64_t)gj * ld] = dfac[idx];
-      }
-    }
+    if (task == 0) copy_diag_block(A, ld, F, dfac, np - 1, tid);   // the last one; earlier blocks moved one step after they were made
     return;
   }
   const int k0 = p * PW, kb = min(PW, F - k0), rest0 = k0 + kb;
@@ -650,6 +661,10 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
   double* T0 = dinv + PW + 2;         // warp 0's scratch for the solve of the off-diagonal block
   double* Xs = sm + kRoleAWarp0 + (warp > 0 ? warp - 1 : 0) * kRoleAColWarp;   // Xs[c * LDP + i]
   double* Ts = Xs + CWID * LDP;                                                 // Ts[c * 12 + ii]
+  const bool probe = E.dbg && p == 2 && task == 0 && c == E.dbg_clique && lane == 0;   // GTB_DEBUG=8: cycle stamps
+  auto stamp = [&](int k) { if (probe) E.dbg[k] = clock64(); };
+  if (warp == 0) stamp(0);
+  if (task == 0 && p >= 1) copy_diag_block(A, ld, F, dfac, p - 1, tid);
   // column warps: issue every global load of the slice up front (fragment layout), they overlap the diagonal-block loads
   const int jbase = rest0 + task * SLICE + (warp - 1) * CWID;
   const bool colwarp = warp > 0 && jbase < dim;
@@ -690,6 +705,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     }
   }
   __syncthreads();
+  if (warp == 0) stamp(1);
   // look-ahead on the diagonal block, shared by the 8 warps: D -= P^T P on the 36 upper 8 x 8 tile pairs
   if (p >= 1) {
     double acc[5][2];
@@ -721,6 +737,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
       }
     __syncthreads();
   }
+  if (warp == 0) stamp(2);
   // column warps: X = B - P^T Q (needs only panel p-1), while warp 0 factors
   if (colwarp) {
     double acc[8][2];
@@ -737,6 +754,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     for (int mt = 0; mt < 8; ++mt)
 #pragma unroll
       for (int e = 0; e < 2; ++e) Xs[(2 * t + e) * LDP + mt * 8 + g] = b0[mt][e] - acc[mt][e];
+    if (warp == 1) stamp(8);
   }
   if (warp == 0) {
     bool okw = true;
@@ -744,10 +762,11 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
 #pragma unroll 1
     for (int h = 0; h < nh; ++h) {
       okw = potrf32_warp(Ds + h * NB * LDP + h * NB, dinv + h * NB, Ws + h * NB * 12, lane);
+      stamp(3 + 2 * h);
       if (!okw) break;
       if (h == 0 && nh == 2) {
         // off-diagonal block T = D00^-T D01 (columns 32..63, rows 0..31), then D11 -= T^T T on its 10 upper tile pairs
-        trsm_stages<4>(Ds, Ws, Ds + NB * LDP, T0, 0, 4, g, t);
+        trsm_stages<4, 4>(Ds, Ws, Ds + NB * LDP, T0, 4, g, t);
         double acc[10][2];
 #pragma unroll
         for (int q = 0; q < 10; ++q) acc[q][0] = acc[q][1] = 0.0;
@@ -773,6 +792,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
               if (i <= jj && NB + jj < kb) Ds[(NB + jj) * LDP + NB + i] -= acc[q][e];
             }
         __syncwarp();
+        stamp(4);
       }
     }
     if (lane == 0) *s_ok = okw ? 1 : 0;
@@ -784,7 +804,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     // factored diagonal block -> side buffer (other CTAs of this launch still read the unfactored block from the front)
     double* db = dfac + p * PW * PW;
     for (int idx = tid; idx < PW * PW; idx += blockDim.x) {
-      const int i = idx / PW, j = idx - i * PW;
+      const int j = idx / PW, i = idx - j * PW;   // column-major
       db[idx] = (i <= j) ? Ds[j * LDP + i] : 0.0;
     }
     if (k0 + kb == F && tid == 0) {   // last panel: exponent test (base/cholesky.cpp:146-158)
@@ -800,8 +820,10 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     }
   }
   if (!colwarp) return;
+  if (warp == 1) stamp(9);
   // blocked forward substitution Y = R^-T X in 8-row stages
-  trsm_stages<1>(Ds, Ws, Xs, Ts, 0, (kb + 7) / 8, g, t);
+  trsm_stages<1, 8>(Ds, Ws, Xs, Ts, (kb + 7) / 8, g, t);
+  if (warp == 1) stamp(10);
   for (int cc = 0; cc < CWID; ++cc) {
     const int j = jbase + cc;
     if (j < dim) {
@@ -809,6 +831,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
       if (lane + NB < kb) A[(k0 + lane + NB) + (int64_t)j * ld] = Xs[cc * LDP + lane + NB];
     }
   }
+  if (warp == 1) stamp(11);
 }
 
 // ----------------------------------------------------------------------------------------------------
@@ -906,14 +929,27 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
     }
   }
   gsync();
-  // blocked back-substitution with R (upper triangular), bottom block first
+  // blocked back-substitution with R (upper triangular), bottom block first.  CTA variant: the next diagonal block is
+  // fetched into shared memory by the whole CTA while the current block's update runs, and every row issues its 32
+  // loads of the update before the first multiply (the loop is latency-bound: one SM streams R once).
+  double* dblk = xblk + 32;   // CTA only: dblk[k * 33 + l] = R(b0 + l, b0 + k)
+  if (!WARP) {
+    const int b0 = ((F - 1) / 32) * 32, kb = F - b0;
+    for (int q = gtid; q < 1024; q += gsize) {
+      const int k = q >> 5, l = q & 31;
+      dblk[k * 33 + l] = (k < kb && l <= k) ? A[(b0 + l) + (int64_t)(b0 + k) * ld] : 1.0;
+    }
+    __syncthreads();
+  }
   for (int b0 = ((F - 1) / 32) * 32; b0 >= 0; b0 -= 32) {
     const int kb = min(32, F - b0);
     if (WARP || warp == 0) {
       double r[32];
 #pragma unroll
-      for (int k = 0; k < 32; ++k)
-        r[k] = (k < kb && lane <= k && lane < kb) ? A[(b0 + lane) + (int64_t)(b0 + k) * ld] : 1.0;
+      for (int k = 0; k < 32; ++k) {
+        if (WARP) r[k] = (k < kb && lane <= k && lane < kb) ? A[(b0 + lane) + (int64_t)(b0 + k) * ld] : 1.0;
+        else r[k] = dblk[k * 33 + lane];
+      }
       double my = (lane < kb) ? rhs[b0 + lane] : 0.0;
       // reciprocal of this lane's diagonal entry: one division per lane instead of a chain of 32
       double dg = 1.0;
@@ -929,22 +965,39 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
           else if (lane < k) my -= r[k] * xk;
         }
       }
-      if (lane < kb) {
-        rhs[b0 + lane] = my;
-        if (!WARP) xblk[lane] = my;
-      }
+      if (lane < kb) rhs[b0 + lane] = my;
+      if (!WARP) xblk[lane] = (lane < kb) ? my : 0.0;
     }
     if (WARP) break;   // F <= 32: single block
     __syncthreads();
+    // next diagonal block (full: only the bottom block can be ragged)
+    double dn[2] = {1.0, 1.0};
+    if (b0 >= 32) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int q = gtid + h * gsize, k = q >> 5, l = q & 31;
+        if (q < 1024 && l <= k) dn[h] = A[(b0 - 32 + l) + (int64_t)(b0 - 32 + k) * ld];
+      }
+    }
     for (int i = gtid; i < b0; i += gsize) {
       const double* row = A + i + (int64_t)b0 * ld;
+      double v[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k) v[k] = (k < kb) ? row[(int64_t)k * ld] : 0.0;
       double a0 = 0.0, a1 = 0.0;
-#pragma unroll 8
+#pragma unroll
       for (int k = 0; k < 32; k += 2) {
-        if (k < kb) a0 += row[(int64_t)k * ld] * xblk[k];
-        if (k + 1 < kb) a1 += row[(int64_t)(k + 1) * ld] * xblk[k + 1];
+        a0 += v[k] * xblk[k];
+        a1 += v[k + 1] * xblk[k + 1];
       }
       rhs[i] -= a0 + a1;
+    }
+    if (b0 >= 32) {   // nobody reads dblk between the two barriers (warp 0 took its copy before the first one)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int q = gtid + h * gsize;
+        if (q < 1024) dblk[(q >> 5) * 33 + (q & 31)] = dn[h];
+      }
     }
     __syncthreads();
   }

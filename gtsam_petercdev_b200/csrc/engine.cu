@@ -752,7 +752,7 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       need(off < INT32_MAX, "back-substitution scratch overflow");
       e->bs_scratch_doubles = std::max(e->bs_scratch_doubles, off);
     }
-    L.bs_cta_smem = (maxN + 512 + 32) * (int32_t)sizeof(double);
+    L.bs_cta_smem = (maxN + 512 + 32 + 32 * 33) * (int32_t)sizeof(double);
 
     // re-sort the small part of the level by dimension and cut into thread classes
     auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
@@ -875,7 +875,7 @@ static void install_plan(Engine* e) {
   e->d_bs_scratch_off.upload(e->bs_scratch_off, st);
   e->d_bs_scratch.alloc((size_t)e->bs_scratch_doubles + 1);
   e->d_step_tasks.upload(e->step_tasks_list, st);
-  e->d_dbg.alloc(8);
+  e->d_dbg.alloc(16);
   e->d_fail.alloc(1);
   e->d_dfac.alloc((size_t)dfac_total + PW * PW);
   e->d_arena.alloc((size_t)e->arena_doubles + 16);
@@ -1672,7 +1672,7 @@ int64_t gtb_profile_read_raw(gtb_engine* e, int32_t* klass, float* ms, int64_t c
 void gtb_debug_read(gtb_engine* e, long long* out8) {
   if (!e || !e->has_device) return;
   cudaStreamSynchronize(e->stream);
-  cudaMemcpy(out8, e->d_dbg.p, 8 * sizeof(long long), cudaMemcpyDeviceToHost);
+  cudaMemcpy(out8, e->d_dbg.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost);
 }
 void* gtb_stream(gtb_engine* e) { return e ? (void*)e->stream : nullptr; }
 

@@ -31,7 +31,13 @@ print("front_step launches", len(fs), "sum", fs.sum(), "sorted top", np.sort(fs)
 
 import ctypes
 if os.environ.get("GTB_DEBUG") and int(os.environ["GTB_DEBUG"]) & 8:
-    buf = (ctypes.c_longlong * 8)()
+    buf = (ctypes.c_longlong * 16)()
     e.lib.gtb_debug_read.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     e.lib.gtb_debug_read(e.h, buf)
-    print("role A cycles (root, p=1, slice 0): load D/P %d, PtP %d, potrf %d, dfac+update %d, trsm+store %d" % tuple(buf[:5]))
+    b = list(buf)
+    names = {1: "loads + sync", 2: "D -= PtP + sync", 3: "potrf 0 + inverses", 4: "T solve + D11 update", 5: "potrf 1 + inverses"}
+    print("role A cycle stamps (root, p=2, slice 0), warp 0:")
+    for k in range(1, 6):
+        print("  %-24s %7d" % (names[k], b[k] - b[k - 1]))
+    print("column warp 1: X update done at %d, released at %d, solve %d, store %d (cycles from kernel start)" % (
+        b[8] - b[0], b[9] - b[0], b[10] - b[9], b[11] - b[10]))
