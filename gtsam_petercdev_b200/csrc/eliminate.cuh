@@ -845,7 +845,7 @@ constexpr int kBsWarpDoubles = 32 + 160 + 32;   // rhs, xs, reduction scratch pe
 // S x_S for CTA-class cliques, spread over many CTAs: blockIdx.x = clique slot, y = 128-row block, z = 128-column
 // chunk.  Partial sums go to scratch[off + chunk * F + i]; backsolve_kernel<false> adds them in chunk order
 // (deterministic, no atomics).
-constexpr int kGemvRows = 128, kGemvCols = 128;
+constexpr int kGemvRows = 128, kGemvCols = 32;
 __global__ void __launch_bounds__(kGemvRows)
 backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t* __restrict__ scratch_off,
                       const double* __restrict__ delta, double* __restrict__ scratch) {
@@ -863,19 +863,26 @@ backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t
   const double* row = E.arena + ci.front_off + i + (int64_t)(F + j0) * ld;
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
   int j = 0;
-  for (; j + 16 <= nj; j += 16) {   // 16 independent loads in flight per thread
-    double v[16];
+  for (; j + 32 <= nj; j += 32) {   // 32 independent loads in flight per thread: the kernel is latency-bound
+    double v[32];
 #pragma unroll
-    for (int u = 0; u < 16; ++u) v[u] = row[(int64_t)(j + u) * ld];
+    for (int u = 0; u < 32; ++u) v[u] = row[(int64_t)(j + u) * ld];
 #pragma unroll
-    for (int u = 0; u < 16; u += 4) {
+    for (int u = 0; u < 32; u += 4) {
       a0 += v[u] * xs[j + u];
       a1 += v[u + 1] * xs[j + u + 1];
       a2 += v[u + 2] * xs[j + u + 2];
       a3 += v[u + 3] * xs[j + u + 3];
     }
   }
-  for (; j < nj; ++j) a0 += row[(int64_t)j * ld] * xs[j];
+  if (j < nj) {
+    double v[32];
+#pragma unroll
+    for (int u = 0; u < 32; ++u) v[u] = (j + u < nj) ? row[(int64_t)(j + u) * ld] : 0.0;
+#pragma unroll
+    for (int u = 0; u < 32; ++u)
+      if (j + u < nj) a0 += v[u] * xs[j + u];
+  }
   scratch[scratch_off[blockIdx.x] + (int64_t)blockIdx.z * F + i] = (a0 + a1) + (a2 + a3);
 }
 
