@@ -263,7 +263,8 @@ def main():
         hbm, peak_src = 6650.0, "fallback"
     # algorithmic work per step of each candidate class
     work = {
-        "front_step": ("tensor", st["flops_large"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
+        "front_step": ("tensor", (st["flops_large"] - st["flops_syrk_schur"]) / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
+        "schur_step": ("tensor", st["flops_syrk_schur"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
         "small_front": ("hbm", (st["bytes_small"] - st["bytes_thin"]) / 1e9, hbm, "GB/s"),
         "thin_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
         "linearize": ("hbm", st["bytes_linearize"] / 1e9, hbm, "GB/s"),

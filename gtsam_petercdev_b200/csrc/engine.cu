@@ -82,8 +82,10 @@ struct LevelSched {
   int32_t n_bs_warp = 0, n_bs_cta = 0, bs_cta_smem = 0;
   int32_t bs_max_F = 0, bs_max_S = 0;   // CTA class: grid of the partial-GEMV kernel
   int64_t zero_blocks = 0;
-  std::vector<int64_t> step_begin;  // per panel step 0..max_np: range of the compact task list
+  std::vector<int64_t> step_begin;  // per panel step 0..max_np: range of the compact task list (panel-step tasks)
   std::vector<int32_t> step_count;
+  std::vector<int64_t> schur_begin; // per step: tile tasks of the cliques whose Schur-complement step this is
+  std::vector<int32_t> schur_count;
 };
 
 }  // namespace gtb
@@ -302,10 +304,10 @@ struct StageTimer {
 };
 
 // kernel classes for launch counting and optional per-launch event timing
-enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_ZERO, K_LFACT, K_LCHILD, K_STEP,
+enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
        K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
-                                          "small_front", "thin_front", "large_zero", "large_factors", "large_children", "front_step",
+                                          "small_front", "thin_front", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
                                           "backsolve", "backsolve_gemv", "retract", "own_delta"};
 
 static void prof_begin(Engine* e, int k) {
@@ -702,17 +704,23 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
           for (int64_t q = L.large_begin; q < en; ++q) {
             const int32_t c = lc[q];
             const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
-            if (sidx > np_c) continue;
+            if (sidx >= np_c) continue;
             const int n = step_tasks(F, dim, sidx);
-            int nA = 0;
-            if (sidx < np_c) {
-              const int k0 = sidx * PW, kb = std::min(PW, F - k0);
-              nA = (dim - k0 - kb + SLICE - 1) / SLICE;
-            }
+            const int k0 = sidx * PW, kb = std::min(PW, F - k0);
+            const int nA = (dim - k0 - kb + SLICE - 1) / SLICE;
             const int lo = pass == 0 ? 0 : nA, hi = pass == 0 ? nA : n;
             for (int t = lo; t < hi; ++t) e->step_tasks_list.push_back(StepTask{c, t});
           }
         L.step_count.push_back((int32_t)(e->step_tasks_list.size() - L.step_begin.back()));
+        L.schur_begin.push_back((int64_t)e->step_tasks_list.size());
+        for (int64_t q = L.large_begin; q < en; ++q) {
+          const int32_t c = lc[q];
+          const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
+          if (sidx != np_c) continue;
+          const int n = step_tasks(F, dim, sidx);
+          for (int t = 0; t < n; ++t) e->step_tasks_list.push_back(StepTask{c, t});
+        }
+        L.schur_count.push_back((int32_t)(e->step_tasks_list.size() - L.schur_begin.back()));
       }
     }
     // extend-add work of this level's large parents.  Phase 1 only adds the children that are top cliques themselves:
@@ -1032,9 +1040,12 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
     if (L.n_work) {
       LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
     }
-    for (size_t s = 0; s < L.step_count.size(); ++s)
+    for (size_t s = 0; s < L.step_count.size(); ++s) {
       if (L.step_count[s] > 0)
         LAUNCH(e, K_STEP, front_step_kernel<<<L.step_count[s], 256, kStepSmem, st>>>(E, e->d_step_tasks.p + L.step_begin[s], (int)s));
+      if (L.schur_count[s] > 0)
+        LAUNCH(e, K_SCHUR, schur_step_kernel<<<L.schur_count[s], 256, kStepSmemTile, st>>>(E, e->d_step_tasks.p + L.schur_begin[s]));
+    }
   }
 }
 
@@ -1066,6 +1077,7 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     CK(cudaFuncSetAttribute(thin_front_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(thin_front_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(front_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem));
+    CK(cudaFuncSetAttribute(schur_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmemTile));
     CK(cudaFuncSetAttribute(backsolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr = true;
   }
