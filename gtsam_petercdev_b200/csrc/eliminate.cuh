@@ -43,7 +43,7 @@ struct ElimDev {
   const double* damp;   // per global scalar, or nullptr
   int32_t* fail;        // min failing clique id, initialised to INT_MAX
   long long* dbg;       // optional cycle probe of role A (GTB_DEBUG & 8)
-  int32_t dbg_clique;
+  int32_t dbg_clique, dbg_child;
   int32_t debug;        // experiment switches (GTB_DEBUG env): 1 skip tile tasks, 2 skip role-A column work, 4 skip role A
 };
 
@@ -381,7 +381,7 @@ constexpr int LDT = NB + 4;  // shared leading dimension of a K x 64 operand til
 constexpr int LDP = PW + 4;  // shared leading dimension of the role-A operands (68: conflict-free for the DMMA fragments)
 constexpr int CWID = 8;      // columns per role-A column warp (one DMMA n-tile)
 constexpr int SLICE = 7 * CWID;   // columns per role-A CTA: warp 0 factors the diagonal block, warps 1..7 own 8 columns each
-constexpr int kStepSmemTile = 4 * TW * LDT * (int)sizeof(double);                       // two double-buffered operand tiles
+constexpr int kStepSmemTile = 2 * 3 * TW * LDT * (int)sizeof(double);                   // two operands, 3-deep ring of K-chunks
 // role A: Ps, Ds, Ws (8 x 8 inverses), dinv, flag, warp 0's scratch, then Xs + Ts per column warp
 constexpr int kRoleAWarp0 = 2 * PW * LDP + PW * 12 + PW + 2 + NB * 12;
 constexpr int kRoleAColWarp = CWID * LDP + CWID * 12;
@@ -395,13 +395,24 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                : "d"(a), "d"(b));
 }
 
+// 16-byte asynchronous global -> shared copy; bytes beyond src_bytes are zero-filled (src_bytes = 0, 8 or 16)
+__device__ __forceinline__ void cp_async16(double* smem_dst, const double* gsrc, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 // C[i, j] -= sum_{k in [ka, kend)} R[k, i] * R[k, j] for the 64 x 64 tile at (r0, c0), rows < re, upper triangle.
-// 256 threads = 8 warps as 2 (rows) x 4 (cols); each warp owns 32 x 16 = 4 x 2 DMMA tiles.  Operands are staged
-// through double-buffered shared memory in K-chunks of 32 (global loads of chunk n+1 overlap the DMMAs of chunk n).
+// 256 threads = 8 warps as 2 (rows) x 4 (cols); each warp owns 32 x 16 = 4 x 2 DMMA tiles.  Operands are staged through
+// a kStages-deep ring of shared-memory K-chunks of 32 filled with cp.async (two chunks in flight behind the one being
+// multiplied: a lone CTA on an SM otherwise waits on L2/HBM every chunk).  ka and the front's leading dimension are
+// even, so every 16-byte copy is aligned; ragged edges are zero-filled by the copy itself.
+constexpr int kStages = 3;
 __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int dim, int r0, int c0, int re, int ka,
                                             int kend, double* sm) {
-  double* Xs = sm;                 // [2][TW * LDT]
-  double* Ys = sm + 2 * TW * LDT;  // [2][TW * LDT]
+  double* Xs = sm;                        // [kStages][TW * LDT]
+  double* Ys = sm + kStages * TW * LDT;   // [kStages][TW * LDT]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int wr = warp >> 2, wc = warp & 3;
   const int g = lane >> 2, t = lane & 3;
@@ -410,35 +421,33 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
   for (int a = 0; a < 4; ++a)
 #pragma unroll
     for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-  const int lc0 = tid >> 5;   // first of 8 operand columns (stride 8); lane = k within the chunk
-  double xr[8], yr[8];
-  auto fetch = [&](int kc) {
-    const int kn = min(NB, kend - kc);
+  // copy assignment: thread -> (column lcol = tid / 16 + 16 q, k pair kp = tid % 16), q = 0..3
+  const int kp = (tid & 15) * 2, lc0 = tid >> 4;
+  auto fetch = [&](int kc, int buf) {
+    const int kn = kend - kc - kp;   // valid k from this pair on
+    const int nb = kn >= 2 ? 16 : (kn == 1 ? 8 : 0);
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      const int lcol = lc0 + 8 * q;
+    for (int q = 0; q < 4; ++q) {
+      const int lcol = lc0 + 16 * q;
       const int xi = r0 + lcol, yj = c0 + lcol;
-      xr[q] = (xi < dim && lane < kn) ? A[kc + lane + (int64_t)xi * ld] : 0.0;
-      yr[q] = (yj < dim && lane < kn) ? A[kc + lane + (int64_t)yj * ld] : 0.0;
+      // out-of-range columns read the front's first column with size 0: pure zero fill, no access
+      cp_async16(Xs + buf * TW * LDT + lcol * LDT + kp, A + kc + kp + (int64_t)(xi < dim ? xi : 0) * ld, xi < dim ? nb : 0);
+      cp_async16(Ys + buf * TW * LDT + lcol * LDT + kp, A + kc + kp + (int64_t)(yj < dim ? yj : 0) * ld, yj < dim ? nb : 0);
     }
   };
-  auto stash = [&](int buf) {
+  const int nchunk = (kend - ka + NB - 1) / NB;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      const int lcol = lc0 + 8 * q;
-      Xs[buf * TW * LDT + lcol * LDT + lane] = xr[q];
-      Ys[buf * TW * LDT + lcol * LDT + lane] = yr[q];
-    }
-  };
-  fetch(ka);
-  stash(0);
-  __syncthreads();
-  int buf = 0;
-  for (int kc = ka; kc < kend; kc += NB) {
-    const bool more = kc + NB < kend;
-    if (more) fetch(kc + NB);
-    const double* X = Xs + buf * TW * LDT;
-    const double* Y = Ys + buf * TW * LDT;
+  for (int s = 0; s < kStages - 1; ++s) {
+    if (s < nchunk) fetch(ka + s * NB, s);
+    cp_async_commit();
+  }
+  for (int ch = 0; ch < nchunk; ++ch) {
+    cp_async_wait<kStages - 2>();   // chunk ch has landed (for this thread's copies)
+    __syncthreads();                // ... and for everybody's; also: everybody is done with the buffer refilled below
+    if (ch + kStages - 1 < nchunk) fetch(ka + (ch + kStages - 1) * NB, (ch + kStages - 1) % kStages);
+    cp_async_commit();
+    const double* X = Xs + (ch % kStages) * TW * LDT;
+    const double* Y = Ys + (ch % kStages) * TW * LDT;
 #pragma unroll
     for (int ks = 0; ks < NB; ks += 4) {
       double af[4], bf[2];
@@ -451,10 +460,8 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
 #pragma unroll
         for (int b = 0; b < 2; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
     }
-    if (more) stash(buf ^ 1);
-    __syncthreads();
-    buf ^= 1;
   }
+  cp_async_wait<0>();
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
@@ -837,7 +844,18 @@ __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const Ste
   const int nt = (dim - F + TW - 1) / TW;
   int ty, tx;
   trapezoid_decode(me.task, nt, ty, tx);
-  if (!(E.debug & 1)) tile_update(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
+  const bool probe = E.dbg && me.clique == E.dbg_child && threadIdx.x == 0 && (me.task == 0 || me.task == 77);
+  long long t0 = 0, g0 = 0;
+  if (probe) { t0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g0)); }
+  // a root's trailing block is the 1 x 1 constant term: nothing reads it
+  if (!(E.debug & 1) && ci.parent >= 0) tile_update(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
+  if (probe) {
+    long long g1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g1));
+    const int o = me.task == 0 ? 12 : 14;
+    E.dbg[o] = clock64() - t0;
+    E.dbg[o + 1] = g1 - g0;
+  }
   if (me.task == 0) copy_diag_block(A, ld, F, E.dfac + ci.dfac_off, (F + PW - 1) / PW - 1, threadIdx.x);
 }
 

@@ -1005,6 +1005,13 @@ static ElimDev elim_dev(Engine* e, bool damp) {
   E.debug = dbg;
   E.dbg = (dbg & 8) ? e->d_dbg.p : nullptr;
   E.dbg_clique = e->plan.n_cliques - 1;   // the root
+  E.dbg_child = -1;                       // its widest child (Schur-step probe)
+  if (E.dbg) {
+    const Plan& p = e->plan;
+    const int32_t r = p.n_cliques - 1;
+    for (int64_t k = p.child_off[r]; k < p.child_off[r + 1]; ++k)
+      if (E.dbg_child < 0 || p.S[p.children[k]] > p.S[E.dbg_child]) E.dbg_child = p.children[k];
+  }
   return E;
 }
 

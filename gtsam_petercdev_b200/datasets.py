@@ -269,3 +269,35 @@ def ladybug_shape(seed=1723):
 
 def venice_shape(seed=1778):
     return ba_shape(1778, 993000, 5.03, seed=seed)
+
+
+def read_bal(path):
+    """Bundle Adjustment in the Large file -> Problem, following SfmData::FromBalFile (sfm/SfmData.cpp:189-247) and the
+    graph of tests/testGeneralSFMFactorB.cpp:44-58: every number is read as a 32-bit float, v is negated, the OpenGL
+    camera (R, t) becomes wRc = R^T diag(1,-1,-1), wtc = -R^T t (openGL2gtsam, sfm/SfmData.cpp:79-86), cameras get the
+    plain keys 0..n-1 and points the keys P(j), measurements get Unit noise, no priors."""
+    tok = open(path).read().split()
+    n_cams, n_points, n_obs = int(tok[0]), int(tok[1]), int(tok[2])
+    f32 = lambda a: np.array(a, dtype=np.float32).astype(np.float64)   # noqa: E731
+    pos = 3
+    obs = np.array(tok[pos:pos + 4 * n_obs]).reshape(n_obs, 4)
+    pos += 4 * n_obs
+    cam_idx, pt_idx = obs[:, 0].astype(np.int64), obs[:, 1].astype(np.int64)
+    uv = np.stack([f32(obs[:, 2]), -f32(obs[:, 3])], axis=1)
+    cam = f32(tok[pos:pos + 9 * n_cams]).reshape(n_cams, 9)
+    pos += 9 * n_cams
+    pts = f32(tok[pos:pos + 3 * n_points]).reshape(n_points, 3)
+    R = _rodrigues(cam[:, 0:3])
+    wRc = np.transpose(R, (0, 2, 1)) @ np.diag([1.0, -1.0, -1.0])
+    wtc = -np.einsum("nji,nj->ni", R, cam[:, 3:6])
+    cal = np.concatenate([cam[:, 6:9], np.zeros((n_cams, 2))], axis=1)
+    cams = np.concatenate([wRc.reshape(n_cams, 9), wtc, cal], axis=1)
+    # the reference iterates tracks (points) and, inside, their measurements in file order
+    o = np.argsort(pt_idx, kind="stable")
+    ckeys = np.arange(n_cams, dtype=np.uint64)
+    pkeys = symbol("p", np.arange(n_points))
+    p = Problem()
+    p.set_variables("cam", ckeys, cams)
+    p.set_variables("point", pkeys, pts)
+    p.set_factors("sfm", np.stack([ckeys[cam_idx[o]], pkeys[pt_idx[o]]], axis=1), uv[o], 1, np.array([[1.0]]))
+    return p

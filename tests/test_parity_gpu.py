@@ -136,3 +136,18 @@ def test_indeterminate_system_reports_the_reference_key():
     e.factorize(1e-3)
     e.backsolve()
     assert np.all(np.isfinite(e.delta()))
+
+
+def test_bal_known_answer():
+    """The reference's own end-to-end test (tests/testGeneralSFMFactorB.cpp:44-63): BAL dubrovnik-3-7-pre, default LM,
+    final graph error 0.0199833 within 1e-5.  The problem arrays come from the fixture (parsed here by
+    datasets.read_bal, solved there by the unmodified reference)."""
+    from gtsam_petercdev_b200.problem import Problem
+    g = load_golden("bal_dubrovnik_3_7__lm_colamd")
+    p = Problem({k[len("problem_"):]: g[k] for k in g if k.startswith("problem_")})
+    e = Engine(p, device=0)
+    e.set_ordering(g["ordering"])
+    r = e.lm_optimize()
+    assert abs(r["final_error"] - 0.0199833) < 1e-5
+    assert abs(r["final_error"] - g["final_error"][0]) <= 1e-6 * g["final_error"][0]
+    assert r["iterations"] == int(g["iterations"][0])

@@ -41,3 +41,4 @@ if os.environ.get("GTB_DEBUG") and int(os.environ["GTB_DEBUG"]) & 8:
         print("  %-24s %7d" % (names[k], b[k] - b[k - 1]))
     print("column warp 1: X update done at %d, released at %d, solve %d, store %d (cycles from kernel start)" % (
         b[8] - b[0], b[9] - b[0], b[10] - b[9], b[11] - b[10]))
+    print("schur step of the root's last child: tile 0 %d cycles (%d ns), tile 77 %d cycles (%d ns)" % (b[12], b[13], b[14], b[15]))
