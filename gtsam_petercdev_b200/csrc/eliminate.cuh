@@ -508,33 +508,35 @@ struct StepTask { int32_t clique; int32_t task; };
 // lane = column; rows / columns beyond the front are identity padding.  Also leaves 1 / R(i, i) in dinv_h and the inverses
 // of the four 8 x 8 diagonal blocks in Ws_h[i * 12 + r].  Returns false on a non-positive pivot (Eigen LLT
 // NumericalIssue, base/cholesky.cpp:126-128).  Not inlined: the unrolled body is ~4.5k instructions and is used twice.
-__device__ __noinline__ bool potrf32_warp(double* Dh, double* dinv_h, double* Ws_h, int lane) {
+__device__ __noinline__ bool potrf32_warp(double* Dh, double* dinv_h, double* Ws_h, double* rowbuf, int lane) {
   bool okw = true;
   double d[NB];
 #pragma unroll
   for (int i = 0; i < NB; ++i) d[i] = Dh[lane * LDP + i];
   double myinv = 1.0;
-  // software-pipelined: the next pivot column is updated first so that its rsqrt overlaps the rest of the rank-1 update
+  // software-pipelined: the next pivot column is updated first so that its rsqrt overlaps the rest of the rank-1 update.
+  // No predication on the triangle: entries below the diagonal of a column (i > lane) and rows above the pivot hold
+  // garbage that is never read, which removes ~500 compare instructions from a body that is instruction-fetch-bound.
+  // The scaled pivot row is broadcast through shared memory (one LDS per use instead of two shuffles), double-buffered.
   double pk = __shfl_sync(0xffffffffu, d[0], 0);
   double rinv = rsqrt(pk);
 #pragma unroll
   for (int k = 0; k < NB; ++k) {
+    double* rb = rowbuf + (k & 1) * NB;
     okw = okw && (pk > 0.0);
-    if (lane > k) d[k] *= rinv;
-    else if (lane == k) { d[k] = pk * rinv; myinv = rinv; }
+    d[k] *= rinv;                       // lane == k: pk * rinv = sqrt(pk); lanes < k: unused
+    if (lane == k) myinv = rinv;
     const double ukl = d[k];
+    rb[lane] = ukl;
+    __syncwarp();
     double pk_next = 1.0, rinv_next = 1.0;
     if (k + 1 < NB) {
-      const double uki = __shfl_sync(0xffffffffu, d[k], k + 1);
-      if (k + 1 <= lane) d[k + 1] -= uki * ukl;
+      d[k + 1] -= rb[k + 1] * ukl;
       pk_next = __shfl_sync(0xffffffffu, d[k + 1], k + 1);
       rinv_next = rsqrt(pk_next);
     }
 #pragma unroll
-    for (int i = k + 2; i < NB; ++i) {
-      const double uki = __shfl_sync(0xffffffffu, d[k], i);
-      if (i <= lane) d[i] -= uki * ukl;
-    }
+    for (int i = k + 2; i < NB; ++i) d[i] -= rb[i] * ukl;
     pk = pk_next;
     rinv = rinv_next;
   }
@@ -642,6 +644,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     int ty, tx;
     trapezoid_decode(task, nct, ty, tx);
     if (!(E.debug & 1)) tile_update(A, ld, dim, rest0 + ty * TW, rest0 + tx * TW, F, k0 - PW, k0, sm);
+    if (task == 0) copy_diag_block(A, ld, F, dfac, p - 1, tid);   // off the critical path: tile CTAs finish early
     return;
   }
   // ---- role A: slice `task` of row panel p (64 pivots) ----
@@ -662,7 +665,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
   const bool probe = E.dbg && p == 2 && task == 0 && c == E.dbg_clique && lane == 0;   // GTB_DEBUG=8: cycle stamps
   auto stamp = [&](int k) { if (probe) E.dbg[k] = clock64(); };
   if (warp == 0) stamp(0);
-  if (task == 0 && p >= 1) copy_diag_block(A, ld, F, dfac, p - 1, tid);
+  if (task == 0 && p >= 1 && F - rest0 <= 0) copy_diag_block(A, ld, F, dfac, p - 1, tid);   // no tile task to do it
   // column warps: issue every global load of the slice up front (fragment layout), they overlap the diagonal-block loads
   const int jbase = rest0 + task * SLICE + (warp - 1) * CWID;
   const bool colwarp = warp > 0 && jbase < dim;
@@ -759,7 +762,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     const int nh = kb > NB ? 2 : 1;
 #pragma unroll 1
     for (int h = 0; h < nh; ++h) {
-      okw = potrf32_warp(Ds + h * NB * LDP + h * NB, dinv + h * NB, Ws + h * NB * 12, lane);
+      okw = potrf32_warp(Ds + h * NB * LDP + h * NB, dinv + h * NB, Ws + h * NB * 12, T0, lane);
       stamp(3 + 2 * h);
       if (!okw) break;
       if (h == 0 && nh == 2) {
