@@ -313,11 +313,36 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
   }
   gsync();
   double* dst = E.arena + ci.front_off;
+  // write-out.  Conditional rows [R S d] always go to the clique's own front (back-substitution reads them).  The Schur
+  // complement goes to the own front too when the parent assembles in shared memory; when the parent is a large front
+  // (already cleared and holding its own factors) it is added there directly, through the child -> parent column map.
+  bool fused = false;
+  double* pdst = nullptr;
+  int pld = 0;
+  int32_t* pm_s = reinterpret_cast<int32_t*>(stage);   // S + 1 <= 208 entries; the staging area is free
+  if (ci.parent >= 0) {
+    const CliqueDev cp = E.cliques[ci.parent];
+    fused = is_fused_child(F, dim, cp.F, cp.F + cp.S + 1);
+    if (fused) {
+      pdst = E.arena + cp.front_off;
+      pld = cp.ld;
+      gsync();   // rdiag (same storage) no longer needed
+      const int32_t* pm = E.pmap + ci.pmap_off;
+      for (int q = gtid; q <= ci.S; q += gsize) pm_s[q] = pm[q];
+      gsync();
+    }
+  }
   {
     int idx = gtid;
     int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
     for (; idx < plen; idx += gsize) {
-      dst[i + (int64_t)j * ci.ld] = P[idx];
+      if (i < F || !fused) {
+        dst[i + (int64_t)j * ci.ld] = P[idx];
+      } else {
+        int a = pm_s[i - F], b = pm_s[j - F];
+        if (a > b) { const int t = a; a = b; b = t; }
+        atomicAdd(pdst + a + (int64_t)b * pld, P[idx]);
+      }
       i += gsize;
       while (i > j) { i -= j + 1; ++j; }
     }

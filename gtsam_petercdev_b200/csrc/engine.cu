@@ -134,6 +134,8 @@ struct gtb_engine {
   std::vector<int32_t> owner;         // per clique: owning rank, or -1 for the top of the tree
   std::vector<int64_t> front_off;     // per clique: offset in this engine's arena (top fronts live in one tail region)
   std::vector<int32_t> top_list;
+  std::vector<int32_t> large_list;    // every large front this rank touches: its own (phase 0) first, then the top
+  int32_t n_large_own = 0;
   int64_t top_off = 0, top_doubles = 0, arena_doubles = 0, top_work_begin = 0, top_zero_blocks = 0;
   int32_t n_top_work = 0;
   std::vector<int32_t> bs_list, bs_scratch_off;
@@ -158,7 +160,7 @@ struct gtb_engine {
   DevBuf<SlotDev> d_slots;
   DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list, d_bs_scratch_off;
   DevBuf<double> d_bs_scratch, d_delta_own;
-  DevBuf<int32_t> d_top_list;
+  DevBuf<int32_t> d_top_list, d_large_list;
   DevBuf<uint8_t> d_own_mask;
   DevBuf<ChildWork> d_child_work;
   DevBuf<StepTask> d_step_tasks;
@@ -550,6 +552,9 @@ static void finalize_problem(Engine* e) {
 // ------------------------------------------------------------------------------------------------------
 // extend-add work items of one child: column chunks of roughly equal triangle area
 static void push_child_work(Engine* e, int32_t ch) {
+  const Plan& pp = e->plan;
+  const int32_t par = pp.parent[ch];
+  if (is_fused_child(pp.F[ch], pp.F[ch] + pp.S[ch] + 1, pp.F[par], pp.F[par] + pp.S[par] + 1)) return;   // added by the child itself
   const int32_t S1 = e->plan.S[ch] + 1;
   const int32_t nchunk = std::max(1, std::min(64, (int32_t)(((int64_t)S1 * S1 / 2) / 8192)));
   int32_t c0 = 0;
@@ -832,6 +837,11 @@ static void install_plan(Engine* e) {
       e->top_zero_blocks = std::max<int64_t>(e->top_zero_blocks, (sz / 2 + 255) / 256);
     }
   e->top_zero_blocks = std::min<int64_t>(e->top_zero_blocks, 64);
+  e->large_list.clear();
+  for (int32_t c = 0; c < C; ++c)
+    if (e->owner[c] == e->rank && !is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) e->large_list.push_back(c);
+  e->n_large_own = (int32_t)e->large_list.size();
+  e->large_list.insert(e->large_list.end(), e->top_list.begin(), e->top_list.end());
   e->top_doubles = tail - e->top_off;
   e->arena_doubles = e->top_list.empty() ? p.arena_doubles : tail;
   e->top_work_begin = (int64_t)e->child_work.size();
@@ -877,6 +887,7 @@ static void install_plan(Engine* e) {
   e->d_gidx.upload(p.gidx, st);
   e->d_level_cliques.upload(e->sched_lists, st);
   e->d_top_list.upload(e->top_list, st);
+  e->d_large_list.upload(e->large_list, st);
   e->d_own_mask.upload(own, st);
   e->d_child_work.upload(e->child_work, st);
   e->d_bs_list.upload(e->bs_list, st);
@@ -1039,11 +1050,6 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
         LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
     }
     if (!L.n_large) continue;
-    const int32_t* ll = lists + L.large_begin;
-    if (phase == 0) {
-      LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3((unsigned)L.zero_blocks, L.n_large), 256, 0, st>>>(E, ll));
-      LAUNCH(e, K_LFACT, large_factors_kernel<<<L.n_large, 256, 0, st>>>(E, ll));
-    }
     if (L.n_work) {
       LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
     }
@@ -1088,12 +1094,17 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     CK(cudaFuncSetAttribute(backsolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr = true;
   }
+  // every large front this rank touches is cleared and given its own factors first: thin children add their Schur
+  // complements into their parents as soon as they are eliminated.  The top of the tree is cleared on every rank but
+  // gets its factors (and damping) on rank 0 only: the fan-in sums the copies.
+  if (!e->large_list.empty()) {
+    const int nz = (int)e->large_list.size(), nf = e->rank == 0 ? nz : e->n_large_own;
+    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3(64, nz), 256, 0, st>>>(E, e->d_large_list.p));
+    if (nf) LAUNCH(e, K_LFACT, large_factors_kernel<<<nf, 256, 0, st>>>(E, e->d_large_list.p));
+  }
   factorize_levels(e, E, 0);
   if (!e->top_list.empty()) {
     // fan-in: every rank adds what it owns into its copy of the top fronts, the copies are summed onto rank 0
-    const int nt = (int)e->top_list.size();
-    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3((unsigned)e->top_zero_blocks, nt), 256, 0, st>>>(E, e->d_top_list.p));
-    if (e->rank == 0) LAUNCH(e, K_LFACT, large_factors_kernel<<<nt, 256, 0, st>>>(E, e->d_top_list.p));
     if (e->n_top_work)
       LAUNCH(e, K_LCHILD, large_children_kernel<<<e->n_top_work, 256, 0, st>>>(E, e->d_child_work.p + e->top_work_begin));
     comm(e, GTB_COMM_REDUCE_SUM_TO_0, e->d_arena.p + e->top_off, e->top_doubles);

@@ -68,9 +68,19 @@ struct Plan {
 //   thin  : few frontal scalars (a point or a pose), packed upper triangle in shared memory
 //   dense : any F, full square in shared memory
 // everything else is a "large" front that lives in global memory and is factored by the blocked panel kernels.
+#ifdef __CUDACC__
+#define GTB_HD __host__ __device__
+#else
+#define GTB_HD
+#endif
 constexpr int32_t kThinMaxF = 12, kThinMaxDim = 208, kDenseMaxDim = 128;
-inline bool is_thin_front(int32_t F, int32_t dim) { return F <= kThinMaxF && dim <= kThinMaxDim; }
-inline bool is_small_front(int32_t F, int32_t dim) { return dim <= kDenseMaxDim || is_thin_front(F, dim); }
+GTB_HD inline bool is_thin_front(int32_t F, int32_t dim) { return F <= kThinMaxF && dim <= kThinMaxDim; }
+GTB_HD inline bool is_small_front(int32_t F, int32_t dim) { return dim <= kDenseMaxDim || is_thin_front(F, dim); }
+// A thin front whose parent is a large front adds its Schur complement straight into the parent (atomics) when it is
+// eliminated and keeps only its conditional rows: nothing re-reads the child later.
+GTB_HD inline bool is_fused_child(int32_t F, int32_t dim, int32_t parent_F, int32_t parent_dim) {
+  return is_thin_front(F, dim) && !is_small_front(parent_F, parent_dim);
+}
 
 // Throws std::runtime_error with a message on inconsistent input.
 // small_max: fronts with F+S+1 <= small_max are handled by the shared-memory kernel.
