@@ -27,7 +27,10 @@ struct CliqueDev {
   int32_t pmap_off, gidx_off;
   int32_t first_key_var;  // variable id of the first frontal key (failure reporting)
   int32_t dfac_off;       // large fronts: offset of the factored diagonal blocks' side buffer (doubles)
+  int32_t flags;          // kCliqueStar: a point clique whose factors are SFM factors of distinct cameras
+  int32_t pad;
 };
+constexpr int32_t kCliqueStar = 1;
 
 struct SlotDev { int32_t col0, col1, bucket, index; };
 
@@ -164,6 +167,11 @@ __constant__ unsigned char c_pairB[91] = {
     8, 8, 8, 8, 8, 8, 8, 8, 8, 9, 9, 9, 9, 9, 9, 9, 9, 9, 9, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10, 10,
     11, 11, 11, 11, 11, 11, 11, 11, 11, 11, 11, 11, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12, 12};
 
+// SFM factor (W = 13: camera 0..8, point 9..11, rhs 12) column pairs a <= b: the first 81 involve the camera block (unique to
+// the factor inside a point clique), the last 10 only the point and the rhs (shared by all factors of the clique)
+__constant__ unsigned char c_starA[91] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 2, 2, 2, 2, 2, 2, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 4, 4, 4, 4, 4, 4, 4, 4, 4, 5, 5, 5, 5, 5, 5, 5, 5, 6, 6, 6, 6, 6, 6, 6, 7, 7, 7, 7, 7, 7, 8, 8, 8, 8, 8, 9, 9, 9, 9, 10, 10, 10, 11, 11, 12};
+__constant__ unsigned char c_starB[91] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 4, 5, 6, 7, 8, 9, 10, 11, 12, 5, 6, 7, 8, 9, 10, 11, 12, 6, 7, 8, 9, 10, 11, 12, 7, 8, 9, 10, 11, 12, 8, 9, 10, 11, 12, 9, 10, 11, 12, 10, 11, 12, 11, 12, 12};
+
 __device__ __forceinline__ int tri(int i, int j) { return ((j * (j + 1)) >> 1) + i; }   // i <= j
 
 constexpr int kThinStage = 416;   // doubles of factor rows staged per group and pass (16 SFM factors)
@@ -180,6 +188,9 @@ template <bool WARP>
 __global__ void __launch_bounds__(WARP ? kThinWarps * 32 : 128)
 thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int group_doubles) {
   extern __shared__ double sh[];
+  __shared__ unsigned char s_star[2 * 91];   // divergent indexing of a __constant__ table serialises: keep a copy here
+  for (int q = threadIdx.x; q < 91; q += blockDim.x) { s_star[q] = c_starA[q]; s_star[91 + q] = c_starB[q]; }
+  __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = WARP ? blockIdx.x * kThinWarps + warp : blockIdx.x;
   if (slot >= count) return;
@@ -193,9 +204,44 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
   const int F = ci.F, N = F + ci.S, dim = N + 1;
   const int plen = (dim * (dim + 1)) >> 1;
   for (int i = gtid; i < plen; i += gsize) P[i] = 0.0;
+  const int nfac = ci.fac_end - ci.fac_begin;
+  const bool star = (ci.flags & kCliqueStar) != 0;
+  if (star) {
+    // point clique: every factor is an SFM factor of a different camera, so the 81 column pairs that involve the camera
+    // block of a factor touch entries no other factor touches: all factors accumulate at once, no barrier in between.
+    // The 10 point / rhs pairs are shared: one thread each, factors in gather order (deterministic sums).
+    int* scol = reinterpret_cast<int*>(stage + nfac * 26);   // camera block column of each factor
+    gsync();
+    for (int t = gtid; t < nfac * 26; t += gsize) {
+      const int s = t / 26, r = t - s * 26;
+      const SlotDev sl = E.slots[ci.fac_begin + s];
+      stage[t] = E.Ab[2][(int64_t)sl.index * 26 + r];
+      if (r == 0) scol[s] = sl.col0;
+    }
+    gsync();
+    for (int t = gtid; t < nfac * 81; t += gsize) {
+      const int s = t / 81, q = t - s * 81;
+      const int a = s_star[q], b = s_star[91 + q];
+      const double* ab = stage + s * 26;
+      const double acc = ab[a] * ab[b] + ab[13 + a] * ab[13 + b];
+      const int i = scol[s] + a;
+      const int j = (b < 9) ? scol[s] + b : (b < 12 ? b - 9 : N);
+      P[(i <= j) ? tri(i, j) : tri(j, i)] += acc;
+    }
+    if (gtid < 10) {
+      const int a = s_star[81 + gtid], b = s_star[91 + 81 + gtid];
+      double acc = 0.0;
+      for (int s = 0; s < nfac; ++s) {
+        const double* ab = stage + s * 26;
+        acc += ab[a] * ab[b] + ab[13 + a] * ab[13 + b];
+      }
+      const int i = (a < 12) ? a - 9 : N, j = (b < 12) ? b - 9 : N;
+      P[tri(i, j)] += acc;
+    }
+  }
   // own factors, gather order.  The whitened rows of a batch of factors are staged into shared memory with one
   // round of global loads, then accumulated factor by factor (fixed order: deterministic sums).
-  for (int s0 = ci.fac_begin; s0 < ci.fac_end;) {
+  for (int s0 = star ? ci.fac_end : ci.fac_begin; s0 < ci.fac_end;) {
     int s1 = s0, used = 0;
     while (s1 < ci.fac_end) {
       const int b = E.slots[s1].bucket;
@@ -296,21 +342,6 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
     }
   }
   gsync();
-  // (3) C -= S^T S on the packed upper triangle, every element independent (:142); (i, j) advance incrementally
-  {
-    int idx = ((F * (F + 1)) >> 1) + gtid;
-    int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
-    for (; idx < plen; idx += gsize) {
-      if (i >= F) {
-        const int bi = (i * (i + 1)) >> 1, bj = (j * (j + 1)) >> 1;
-        double acc = 0.0;
-        for (int r = 0; r < F; ++r) acc += P[bi + r] * P[bj + r];
-        P[idx] -= acc;
-      }
-      i += gsize;
-      while (i > j) { i -= j + 1; ++j; }
-    }
-  }
   gsync();
   double* dst = E.arena + ci.front_off;
   // write-out.  Conditional rows [R S d] always go to the clique's own front (back-substitution reads them).  The Schur
@@ -336,12 +367,21 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
     int idx = gtid;
     int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
     for (; idx < plen; idx += gsize) {
+      // (3) C -= S^T S on the packed upper triangle, every element independent (base/cholesky.cpp:142), fused with the
+      // write-out: rows < F of P are final and nothing below them is read again
+      double v = P[idx];
+      if (i >= F) {
+        const int bi = (i * (i + 1)) >> 1, bj = (j * (j + 1)) >> 1;
+        double acc = 0.0;
+        for (int r = 0; r < F; ++r) acc += P[bi + r] * P[bj + r];
+        v -= acc;
+      }
       if (i < F || !fused) {
-        dst[i + (int64_t)j * ci.ld] = P[idx];
+        dst[i + (int64_t)j * ci.ld] = v;
       } else {
         int a = pm_s[i - F], b = pm_s[j - F];
         if (a > b) { const int t = a; a = b; b = t; }
-        atomicAdd(pdst + a + (int64_t)b * pld, P[idx]);
+        atomicAdd(pdst + a + (int64_t)b * pld, v);
       }
       i += gsize;
       while (i > j) { i -= j + 1; ++j; }

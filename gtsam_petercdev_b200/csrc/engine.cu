@@ -869,6 +869,19 @@ static void install_plan(Engine* e) {
     d.pmap_off = (int32_t)p.pmap_off[c]; d.gidx_off = (int32_t)p.gidx_off[c];
     d.first_key_var = p.vars[p.vars_off[c]];
     d.dfac_off = 0;
+    d.pad = 0;
+    // star: a point eliminated alone, all of its factors are SFM factors (bucket 2) of distinct cameras, at most 15
+    d.flags = 0;
+    {
+      const int64_t f0 = p.fac_off[c], f1 = p.fac_off[c + 1];
+      bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= 15 && is_thin_front(p.F[c], p.F[c] + p.S[c] + 1);
+      for (int64_t f = f0; star && f < f1; ++f) {
+        const FactorSlot& fs = p.slots[f];
+        star = e->g_bucket[fs.factor] == 2 && fs.col1 == 0 && fs.col0 >= 3;
+        for (int64_t g2 = f0; star && g2 < f; ++g2) star = p.slots[g2].col0 != fs.col0;
+      }
+      if (star) d.flags |= kCliqueStar;
+    }
     if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
       dfac_total += (int64_t)((p.F[c] + PW - 1) / PW) * PW * PW;
