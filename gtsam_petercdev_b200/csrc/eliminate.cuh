@@ -60,6 +60,12 @@ __device__ __forceinline__ int frexp_exp(double x) {
   return e;
 }
 
+// Programmatic dependent launch: the kernels of the level loop form one long dependent chain on one stream.  Each of
+// them lets its successor be scheduled as soon as all of its own CTAs have started (trigger), reads its static
+// schedule (task list, clique descriptors), and only then waits for the predecessor grid to finish and flush.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------------------------------
 // small fronts: one CTA per clique, the whole front lives in shared memory
 // ----------------------------------------------------------------------------------------------------
@@ -412,9 +418,11 @@ __global__ void __launch_bounds__(256) large_factors_kernel(ElimDev E, const int
 // extend-add of children into large parents: blockIdx.x = (child, column chunk) pair
 struct ChildWork { int32_t child; int32_t col_begin; int32_t col_end; int32_t pad; };
 __global__ void __launch_bounds__(256) large_children_kernel(ElimDev E, const ChildWork* __restrict__ work) {
+  pdl_trigger();
   const ChildWork w = work[blockIdx.x];
   const CliqueDev cc = E.cliques[w.child];
   const CliqueDev cp = E.cliques[cc.parent];
+  pdl_wait();
   const double* src = E.arena + cc.front_off;
   double* dst = E.arena + cp.front_off;
   const int32_t* pm = E.pmap + cc.pmap_off;
@@ -689,9 +697,11 @@ __device__ __forceinline__ void copy_diag_block(double* __restrict__ A, int ld, 
 
 __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTask* __restrict__ tasks, int p) {
   extern __shared__ __align__(16) double sm[];
+  pdl_trigger();
   const StepTask me = tasks[blockIdx.x];   // compact list: role-A slices (the critical path) first, no empty CTAs
   const int c = me.clique;
   const CliqueDev ci = E.cliques[c];
+  pdl_wait();
   const int F = ci.F, dim = F + ci.S + 1, ld = ci.ld;
   const int np = (F + PW - 1) / PW;
   double* A = E.arena + ci.front_off;
@@ -905,8 +915,10 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
 // CTA per SM by role A's registers: 70 % of the large-front flops of a bundle-adjustment tree are in these launches.
 __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const StepTask* __restrict__ tasks) {
   extern __shared__ __align__(16) double sm[];
+  pdl_trigger();
   const StepTask me = tasks[blockIdx.x];
   const CliqueDev ci = E.cliques[me.clique];
+  pdl_wait();
   const int F = ci.F, dim = F + ci.S + 1, ld = ci.ld;
   double* A = E.arena + ci.front_off;
   const int nt = (dim - F + TW - 1) / TW;
@@ -942,10 +954,12 @@ constexpr int kGemvRows = 128, kGemvCols = 32;
 __global__ void __launch_bounds__(kGemvRows)
 backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t* __restrict__ scratch_off,
                       const double* __restrict__ delta, double* __restrict__ scratch) {
+  pdl_trigger();
   const CliqueDev ci = E.cliques[list[blockIdx.x]];
   const int F = ci.F, S = ci.S, ld = ci.ld;
   const int i0 = blockIdx.y * kGemvRows, j0 = blockIdx.z * kGemvCols;
   if (i0 >= F || j0 >= S) return;
+  pdl_wait();
   __shared__ double xs[kGemvCols];
   const int nj = min(kGemvCols, S - j0);
   const int32_t* g = E.gidx + ci.gidx_off + F + j0;
@@ -989,7 +1003,9 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
   if (slot >= count) return;   // WARP: whole warp exits together; CTA: never true
   const int gsize = WARP ? 32 : (int)blockDim.x;
   const int gtid = WARP ? lane : (int)threadIdx.x;
+  pdl_trigger();
   const CliqueDev ci = E.cliques[list[slot]];
+  pdl_wait();
   const int F = ci.F, S = ci.S, N = F + S, ld = ci.ld;
   const double* A = E.arena + ci.front_off;
   const int32_t* g = E.gidx + ci.gidx_off;

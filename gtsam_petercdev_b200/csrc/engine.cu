@@ -336,6 +336,23 @@ static void check_launch(Engine* e, int k) {
     check_launch(e, k);     \
   } while (0)
 
+// Launch with programmatic stream serialization: the kernel may be scheduled before its predecessor on the stream has
+// finished; it calls pdl_wait() before touching anything the predecessor writes (eliminate.cuh).
+template <class... KArgs, class... Args>
+static void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  CK(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+}
+
 // ------------------------------------------------------------------------------------------------------
 // problem set-up
 // ------------------------------------------------------------------------------------------------------
@@ -1064,13 +1081,13 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
     }
     if (!L.n_large) continue;
     if (L.n_work) {
-      LAUNCH(e, K_LCHILD, large_children_kernel<<<L.n_work, 256, 0, st>>>(E, e->d_child_work.p + L.work_begin));
+      LAUNCH(e, K_LCHILD, launch_pdl(large_children_kernel, L.n_work, 256, 0, st, E, e->d_child_work.p + L.work_begin));
     }
     for (size_t s = 0; s < L.step_count.size(); ++s) {
       if (L.step_count[s] > 0)
-        LAUNCH(e, K_STEP, front_step_kernel<<<L.step_count[s], 256, kStepSmem, st>>>(E, e->d_step_tasks.p + L.step_begin[s], (int)s));
+        LAUNCH(e, K_STEP, launch_pdl(front_step_kernel, L.step_count[s], 256, kStepSmem, st, E, e->d_step_tasks.p + L.step_begin[s], (int)s));
       if (L.schur_count[s] > 0)
-        LAUNCH(e, K_SCHUR, schur_step_kernel<<<L.schur_count[s], 256, kStepSmemTile, st>>>(E, e->d_step_tasks.p + L.schur_begin[s]));
+        LAUNCH(e, K_SCHUR, launch_pdl(schur_step_kernel, L.schur_count[s], 256, kStepSmemTile, st, E, e->d_step_tasks.p + L.schur_begin[s]));
     }
   }
 }
@@ -1148,17 +1165,17 @@ static void backsolve_levels(Engine* e, const ElimDev& E, int phase) {
     const int32_t* bl = e->d_bs_list.p + L.bs_begin;
     const int32_t* so = e->d_bs_scratch_off.p + L.bs_begin;
     if (L.n_bs_warp)
-      LAUNCH(e, K_BACKSOLVE, backsolve_kernel<true><<<(L.n_bs_warp + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
-                                                      kBsWarps * kBsWarpDoubles * sizeof(double), e->stream>>>(
-                                 E, bl, L.n_bs_warp, e->d_delta.p, so, e->d_bs_scratch.p));
+      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<true>, (L.n_bs_warp + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
+                                        kBsWarps * kBsWarpDoubles * sizeof(double), e->stream, E, bl, L.n_bs_warp, e->d_delta.p,
+                                        so, (const double*)e->d_bs_scratch.p));
     if (L.n_bs_cta) {
       if (L.bs_max_S > 0)
-        LAUNCH(e, K_BSGEMV, backsolve_gemv_kernel<<<dim3(L.n_bs_cta, (L.bs_max_F + kGemvRows - 1) / kGemvRows,
-                                                         (L.bs_max_S + kGemvCols - 1) / kGemvCols),
-                                                    kGemvRows, 0, e->stream>>>(E, bl + L.n_bs_warp, so + L.n_bs_warp,
-                                                                               e->d_delta.p, e->d_bs_scratch.p));
-      LAUNCH(e, K_BACKSOLVE, backsolve_kernel<false><<<L.n_bs_cta, 512, L.bs_cta_smem, e->stream>>>(
-                                 E, bl + L.n_bs_warp, L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, e->d_bs_scratch.p));
+        LAUNCH(e, K_BSGEMV, launch_pdl(backsolve_gemv_kernel,
+                                       dim3(L.n_bs_cta, (L.bs_max_F + kGemvRows - 1) / kGemvRows, (L.bs_max_S + kGemvCols - 1) / kGemvCols),
+                                       kGemvRows, 0, e->stream, E, bl + L.n_bs_warp, so + L.n_bs_warp, (const double*)e->d_delta.p,
+                                       e->d_bs_scratch.p));
+      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<false>, L.n_bs_cta, 512, L.bs_cta_smem, e->stream, E, bl + L.n_bs_warp,
+                                        L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, (const double*)e->d_bs_scratch.p));
     }
   }
 }
