@@ -273,8 +273,15 @@ def main():
     dom = max((k for k in per_step if k in work), key=lambda k: per_step[k][0])
     bound, amount, peak, unit = work[dom]
     achieved = amount / (per_step[dom][0] / 1e3)
+    # DRAM bytes per launch of the dominant class, from the committed ncu pass over every launch of this same command
+    traffic, traffic_src = None, None
+    tf = os.path.join(ROOT, "profiles", "r01", "ncu_traffic_c3_metis.json")
+    if args.workload == "c3" and args.ordering == "metis" and os.path.exists(tf):
+        tj = json.load(open(tf))
+        if dom in tj:
+            traffic, traffic_src = tj[dom]["traffic_bytes_per_launch"], "profiles/r01/ncu_traffic_c3_metis.json (" + tj["_source"] + ")"
     roofline = {"kernel": dom, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "share_of_step": share[dom],
+                "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write)", "traffic_source": traffic_src, "peak_source": peak_src, "share_of_step": share[dom],
                 "launches_per_step": per_step[dom][1], "ms_per_step": per_step[dom][0],
                 "all_classes_ms_per_step": {k: round(v[0], 4) for k, v in sorted(per_step.items(), key=lambda kv: -kv[1][0])},
                 "other": {k: {"achieved": work[k][1] / (per_step[k][0] / 1e3), "unit": work[k][3], "frac": work[k][1] / (per_step[k][0] / 1e3) / work[k][2]}
