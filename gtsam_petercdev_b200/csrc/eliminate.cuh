@@ -403,10 +403,13 @@ __global__ void __launch_bounds__(256) large_zero_kernel(ElimDev E, const int32_
   const int c = list[blockIdx.y];
   const CliqueDev ci = E.cliques[c];
   const int dim = ci.F + ci.S + 1;
-  double2* A = reinterpret_cast<double2*>(E.arena + ci.front_off);
-  const int64_t total = ((int64_t)ci.ld * dim) >> 1;  // ld is a multiple of 4
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x)
-    A[i] = make_double2(0.0, 0.0);
+  // upper triangle only (nothing reads below the diagonal): column j, rows 0..j, as 16-byte stores (ld is a multiple of 4)
+  double* A = E.arena + ci.front_off;
+  for (int j = blockIdx.x; j < dim; j += gridDim.x) {
+    double2* col = reinterpret_cast<double2*>(A + (int64_t)j * ci.ld);
+    const int n2 = (j + 2) >> 1;
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) col[i] = make_double2(0.0, 0.0);
+  }
 }
 __global__ void __launch_bounds__(256) large_factors_kernel(ElimDev E, const int32_t* __restrict__ list) {
   const int c = list[blockIdx.x];
