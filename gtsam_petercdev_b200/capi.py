@@ -66,6 +66,7 @@ _SIGS = {
     "gtb_profile_read": (C.c_int, [_P, _P, _P]),
     "gtb_profile_read_raw": (C.c_int64, [_P, _P, _P, C.c_int64]),
     "gtb_stream": (_P, [_P]),
+    "gtb_set_robust": (C.c_int, [_P, C.c_int, C.c_int, C.c_double]),
     "gtb_set_distributed": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P]),
     "gtb_partition_get": (C.c_int, [_P, _P, _P]),
 }

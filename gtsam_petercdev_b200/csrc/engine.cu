@@ -108,6 +108,8 @@ struct gtb_engine {
     std::vector<int8_t> nk;      // resolved kinds
     std::vector<double> noise;   // n x m*m
     bool any_noise = false;
+    int32_t loss = 0;
+    double loss_k = 0;
   } fac[7];
   std::vector<int64_t> graph_order;
   bool finalized = false;
@@ -527,6 +529,7 @@ static void finalize_problem(Engine* e) {
     e->d_Ab[b].alloc((size_t)f.n * kM[b] * kW[b]);
     bk.n = (int32_t)f.n;
     bk.any_noise = f.any_noise ? 1 : 0;
+    bk.loss = f.loss; bk.pad = 0; bk.loss_k = f.loss_k;
     bk.row0 = e->d_row[b][0].p; bk.row1 = e->d_row[b][1].p;
     bk.goff0 = e->d_goff[b][0].p; bk.goff1 = e->d_goff[b][1].p;
     bk.z = e->d_z[b].p; bk.nk = e->d_nk[b].p; bk.noise = e->d_noise[b].p; bk.Ab = e->d_Ab[b].p;
@@ -1411,6 +1414,21 @@ gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, 
   if (keys)
     for (size_t i = 0; i < p.vars.size(); ++i) keys[i] = e->vkeys[p.vars[i]];
   return GTB_OK;
+}
+gtb_status gtb_set_robust(gtb_engine* e, int bucket, int loss, double k) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need(bucket >= 0 && bucket < 7, "bad factor bucket");
+  need(loss >= GTB_LOSS_NONE && loss <= GTB_LOSS_L2WITHDEADZONE, "unknown m-estimator");
+  // the reference's constructors reject a non-positive parameter (linear/LossFunctions.cpp:140-144, 173-177, ...)
+  need(loss == GTB_LOSS_NONE || k > 0, "m-estimator parameter must be positive");
+  e->fac[bucket].loss = loss;
+  e->fac[bucket].loss_k = k;
+  e->bk[bucket].loss = loss;
+  e->bk[bucket].loss_k = k;
+  e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+  e->lm_have_error = false;
+  GTB_CATCH(e)
 }
 gtb_status gtb_set_distributed(gtb_engine* e, int32_t rank, int32_t world, gtb_comm_fn fn, void* user) {
   if (!e) return GTB_ERR_INVALID;

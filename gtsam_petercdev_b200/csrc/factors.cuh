@@ -31,6 +31,9 @@ struct BucketDev {
   const int8_t* nk;          // resolved noise kind per factor
   const double* noise;       // n x d*d
   double* Ab;                // n x m x W, row-major per factor
+  int32_t loss;              // robust m-estimator of the whole bucket (0 = none), Block reweighting
+  int32_t pad;
+  double loss_k;
 };
 
 template <int B> struct BucketTraits;
@@ -225,6 +228,64 @@ __device__ inline P3 pose3_expmap(const double* xi) {
 // Gaussian: R * A (linear/NoiseModel.cpp:217-220); Diagonal: rows scaled by 1/sigma (:335-341);
 // Isotropic: everything scaled by 1/sigma (:662-674)
 // ----------------------------------------------------------------------------------------------------
+// Robust m-estimators of noiseModel::Robust with the default Block reweighting (linear/NoiseModel.cpp:709-737,
+// linear/LossFunctions.cpp:51-90): after whitening, A and b are scaled by sqrt(w(|b|)); the factor's error is rho(|b|).
+// w and rho as in linear/LossFunctions.cpp (Fair :146-155, Huber :179-192, Cauchy :217-224, Tukey :250-268,
+// Welsch :289-297, GemanMcClure :320-331, DCS :354-373, L2WithDeadZone :400-412).
+enum { LOSS_NONE = 0, LOSS_FAIR, LOSS_HUBER, LOSS_CAUCHY, LOSS_TUKEY, LOSS_WELSCH, LOSS_GEMANMCCLURE, LOSS_DCS, LOSS_L2DEADZONE };
+__device__ __forceinline__ double loss_weight(int kind, double k, double d) {
+  const double a = fabs(d);
+  switch (kind) {
+    case LOSS_FAIR: return 1.0 / (1.0 + a / k);
+    case LOSS_HUBER: return a <= k ? 1.0 : k / a;
+    case LOSS_CAUCHY: return (k * k) / (k * k + d * d);
+    case LOSS_TUKEY: {
+      if (a > k) return 0.0;
+      const double u = 1.0 - d * d / (k * k);
+      return u * u;
+    }
+    case LOSS_WELSCH: return exp(-(d * d) / (k * k));
+    case LOSS_GEMANMCCLURE: {
+      const double c2 = k * k, c4 = c2 * c2, q = c2 + d * d;
+      return c4 / (q * q);
+    }
+    case LOSS_DCS: {
+      const double e2 = d * d;
+      if (e2 > k) {
+        const double w = 2.0 * k / (k + e2);
+        return w * w;
+      }
+      return 1.0;
+    }
+    case LOSS_L2DEADZONE: return a <= k ? 0.0 : (d > k ? (-k + d) / d : (k + d) / d);
+    default: return 1.0;
+  }
+}
+__device__ __forceinline__ double loss_rho(int kind, double k, double d) {
+  const double a = fabs(d);
+  switch (kind) {
+    case LOSS_FAIR: {
+      const double n = a / k;
+      return k * k * (n - log1p(n));
+    }
+    case LOSS_HUBER: return a <= k ? d * d / 2 : k * (a - k / 2);
+    case LOSS_CAUCHY: return k * k * log1p(d * d / (k * k)) * 0.5;
+    case LOSS_TUKEY: {
+      if (a > k) return k * k / 6.0;
+      const double u = 1.0 - d * d / (k * k);
+      return k * k * (1 - u * u * u) / 6.0;
+    }
+    case LOSS_WELSCH: return k * k * 0.5 * -expm1(-(d * d) / (k * k));
+    case LOSS_GEMANMCCLURE: return 0.5 * (k * k * d * d) / (k * k + d * d);
+    case LOSS_DCS: {
+      const double e2 = d * d, e4 = e2 * e2, c2 = k * k;
+      return (c2 * e2 + k * e4) / ((e2 + k) * (e2 + k));
+    }
+    case LOSS_L2DEADZONE: return a < k ? 0.0 : 0.5 * (k - a) * (k - a);
+    default: return 0.5 * d * d;
+  }
+}
+
 template <int M, int W>
 __device__ __forceinline__ void whiten_rows(double* Ab, int kind, const double* nz) {
   if (kind == NK_UNIT) return;
@@ -470,6 +531,17 @@ linearize_kernel(BucketDev bk, const double* __restrict__ st0, const double* __r
     const double* s1 = (T::T1 >= 0) ? st1 + (int64_t)bk.row1[i] * state_size(T::T1 >= 0 ? T::T1 : 0) : nullptr;
     Eval<B, true>::run(s0, s1, bk.z + (int64_t)i * T::ZD, Ab);
     if (bk.any_noise) whiten_rows<T::M, T::W>(Ab, bk.nk[i], bk.noise + (int64_t)i * T::M * T::M);
+    if (bk.loss) {
+      double n2 = 0.0;
+#pragma unroll
+      for (int r = 0; r < T::M; ++r) n2 += Ab[r * T::W + T::W - 1] * Ab[r * T::W + T::W - 1];
+      // GeneralSFMFactor::linearize whitens H1, H2 and b one by one through Whiten(Matrix) (slam/GeneralSFMFactor.h:161-167),
+      // and Robust::Whiten(Matrix) reweights with an EMPTY error vector (linear/NoiseModel.h:713-714), i.e. with
+      // sqrt(w(0)) whatever the residual is; only the factor's error() sees rho.  Reproduced as is: parity, not a judgement.
+      const double w = sqrt(loss_weight(bk.loss, bk.loss_k, B == 2 ? 0.0 : sqrt(n2)));
+#pragma unroll
+      for (int k = 0; k < MW; ++k) Ab[k] *= w;
+    }
 #pragma unroll
     for (int k = 0; k < MW; ++k) stage[threadIdx.x * LDS + k] = Ab[k];
   }
@@ -516,7 +588,7 @@ error_kernel(BucketDev bk, const double* __restrict__ st0, const double* __restr
     if (kind != NK_UNIT) whiten_rows<T::M, 1>(r, kind, bk.noise + (int64_t)i * T::M * T::M);
 #pragma unroll
     for (int k = 0; k < T::M; ++k) e += r[k] * r[k];
-    e *= 0.5;
+    e = bk.loss ? loss_rho(bk.loss, bk.loss_k, sqrt(e)) : 0.5 * e;
   }
   e = block_reduce_sum(e, red);
   if (threadIdx.x == 0) partials[blockIdx.x] = e;

@@ -62,6 +62,8 @@ class Engine:
                 nz = np.ascontiguousarray(a[name + "_noise"], dtype=np.float64)
                 assert nz.shape[1] == BUCKET_DIM[b] ** 2
                 self._ck(self.lib.gtb_set_factors(self.h, b, len(z), _ptr(keys), _ptr(z), _ptr(nk), _ptr(nz)))
+                if name + "_robust" in a:
+                    self.set_robust(b, int(a[name + "_robust"][0]), float(a[name + "_robust"][1]))
         if "graph_order" in a:
             go = np.ascontiguousarray(a["graph_order"], dtype=np.int64)
             self._ck(self.lib.gtb_set_graph_order(self.h, len(go), _ptr(go)))
@@ -90,6 +92,13 @@ class Engine:
         """Per-step host -> device refresh of one variable type (same layout as Problem arrays)."""
         state = np.ascontiguousarray(state, dtype=np.float64)
         self._ck(self.lib.gtb_set_variables(self.h, vtype, len(state), None, _ptr(state)))
+
+    def set_robust(self, bucket, loss, k):
+        """noiseModel::Robust around the bucket's base noise (linear/NoiseModel.cpp:741); loss = GTB_LOSS_* id or name."""
+        from .problem import LOSSES
+        b = BUCKETS.index(bucket) if isinstance(bucket, str) else bucket
+        lid = LOSSES.index(loss) if isinstance(loss, str) else int(loss)
+        self._ck(self.lib.gtb_set_robust(self.h, b, lid, float(k)))
 
     def set_ordering(self, keys):
         if isinstance(keys, str):

@@ -28,6 +28,8 @@ bucket-major in the order above.
 import numpy as np
 
 BUCKETS = ["between2", "between3", "sfm", "prior2", "prior3", "priorcam", "priorpt"]
+# m-estimators of linear/LossFunctions.h, ids as GTB_LOSS_* in include/gtsam_b200.h
+LOSSES = ["none", "fair", "huber", "cauchy", "tukey", "welsch", "gemanmcclure", "dcs", "l2withdeadzone"]
 BUCKET_Z = [3, 12, 2, 3, 12, 17, 3]
 BUCKET_DIM = [3, 6, 2, 3, 6, 9, 3]          # residual dimension m
 BUCKET_NKEYS = [2, 2, 2, 1, 1, 1, 1]
@@ -147,6 +149,13 @@ class Problem:
         self.a[name + "_z"] = np.ascontiguousarray(z, dtype=np.float64).reshape(m, BUCKET_Z[b])
         self.a[name + "_nk"] = nk
         self.a[name + "_noise"] = nz
+
+    def set_robust(self, bucket, loss, k):
+        """noiseModel::Robust::Create(mEstimator::<loss>::Create(k), base) for every factor of the bucket.
+        Stored as `<bucket>_robust` = [loss id, k] (ids: LOSSES)."""
+        name = BUCKETS[bucket] if isinstance(bucket, int) else bucket
+        lid = LOSSES.index(loss) if isinstance(loss, str) else int(loss)
+        self.a[name + "_robust"] = np.array([float(lid), float(k)])
 
     # ---- queries --------------------------------------------------------------------------
     def n_vars(self, t):

@@ -172,6 +172,22 @@ gtb_status gtb_lm_iterate(gtb_engine* e, const gtb_lm_params* p, double* lambda_
 gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double relative_error_tol,
                            double absolute_error_tol, gtb_lm_result* result);
 
+/* ---- robust noise models -------------------------------------------------------------
+ * noiseModel::Robust::Create(mEstimator, base) with the default Block reweighting (linear/NoiseModel.cpp:709-745,
+ * linear/LossFunctions.cpp): every factor of `bucket` keeps the base noise given to gtb_set_factors and gets the
+ * m-estimator `loss` with parameter k (> 0): the whitened [A|b] is scaled by sqrt(w(|b|)) and the factor's error becomes
+ * rho(|b|).  Call after gtb_set_factors for that bucket; GTB_LOSS_NONE removes it.  One estimator per bucket.       */
+#define GTB_LOSS_NONE 0
+#define GTB_LOSS_FAIR 1
+#define GTB_LOSS_HUBER 2
+#define GTB_LOSS_CAUCHY 3
+#define GTB_LOSS_TUKEY 4
+#define GTB_LOSS_WELSCH 5
+#define GTB_LOSS_GEMANMCCLURE 6
+#define GTB_LOSS_DCS 7
+#define GTB_LOSS_L2WITHDEADZONE 8
+gtb_status gtb_set_robust(gtb_engine* e, int bucket, int loss, double k);
+
 /* ---- several GPUs: one engine per process / GPU ---------------------------------------------
  * The reference parallelises elimination over the children of a clique with TBB tasks
  * (inference/ClusterTree-inst.h:286-318).  Across GPUs the same tree is cut instead: every rank holds the whole

@@ -98,7 +98,27 @@ static NonlinearFactor::shared_ptr make_factor(const gtbio::File& P, int b, size
   int d = kDim[b];
   int kind = P.at(n + "_nk").i32()[i];
   const double* np = P.at(n + "_noise").f64() + i * d * d;
-  auto model = make_noise(kind, np, d);
+  SharedNoiseModel model = make_noise(kind, np, d);
+  if (P.has(n + "_robust")) {
+    // <bucket>_robust = [m-estimator id, parameter]: ids as GTB_LOSS_* in include/gtsam_b200.h
+    const double* rb = P.at(n + "_robust").f64();
+    const int id = (int)rb[0];
+    const double c = rb[1];
+    noiseModel::mEstimator::Base::shared_ptr est;
+    switch (id) {
+      case 1: est = noiseModel::mEstimator::Fair::Create(c); break;
+      case 2: est = noiseModel::mEstimator::Huber::Create(c); break;
+      case 3: est = noiseModel::mEstimator::Cauchy::Create(c); break;
+      case 4: est = noiseModel::mEstimator::Tukey::Create(c); break;
+      case 5: est = noiseModel::mEstimator::Welsch::Create(c); break;
+      case 6: est = noiseModel::mEstimator::GemanMcClure::Create(c); break;
+      case 7: est = noiseModel::mEstimator::DCS::Create(c); break;
+      case 8: est = noiseModel::mEstimator::L2WithDeadZone::Create(c); break;
+      case 0: break;
+      default: throw std::runtime_error("bad m-estimator id");
+    }
+    if (est) model = noiseModel::Robust::Create(est, model);
+  }
   const uint64_t* k = keys.u64() + i * (b < 3 ? 2 : 1);
   switch (b) {
     case 0: return std::make_shared<BetweenFactor<Pose2>>(k[0], k[1], mk_pose2(z), model);
