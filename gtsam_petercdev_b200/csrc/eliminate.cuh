@@ -379,7 +379,11 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
       if (i >= F) {
         const int bi = (i * (i + 1)) >> 1, bj = (j * (j + 1)) >> 1;
         double acc = 0.0;
-        for (int r = 0; r < F; ++r) acc += P[bi + r] * P[bj + r];
+        if (F == 3) {   // points: the bulk of a bundle-adjustment problem
+          acc = P[bi] * P[bj] + P[bi + 1] * P[bj + 1] + P[bi + 2] * P[bj + 2];
+        } else {
+          for (int r = 0; r < F; ++r) acc += P[bi + r] * P[bj + r];
+        }
         v -= acc;
       }
       if (i < F || !fused) {
