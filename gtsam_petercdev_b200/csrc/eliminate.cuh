@@ -300,13 +300,14 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
     const int S1 = cc.S + 1;
     const double* src = E.arena + cc.front_off + cc.F + (int64_t)cc.F * cc.ld;
     const int32_t* pm = E.pmap + cc.pmap_off;
-    for (int j = WARP ? 0 : warp; j < S1; j += WARP ? 1 : (gsize >> 5)) {
-      const int pj = pm[j];
-      for (int i = lane; i <= j; i += 32) {
-        int a = pm[i], b = pj;
-        if (a > b) { const int t = a; a = b; b = t; }
-        P[tri(a, b)] += src[i + (int64_t)j * cc.ld];
-      }
+    // flattened over the child's packed triangle: every load is independent of the others (a column-by-column walk
+    // costs one global round trip per column, which is what a deep pose-graph tree spends its time on)
+    const int total = (S1 * (S1 + 1)) >> 1;
+    for (int idx = gtid; idx < total; idx += gsize) {
+      const int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
+      int a = pm[i], b = pm[j];
+      if (a > b) { const int t = a; a = b; b = t; }
+      P[tri(a, b)] += src[i + (int64_t)j * cc.ld];
     }
     gsync();
   }
@@ -380,7 +381,7 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
         const int bi = (i * (i + 1)) >> 1, bj = (j * (j + 1)) >> 1;
         double acc = 0.0;
         if (F == 3) {   // points: the bulk of a bundle-adjustment problem
-          acc = P[bi] * P[bj] + P[bi + 1] * P[bj + 1] + P[bi + 2] * P[bj + 2];
+          acc = fma(P[bi + 2], P[bj + 2], fma(P[bi + 1], P[bj + 1], P[bi] * P[bj]));   // the loop's rounding sequence
         } else {
           for (int r = 0; r < F; ++r) acc += P[bi + r] * P[bj + r];
         }
