@@ -32,6 +32,7 @@ WORKLOADS = {
     "c3": "C3 Ladybug-scale synthetic BA (1,723 cams, 156,000 points, 679,032 GeneralSFMFactor<Cal3Bundler> + 2 priors)",
     "c2": "C2 sphere2500-shape Pose3 graph (2,500 Pose3, 4,949 BetweenFactor<Pose3> + prior)",
     "c1": "C1 M3500-shape Pose2 graph (3,500 Pose2, 5,450 BetweenFactor<Pose2> + prior)",
+    "c4": "C4 Venice-scale synthetic BA (1,778 cams, ~993,000 points, ~5M GeneralSFMFactor<Cal3Bundler> + 2 priors)",
 }
 DGEMM_FP64_TFLOPS = 35.46   # cuBLAS fp64 8192^3 measured on this pool's B200 (tools/probe_box.py, profiles/probe_r01.json)
 
@@ -44,6 +45,8 @@ def make_problem(workload):
         return datasets.sphere_shape()
     if workload == "c1":
         return datasets.m3500_shape()
+    if workload == "c4":
+        return datasets.venice_shape()
     raise SystemExit(f"unknown workload {workload}")
 
 
@@ -52,7 +55,7 @@ def ordering_for(problem, workload, name):
     oracle/_ref/ref_tool, committed as permutations under tests/golden/): ordering is an input of the path."""
     if name in ("schur", "natural"):
         return name
-    f = os.path.join(ROOT, "tests", "golden", {"c3": "ladybug_shape", "c2": "sphere_shape", "c1": "m3500_shape"}[workload] + "_orderings.npz")
+    f = os.path.join(ROOT, "tests", "golden", {"c3": "ladybug_shape", "c2": "sphere_shape", "c1": "m3500_shape", "c4": "venice_shape"}[workload] + "_orderings.npz")
     perm = np.load(f)[name]
     return problem.variables()[0][perm]
 
@@ -119,7 +122,7 @@ def run_reference(args, rank, world):
     pf, of = os.path.join(tmp, "p.gtb"), os.path.join(tmp, "o.gtb")
     p.save(pf)
     # bounded sample: at ~10 s per C3 step the run is capped to what fits in a few minutes
-    est = {"c3": 11.0, "c2": 0.2, "c1": 0.1}[args.workload]
+    est = {"c3": 11.0, "c2": 0.2, "c1": 0.1, "c4": 120.0}[args.workload]
     steps = max(1, min(args.steps, int(240 / est)))
     warm = 1 if (args.warmup + steps) * est > 240 else args.warmup
     sample = f"{steps} full LM inner iterations of the whole workload after {warm} warm-up (asked {args.steps}/{args.warmup})"
@@ -267,6 +270,7 @@ def main():
         "schur_step": ("tensor", st["flops_syrk_schur"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
         "small_front": ("hbm", (st["bytes_small"] - st["bytes_thin"]) / 1e9, hbm, "GB/s"),
         "thin_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
+        "point_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
         "linearize": ("hbm", st["bytes_linearize"] / 1e9, hbm, "GB/s"),
         "backsolve": ("hbm", st["bytes_backsolve"] / 1e9, hbm, "GB/s"),
     }
@@ -325,7 +329,7 @@ def main():
             p.a["ordering"] = np.ascontiguousarray(o, dtype=np.uint64)
         pf, of = os.path.join(tmp, "p.gtb"), os.path.join(tmp, "o.gtb")
         p.save(pf)
-        iters = 1 if args.workload == "c3" else 5
+        iters = 1 if args.workload in ("c3", "c4") else 5
         subprocess.run([tool, pf, of, "mode=time", f"ordering={o if isinstance(o, str) else 'file'}", f"iters={iters}", "warm=1",
                         f"lambda={lam!r}"], check=True)
         r = gtbio.load(of)

@@ -401,6 +401,136 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
 }
 
 // ----------------------------------------------------------------------------------------------------
+// point fronts: the bulk of a bundle-adjustment problem.  A point eliminated alone whose factors are projections
+// (GeneralSFMFactor, W = 13) from k <= 15 distinct cameras and whose parent is a large front.  Nothing of the
+// (9k+4)^2 / 2 packed front is materialised: with J_c (2 x 9), J_p (2 x 3), b (2) of every factor staged in shared
+// memory, the frontal block V = sum J_p^T J_p (+ damping) is factored in registers, the conditional rows
+// y_j = R^-T (J_p^T [J_c | b])_j are computed per separator column, written to the clique's own front (what
+// back-substitution reads) and kept in shared memory, and every entry of the Schur complement
+//   C_ij = [same camera] (J_c^T J_c)_ij - y_i . y_j          (camera - camera blocks of different cameras are pure -y_i.y_j)
+// goes straight into the parent front through the child -> parent column map (FP64 atomics).  One warp per point,
+// 2.4 KB of shared memory per warp at k = 5 instead of 13 KB: four times the warps in flight of the generic thin kernel.
+// ----------------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ int point_front_doubles(int kmax) {
+  const int nmax = 9 * kmax + 1;
+  return 26 * kmax + 3 * nmax + ((nmax + 2) >> 1) + ((2 * kmax + 2) >> 1) + 2;   // ab | Y | pm (ints) | scol, sfac (ints) | pad
+}
+__global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count,
+                                                                       int kmax) {
+  extern __shared__ double sh[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = blockIdx.x * kThinWarps + warp;
+  if (slot >= count) return;
+  const int nmax = 9 * kmax + 1;
+  double* ab = sh + warp * point_front_doubles(kmax);   // ab[26 s + 13 r + col]: rows of factor s
+  double* Y = ab + 26 * kmax;                           // Y[a * nmax + j] = y_j[a]
+  int* pm_s = reinterpret_cast<int*>(Y + 3 * nmax);     // parent column of separator scalar q (and of the rhs)
+  int* scol = pm_s + ((nmax + 2) & ~1);                 // separator-relative first column of factor s's camera
+  int* sfac = scol + kmax;                              // camera block index -> factor
+  const int c = list[slot];
+  const CliqueDev ci = E.cliques[c];
+  const CliqueDev cp = E.cliques[ci.parent];
+  const int k = ci.fac_end - ci.fac_begin, n = ci.S + 1, nc = ci.S;   // nc = 9 k camera scalars, column nc is the rhs
+  for (int t = lane; t < 26 * k; t += 32) {
+    const int s = t / 26, r = t - s * 26;
+    const SlotDev sl = E.slots[ci.fac_begin + s];
+    ab[t] = E.Ab[2][(int64_t)sl.index * 26 + r];
+    if (r == 0) { scol[s] = sl.col0 - 3; sfac[(sl.col0 - 3) / 9] = s; }
+  }
+  for (int q = lane; q < n; q += 32) pm_s[q] = E.pmap[ci.pmap_off + q];
+  __syncwarp();
+  // frontal block and its right-hand side, factors in gather order (deterministic sums); every lane keeps a copy
+  double v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0, g0 = 0, g1 = 0, g2 = 0, bb = 0;
+  for (int s = 0; s < k; ++s) {
+    const double* f = ab + 26 * s;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const double p0 = f[13 * r + 9], p1 = f[13 * r + 10], p2 = f[13 * r + 11], br = f[13 * r + 12];
+      v00 += p0 * p0; v01 += p0 * p1; v02 += p0 * p2; v11 += p1 * p1; v12 += p1 * p2; v22 += p2 * p2;
+      g0 += p0 * br; g1 += p1 * br; g2 += p2 * br; bb += br * br;
+    }
+  }
+  if (E.damp) {
+    const int32_t* g = E.gidx + ci.gidx_off;
+    v00 += E.damp[g[0]]; v11 += E.damp[g[1]]; v22 += E.damp[g[2]];
+  }
+  // 3 x 3 Cholesky, upper, same pivot rule and reciprocal form as thin_front_kernel (base/cholesky.cpp:125-158)
+  bool ok = v00 > 0.0;
+  const double i0 = rsqrt(v00);
+  const double r00 = v00 * i0, r01 = v01 * i0, r02 = v02 * i0;
+  v11 -= r01 * r01; v12 -= r01 * r02; v22 -= r02 * r02;
+  ok = ok && v11 > 0.0;
+  const double i1 = rsqrt(v11);
+  const double r11 = v11 * i1, r12 = v12 * i1;
+  v22 -= r12 * r12;
+  ok = ok && v22 > 0.0;
+  const double i2 = rsqrt(v22);
+  const double r22 = v22 * i2;
+  if (ok) ok = frexp_exp(r11) - frexp_exp(r22) < 12;
+  if (!ok) {
+    if (lane == 0) atomicMin(E.fail, c);
+    return;
+  }
+  const double d0 = 1.0 / r00, d1 = 1.0 / r11, d2 = 1.0 / r22;
+  double* dst = E.arena + ci.front_off;
+  if (lane == 0) {
+    dst[0] = r00;
+    dst[ci.ld] = r01; dst[1 + ci.ld] = r11;
+    dst[2 * (int64_t)ci.ld] = r02; dst[1 + 2 * (int64_t)ci.ld] = r12; dst[2 + 2 * (int64_t)ci.ld] = r22;
+  }
+  // conditional rows: y_j = R^-T w_j, w_j = J_p^T (column j of [J_c | b]) of the camera's factor, or g for the rhs
+  for (int j = lane; j < n; j += 32) {
+    double w0, w1, w2;
+    if (j < nc) {
+      const int blk = j / 9, col = j - blk * 9;
+      const double* f = ab + 26 * sfac[blk];
+      const double c0 = f[col], c1 = f[13 + col];
+      w0 = f[9] * c0 + f[22] * c1;
+      w1 = f[10] * c0 + f[23] * c1;
+      w2 = f[11] * c0 + f[24] * c1;
+    } else {
+      w0 = g0; w1 = g1; w2 = g2;
+    }
+    const double y0 = w0 * d0;
+    const double y1 = (w1 - r01 * y0) * d1;
+    const double y2 = (w2 - r02 * y0 - r12 * y1) * d2;
+    Y[j] = y0; Y[nmax + j] = y1; Y[2 * nmax + j] = y2;
+    double* col3 = dst + (int64_t)(3 + j) * ci.ld;
+    col3[0] = y0; col3[1] = y1; col3[2] = y2;
+  }
+  __syncwarp();
+  // Schur complement entries (i <= j over the separator scalars and the rhs) straight into the parent
+  double* pdst = E.arena + cp.front_off;
+  const int pld = cp.ld;
+  const int total = (n * (n + 1)) >> 1;
+  int idx = lane;
+  int j = tri_col(idx), i = idx - ((j * (j + 1)) >> 1);
+  for (; idx < total; idx += 32) {
+    double h = 0.0;
+    const int bi = i / 9;
+    if (j < nc) {
+      if (bi == j / 9) {
+        const double* f = ab + 26 * sfac[bi];
+        const int a = i - bi * 9, b = j - bi * 9;
+        h = f[a] * f[b] + f[13 + a] * f[13 + b];
+      }
+    } else if (i < nc) {
+      const double* f = ab + 26 * sfac[bi];
+      const int a = i - bi * 9;
+      h = f[a] * f[12] + f[13 + a] * f[25];
+    } else {
+      h = bb;
+    }
+    const double v = h - (Y[i] * Y[j] + Y[nmax + i] * Y[nmax + j] + Y[2 * nmax + i] * Y[2 * nmax + j]);
+    int a = pm_s[i], b = pm_s[j];
+    if (a > b) { const int t = a; a = b; b = t; }
+    atomicAdd(pdst + a + (int64_t)b * pld, v);
+    i += 32;
+    while (i > j) { i -= j + 1; ++j; }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
 // large fronts: front in global memory (L2-resident), several CTAs per front
 // ----------------------------------------------------------------------------------------------------
 // zeroing of very large fronts is spread over many CTAs

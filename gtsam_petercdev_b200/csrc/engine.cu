@@ -136,6 +136,7 @@ struct gtb_engine {
   std::vector<int32_t> owner;         // per clique: owning rank, or -1 for the top of the tree
   std::vector<int64_t> front_off;     // per clique: offset in this engine's arena (top fronts live in one tail region)
   std::vector<int32_t> top_list;
+  std::vector<uint8_t> is_point;      // per clique: handled by point_front_kernel (star structure, large parent)
   std::vector<int32_t> large_list;    // every large front this rank touches: its own (phase 0) first, then the top
   int32_t n_large_own = 0;
   int64_t top_off = 0, top_doubles = 0, arena_doubles = 0, top_work_begin = 0, top_zero_blocks = 0;
@@ -308,10 +309,10 @@ struct StageTimer {
 };
 
 // kernel classes for launch counting and optional per-launch event timing
-enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
+enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_POINT, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
        K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
-                                          "small_front", "thin_front", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
+                                          "small_front", "thin_front", "point_front", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
                                           "backsolve", "backsolve_gemv", "retract", "own_delta"};
 
 static void prof_begin(Engine* e, int k) {
@@ -689,6 +690,20 @@ static void compute_partition(const Plan& p, int world, std::vector<int32_t>& ow
   }
 }
 
+// A point eliminated alone, every factor a projection (bucket 2) from a distinct camera, at most 15 of them.
+static bool is_star_clique(const Engine* e, int32_t c) {
+  const Plan& p = e->plan;
+  const int64_t f0 = p.fac_off[c], f1 = p.fac_off[c + 1];
+  bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= 15 && is_thin_front(p.F[c], p.F[c] + p.S[c] + 1) &&
+              p.S[c] == 9 * (f1 - f0) && p.child_off[c + 1] == p.child_off[c];
+  for (int64_t f = f0; star && f < f1; ++f) {
+    const FactorSlot& fs = p.slots[f];
+    star = e->g_bucket[fs.factor] == 2 && fs.col1 == 0 && fs.col0 >= 3;
+    for (int64_t g2 = f0; star && g2 < f; ++g2) star = p.slots[g2].col0 != fs.col0;
+  }
+  return star;
+}
+
 // Builds the level schedule of one phase: phase 0 = subtree cliques owned by this rank, phase 1 = the shared top of the
 // tree (factored on rank 0 after the fan-in reduction; empty when there is one rank).
 static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
@@ -789,13 +804,27 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
 
     // re-sort the small part of the level by dimension and cut into thread classes
     auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
-    // thin fronts first (sorted by dimension), then dense ones (sorted by dimension)
-    auto thin = [&](int32_t c) { return is_thin_front(p.F[c], dim_of(c)); };
+    // point fronts first, then the other thin fronts, then dense ones; each group sorted by dimension
+    auto point = [&](int32_t c) { return e->is_point[c] != 0; };
+    auto thin = [&](int32_t c) { return !point(c) && is_thin_front(p.F[c], dim_of(c)); };
     std::stable_sort(lc.begin() + b, lc.begin() + b + ns, [&](int32_t a, int32_t c2) {
-      const int ka = thin(a) ? 0 : 1, kc = thin(c2) ? 0 : 1;
+      const int ka = point(a) ? 0 : (thin(a) ? 1 : 2), kc = point(c2) ? 0 : (thin(c2) ? 1 : 2);
       return ka != kc ? ka < kc : dim_of(a) < dim_of(c2);
     });
     int64_t q = b;
+    // point classes by number of cameras: shared memory per warp grows with k
+    while (q < b + ns && point(lc[q])) {
+      const int64_t q0 = q;
+      const int k0 = p.S[lc[q]] / 9;
+      const int hi = std::max(k0 + 1, k0 * 5 / 4);
+      int32_t mk = 0;
+      while (q < b + ns && point(lc[q]) && p.S[lc[q]] / 9 <= hi) { mk = std::max(mk, p.S[lc[q]] / 9); ++q; }
+      LevelSched::Cls cl;
+      cl.begin = q0; cl.count = (int32_t)(q - q0); cl.kind = 3; cl.threads = kThinWarps * 32;
+      cl.group_doubles = mk;
+      cl.smem = point_front_doubles(mk) * (int32_t)sizeof(double) * kThinWarps;
+      L.small.push_back(cl);
+    }
     // thin classes are cut adaptively so that the shared memory of a class (sized by its largest member) stays within
     // ~20 % of what its smallest member needs: occupancy is limited by shared memory
     while (q < b + ns && thin(lc[q])) {
@@ -836,6 +865,12 @@ static void install_plan(Engine* e) {
   e->bs_scratch_off.clear();
   e->bs_scratch_doubles = 0;
   e->step_tasks_list.clear();
+  e->is_point.assign(C, 0);
+  for (int32_t c = 0; c < C; ++c) {
+    const int32_t par = p.parent[c];
+    if (par >= 0 && is_fused_child(p.F[c], p.F[c] + p.S[c] + 1, p.F[par], p.F[par] + p.S[par] + 1) && is_star_clique(e, c))
+      e->is_point[c] = 1;
+  }
   std::vector<int32_t> lc;
   lc.reserve(C);
   build_phase(e, 0, lc);
@@ -890,18 +925,7 @@ static void install_plan(Engine* e) {
     d.first_key_var = p.vars[p.vars_off[c]];
     d.dfac_off = 0;
     d.pad = 0;
-    // star: a point eliminated alone, all of its factors are SFM factors (bucket 2) of distinct cameras, at most 15
-    d.flags = 0;
-    {
-      const int64_t f0 = p.fac_off[c], f1 = p.fac_off[c + 1];
-      bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= 15 && is_thin_front(p.F[c], p.F[c] + p.S[c] + 1);
-      for (int64_t f = f0; star && f < f1; ++f) {
-        const FactorSlot& fs = p.slots[f];
-        star = e->g_bucket[fs.factor] == 2 && fs.col1 == 0 && fs.col0 >= 3;
-        for (int64_t g2 = f0; star && g2 < f; ++g2) star = p.slots[g2].col0 != fs.col0;
-      }
-      if (star) d.flags |= kCliqueStar;
-    }
+    d.flags = is_star_clique(e, c) ? kCliqueStar : 0;
     if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
       dfac_total += (int64_t)((p.F[c] + PW - 1) / PW) * PW * PW;
@@ -1073,7 +1097,10 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
   for (int32_t l = 0; l < e->plan.n_levels; ++l) {
     const LevelSched& L = e->sched[phase][l];
     for (const auto& c : L.small) {
-      if (c.kind == 0)
+      if (c.kind == 3)
+        LAUNCH(e, K_POINT, point_front_kernel<<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
+                               E, lists + c.begin, c.count, c.group_doubles));
+      else if (c.kind == 0)
         LAUNCH(e, K_THIN, thin_front_kernel<true><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
                               E, lists + c.begin, c.count, c.group_doubles));
       else if (c.kind == 1)
@@ -1121,6 +1148,7 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   if (!attr) {
     CK(cudaFuncSetAttribute(small_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(thin_front_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(point_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(thin_front_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(front_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem));
     CK(cudaFuncSetAttribute(schur_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmemTile));
