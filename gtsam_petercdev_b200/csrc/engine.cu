@@ -690,11 +690,12 @@ static void compute_partition(const Plan& p, int world, std::vector<int32_t>& ow
   }
 }
 
-// A point eliminated alone, every factor a projection (bucket 2) from a distinct camera, at most 15 of them.
-static bool is_star_clique(const Engine* e, int32_t c) {
+// A point eliminated alone, every factor a projection (bucket 2) from a distinct camera, at most kmax of them
+// (15: what the thin kernel's staging area holds; 22: the largest thin front, for the point kernel).
+static bool is_star_clique(const Engine* e, int32_t c, int kmax) {
   const Plan& p = e->plan;
   const int64_t f0 = p.fac_off[c], f1 = p.fac_off[c + 1];
-  bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= 15 && is_thin_front(p.F[c], p.F[c] + p.S[c] + 1) &&
+  bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= kmax && is_thin_front(p.F[c], p.F[c] + p.S[c] + 1) &&
               p.S[c] == 9 * (f1 - f0) && p.child_off[c + 1] == p.child_off[c];
   for (int64_t f = f0; star && f < f1; ++f) {
     const FactorSlot& fs = p.slots[f];
@@ -868,7 +869,7 @@ static void install_plan(Engine* e) {
   e->is_point.assign(C, 0);
   for (int32_t c = 0; c < C; ++c) {
     const int32_t par = p.parent[c];
-    if (par >= 0 && is_fused_child(p.F[c], p.F[c] + p.S[c] + 1, p.F[par], p.F[par] + p.S[par] + 1) && is_star_clique(e, c))
+    if (par >= 0 && is_fused_child(p.F[c], p.F[c] + p.S[c] + 1, p.F[par], p.F[par] + p.S[par] + 1) && is_star_clique(e, c, 22))
       e->is_point[c] = 1;
   }
   std::vector<int32_t> lc;
@@ -925,7 +926,7 @@ static void install_plan(Engine* e) {
     d.first_key_var = p.vars[p.vars_off[c]];
     d.dfac_off = 0;
     d.pad = 0;
-    d.flags = is_star_clique(e, c) ? kCliqueStar : 0;
+    d.flags = is_star_clique(e, c, 15) ? kCliqueStar : 0;
     if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
       dfac_total += (int64_t)((p.F[c] + PW - 1) / PW) * PW * PW;
