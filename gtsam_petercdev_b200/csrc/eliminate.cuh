@@ -1162,6 +1162,28 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
       for (int q = 0; q < nchunk; ++q) a -= part[(int64_t)q * F + i];
       rhs[i] = a;
     }
+  } else if (F == 3 && ld == 4) {
+    // point front (point_front_kernel): three conditional rows stored as one 32-byte column per separator scalar
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+    for (int j = lane; j < S; j += 32) {
+      const double x = delta[g[3 + j]];
+      const double* col = A + (int64_t)(3 + j) * 4;
+      a0 += col[0] * x; a1 += col[1] * x; a2 += col[2] * x;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+      a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+      a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+    }
+    if (lane == 0) {
+      const double* d = A + (int64_t)N * 4;
+      const double x2 = (d[2] - a2) * (1.0 / A[2 + 2 * 4]);
+      const double x1 = (d[1] - a1 - A[1 + 2 * 4] * x2) * (1.0 / A[1 + 1 * 4]);
+      const double x0 = (d[0] - a0 - A[0 + 1 * 4] * x1 - A[0 + 2 * 4] * x2) * (1.0 / A[0]);
+      delta[g[0]] = x0; delta[g[1]] = x1; delta[g[2]] = x2;
+    }
+    return;
   } else {
     for (int j = gtid; j < S; j += gsize) xs[j] = delta[g[F + j]];
     gsync();

@@ -135,6 +135,7 @@ struct gtb_engine {
   void* comm_user = nullptr;
   std::vector<int32_t> owner;         // per clique: owning rank, or -1 for the top of the tree
   std::vector<int64_t> front_off;     // per clique: offset in this engine's arena (top fronts live in one tail region)
+  std::vector<int32_t> ld;            // per clique: leading dimension of its front storage (point fronts keep 3 rows: ld = 4)
   std::vector<int32_t> top_list;
   std::vector<uint8_t> is_point;      // per clique: handled by point_front_kernel (star structure, large parent)
   std::vector<int32_t> large_list;    // every large front this rank touches: its own (phase 0) first, then the top
@@ -879,9 +880,21 @@ static void install_plan(Engine* e) {
   e->sched_lists = lc;
   // the shared top: fronts relocated to one contiguous tail of the arena (identical on every rank) so that the fan-in
   // is a single reduction; assembled before it from own factors (rank 0) and from the subtree children each rank owns
-  e->front_off = p.front_off;
+  // Front storage.  The plan's layout gives every clique a full (N+1)^2 front; a point front only ever stores its three
+  // conditional rows [R S d] (its Schur complement goes straight into the parent), so it gets ld = 4: one 32-byte
+  // column per separator scalar, contiguous.  C3: 4.9 -> 2.0 GB, C4: 29 -> 8 GB.  Same layout on every rank.
+  e->front_off.assign(C, 0);
+  e->ld = p.ld;
+  int64_t off = 0;
+  for (int32_t c = 0; c < C; ++c) {
+    if (e->owner[c] < 0) continue;
+    const int64_t dim = p.F[c] + p.S[c] + 1;
+    if (e->is_point[c]) e->ld[c] = 4;
+    e->front_off[c] = off;
+    off += ((int64_t)e->ld[c] * dim + 15) & ~(int64_t)15;
+  }
   e->top_list.clear();
-  e->top_off = (p.arena_doubles + 15) & ~(int64_t)15;
+  e->top_off = off;
   int64_t tail = e->top_off;
   e->top_zero_blocks = 0;
   for (int32_t c = 0; c < C; ++c)
@@ -899,7 +912,7 @@ static void install_plan(Engine* e) {
   e->n_large_own = (int32_t)e->large_list.size();
   e->large_list.insert(e->large_list.end(), e->top_list.begin(), e->top_list.end());
   e->top_doubles = tail - e->top_off;
-  e->arena_doubles = e->top_list.empty() ? p.arena_doubles : tail;
+  e->arena_doubles = tail;
   e->top_work_begin = (int64_t)e->child_work.size();
   for (int32_t c : e->top_list)
     for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k)
@@ -918,7 +931,7 @@ static void install_plan(Engine* e) {
   for (int32_t c = 0; c < C; ++c) {
     CliqueDev& d = cd[c];
     d.front_off = e->front_off[c];
-    d.F = p.F[c]; d.S = p.S[c]; d.ld = p.ld[c]; d.parent = p.parent[c];
+    d.F = p.F[c]; d.S = p.S[c]; d.ld = e->ld[c]; d.parent = p.parent[c];
     d.fac_begin = (int32_t)p.fac_off[c]; d.fac_end = (int32_t)p.fac_off[c + 1];
     d.child_begin = (int32_t)p.child_off[c]; d.child_end = (int32_t)p.child_off[c + 1];
     need(p.pmap_off[c] < INT32_MAX && p.gidx_off[c] < INT32_MAX, "plan index overflow");
@@ -1492,7 +1505,7 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
   if (!e || !out) return GTB_ERR_INVALID;
   if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
   const Plan& p = e->plan;
-  out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)p.arena_doubles;
+  out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)(e->arena_doubles ? e->arena_doubles : p.arena_doubles);
   out[4] = (double)p.n_small; out[5] = (double)p.n_large; out[6] = p.flops_large; out[7] = p.assembly_bytes;
   double thin_bytes = 0;
   out[8] = p.flops_syrk_frontal; out[9] = p.flops_syrk_schur; out[10] = p.bytes_backsolve;
@@ -1591,7 +1604,7 @@ gtb_status gtb_get_conditionals(gtb_engine* e, double* out) {
   CK(cudaMemcpyAsync(arena.data(), e->d_arena.p, arena.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
   for (int32_t c = 0; c < p.n_cliques; ++c) {
-    const int F = p.F[c], dim = F + p.S[c] + 1, ld = p.ld[c];
+    const int F = p.F[c], dim = F + p.S[c] + 1, ld = e->ld[c];
     const double* A = arena.data() + e->front_off[c];
     double* o = out + p.cond_off[c];
     for (int i = 0; i < F; ++i)
