@@ -158,6 +158,8 @@ struct gtb_engine {
   int64_t partial_off[7] = {0};
   int64_t n_partials = 0;
   double* h_scalars = nullptr;   // pinned
+  double* h_stage[4] = {nullptr, nullptr, nullptr, nullptr};   // pinned staging of the per-step state refresh
+  cudaEvent_t stage_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   DevBuf<int64_t> d_inc_off;
   DevBuf<int32_t> d_inc_bucket, d_inc_index, d_inc_slot, d_var_goff, d_var_dim;
   DevBuf<CliqueDev> d_cliques;
@@ -186,6 +188,10 @@ struct gtb_engine {
 
   ~gtb_engine() {
     if (h_scalars) cudaFreeHost(h_scalars);
+    for (int t = 0; t < 4; ++t) {
+      if (h_stage[t]) cudaFreeHost(h_stage[t]);
+      if (stage_ev[t]) cudaEventDestroy(stage_ev[t]);
+    }
     for (auto ev_ : prof_events) cudaEventDestroy(ev_);
     if (ev[0]) cudaEventDestroy(ev[0]);
     if (ev[1]) cudaEventDestroy(ev[1]);
@@ -367,10 +373,19 @@ static void set_variables(Engine* e, int vt, int64_t n, const uint64_t* keys, co
   if (e->finalized) {
     // state refresh (the per-step host -> device copy)
     need(n == v.n, "variable count changed after gtb_finalize_problem");
-    for (int64_t i = 0; i < n; ++i) to_device_state(vt, state + i * kStateIn[vt], &v.state[i * kStateDev[vt]]);
     if (e->has_device && n) {
-      CK(cudaMemcpyAsync(e->d_state[e->cur][vt].p, v.state.data(), v.state.size() * sizeof(double),
-                         cudaMemcpyHostToDevice, e->stream));
+      // convert straight into a pinned staging buffer so that the copy is a real asynchronous DMA
+      if (!e->h_stage[vt]) {
+        CK(cudaMallocHost(&e->h_stage[vt], v.state.size() * sizeof(double)));
+        CK(cudaEventCreateWithFlags(&e->stage_ev[vt], cudaEventDisableTiming));
+      } else {
+        CK(cudaEventSynchronize(e->stage_ev[vt]));   // the previous refresh has left the buffer
+      }
+      double* hs = e->h_stage[vt];
+      if (kStateIn[vt] == kStateDev[vt] && vt != 0) std::memcpy(hs, state, v.state.size() * sizeof(double));
+      else for (int64_t i = 0; i < n; ++i) to_device_state(vt, state + i * kStateIn[vt], hs + i * kStateDev[vt]);
+      CK(cudaMemcpyAsync(e->d_state[e->cur][vt].p, hs, v.state.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+      CK(cudaEventRecord(e->stage_ev[vt], e->stream));
       e->linearized = e->factorized = e->solved = false;
       e->lm_have_error = false;
     }
