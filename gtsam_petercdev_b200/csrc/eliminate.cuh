@@ -31,6 +31,7 @@ struct CliqueDev {
   int32_t pad;
 };
 constexpr int32_t kCliqueStar = 1;
+constexpr int32_t kCliqueFuseUp = 2;   // large front whose Schur-complement step adds C - S^T S straight into its (large) parent
 
 struct SlotDev { int32_t col0, col1, bucket, index; };
 
@@ -416,7 +417,7 @@ __host__ __device__ __forceinline__ int point_front_doubles(int kmax) {
   return 26 * kmax + 3 * nmax + ((nmax + 2) >> 1) + ((2 * kmax + 2) >> 1) + 2;   // ab | Y | pm (ints) | scol, sfac (ints) | pad
 }
 __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count,
-                                                                       int kmax) {
+                                                                       int kmax, int schur) {
   extern __shared__ double sh[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = blockIdx.x * kThinWarps + warp;
@@ -498,6 +499,7 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
     double* col3 = dst + (int64_t)(3 + j) * ci.ld;
     col3[0] = y0; col3[1] = y1; col3[2] = y2;
   }
+  if (!schur) return;   // the Schur complement is gathered per camera pair by point_pair_kernel / point_diag_kernel
   __syncwarp();
   // Schur complement entries (i <= j over the separator scalars and the rhs) straight into the parent
   double* pdst = E.arena + cp.front_off;
@@ -527,6 +529,115 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
     atomicAdd(pdst + a + (int64_t)b * pld, v);
     i += 32;
     while (i > j) { i -= j + 1; ++j; }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// Schur complement of the point cliques, gathered per camera pair.  point_front_kernel scatters (9k+1)(9k+2)/2 FP64
+// atomics per point into the parent front and is bound by the L2 atomic rate (C4: 1.07 G atomics per step).  Here the
+// sum is turned around: the host lists, once per ordering, for every 9 x 9 block (camera A, camera B) of a parent
+// front the points that see both cameras, and one thread per (block, 3-column slab) accumulates
+//     C_AB = - sum_p Y_p,A^T Y_p,B                                   (different cameras)
+//     C_AA = sum_p J_c^T J_c - Y_p,A^T Y_p,A,   C_A,rhs = sum_p J_c^T b - Y_p,A^T y_p,rhs   (same camera: own factor too)
+// in registers from the conditional rows the point kernel has just written (ld = 4: the 9 columns of a camera are 288
+// contiguous bytes), in a fixed order, and adds the block to the parent once.  Lists longer than kPairSeg items are cut
+// into segments whose partial sums meet in the parent through atomics (81 per segment instead of 81 per item).
+// ----------------------------------------------------------------------------------------------------
+constexpr int kPairSeg = 32;
+struct PairSeg { int64_t dst; int32_t ld; int32_t begin; int32_t count; int32_t ncol; };   // ncol: columns from the block to the parent's rhs column
+__global__ void __launch_bounds__(128) point_pair_kernel(ElimDev E, const PairSeg* __restrict__ segs, int nseg,
+                                                         const uint2* __restrict__ items) {
+  const int gt = blockIdx.x * 128 + threadIdx.x;
+  const int s = gt / 3, slab = gt - 3 * s;
+  if (s >= nseg) return;
+  const PairSeg sg = segs[s];
+  double acc[9][3];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) acc[i][0] = acc[i][1] = acc[i][2] = 0.0;
+  const double* arena = E.arena;
+  for (int q = sg.begin; q < sg.begin + sg.count; ++q) {
+    const uint2 it = __ldg(items + q);
+    const double2* ya = reinterpret_cast<const double2*>(arena + (int64_t)it.x * 4);
+    const double2* yb = reinterpret_cast<const double2*>(arena + (int64_t)it.y * 4) + 6 * slab;
+    double b0[3], b1[3], b2[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const double2 u = __ldg(yb + 2 * c), v = __ldg(yb + 2 * c + 1);
+      b0[c] = u.x; b1[c] = u.y; b2[c] = v.x;
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+      const double2 u = __ldg(ya + 2 * i), v = __ldg(ya + 2 * i + 1);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) acc[i][c] += u.x * b0[c] + u.y * b1[c] + v.x * b2[c];
+    }
+  }
+  double* dst = E.arena + sg.dst + (int64_t)(3 * slab) * sg.ld;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) atomicAdd(dst + i + (int64_t)c * sg.ld, -acc[i][c]);
+}
+// items: 3 words each: first column of the camera's block in the point's front (32-byte units), factor index in the
+// projection bucket, the point's rhs column (32-byte units; bit 31: this is the point's first camera, which carries the
+// - y_rhs . y_rhs of the constant term).  Threads 0..2 of a segment own 3 columns of the 9 x 9 block, thread 3 the rhs column.
+__global__ void __launch_bounds__(128) point_diag_kernel(ElimDev E, const PairSeg* __restrict__ segs, int nseg,
+                                                         const uint32_t* __restrict__ items) {
+  const int gt = blockIdx.x * 128 + threadIdx.x;
+  const int s = gt >> 2, slab = gt & 3;
+  if (s >= nseg) return;
+  const PairSeg sg = segs[s];
+  double acc[9][3];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) acc[i][0] = acc[i][1] = acc[i][2] = 0.0;
+  double cst = 0.0;
+  const double* arena = E.arena;
+  const double* Ab = E.Ab[2];
+  for (int q = sg.begin; q < sg.begin + sg.count; ++q) {
+    const uint32_t iy = __ldg(items + 3 * (int64_t)q), ifac = __ldg(items + 3 * (int64_t)q + 1), ir = __ldg(items + 3 * (int64_t)q + 2);
+    const double2* ya = reinterpret_cast<const double2*>(arena + (int64_t)iy * 4);
+    const double* f = Ab + (int64_t)ifac * 26;
+    if (slab < 3) {
+      double b0[3], b1[3], b2[3], j0[3], j1[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const double2 u = __ldg(ya + 6 * slab + 2 * c), v = __ldg(ya + 6 * slab + 2 * c + 1);
+        b0[c] = u.x; b1[c] = u.y; b2[c] = v.x;
+        j0[c] = __ldg(f + 3 * slab + c); j1[c] = __ldg(f + 13 + 3 * slab + c);
+      }
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        const double2 u = __ldg(ya + 2 * i), v = __ldg(ya + 2 * i + 1);
+        const double a0 = __ldg(f + i), a1 = __ldg(f + 13 + i);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) acc[i][c] += (a0 * j0[c] + a1 * j1[c]) - (u.x * b0[c] + u.y * b1[c] + v.x * b2[c]);
+      }
+    } else {
+      const double2* yr = reinterpret_cast<const double2*>(arena + (int64_t)(ir & 0x7fffffffu) * 4);
+      const double2 ru = __ldg(yr), rv = __ldg(yr + 1);
+      const double br0 = __ldg(f + 12), br1 = __ldg(f + 25);
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        const double2 u = __ldg(ya + 2 * i), v = __ldg(ya + 2 * i + 1);
+        const double a0 = __ldg(f + i), a1 = __ldg(f + 13 + i);
+        acc[i][0] += (a0 * br0 + a1 * br1) - (u.x * ru.x + u.y * ru.y + v.x * rv.x);
+      }
+      cst += br0 * br0 + br1 * br1;
+      if (ir >> 31) cst -= ru.x * ru.x + ru.y * ru.y + rv.x * rv.x;
+    }
+  }
+  if (slab < 3) {
+    double* dst = E.arena + sg.dst + (int64_t)(3 * slab) * sg.ld;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int i = 0; i < 9; ++i)
+        if (i <= 3 * slab + c) atomicAdd(dst + i + (int64_t)c * sg.ld, acc[i][c]);
+  } else {
+    double* dst = E.arena + sg.dst + (int64_t)sg.ncol * sg.ld;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) atomicAdd(dst + i, acc[i][0]);
+    atomicAdd(dst + sg.ncol, cst);
   }
 }
 
@@ -620,8 +731,13 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // multiplied: a lone CTA on an SM otherwise waits on L2/HBM every chunk).  ka and the front's leading dimension are
 // even, so every 16-byte copy is aligned; ragged edges are zero-filled by the copy itself.
 constexpr int kStages = 3;
+// MODE 0: C -= product in place.  MODE 1: the same through atomics (K split over several CTAs).  MODE 2: the updated tile
+// (C itself only when add_c: one K slice carries it) is added into the parent front PA through the child -> parent
+// column map pm instead: the extend-add of a large child fused into its Schur-complement step.
+template <int MODE = 0>
 __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int dim, int r0, int c0, int re, int ka,
-                                            int kend, double* sm) {
+                                            int kend, double* sm, const int32_t* __restrict__ pm = nullptr,
+                                            double* __restrict__ PA = nullptr, int pld = 0, int F = 0, bool add_c = false) {
   double* Xs = sm;                        // [kStages][TW * LDT]
   double* Ys = sm + kStages * TW * LDT;   // [kStages][TW * LDT]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -681,7 +797,17 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int j = c0 + wc * 16 + b * 8 + 2 * t + e;
-        if (i < re && j < dim && i <= j) A[i + (int64_t)j * ld] -= acc[a][b][e];
+        if (i < re && j < dim && i <= j) {
+          if (MODE == 2) {
+            int pa = pm[i - F], pb = pm[j - F];
+            if (pa > pb) { const int tt = pa; pa = pb; pb = tt; }
+            atomicAdd(PA + pa + (int64_t)pb * pld, (add_c ? A[i + (int64_t)j * ld] : 0.0) - acc[a][b][e]);
+          } else if (MODE == 1) {
+            atomicAdd(A + i + (int64_t)j * ld, -acc[a][b][e]);
+          } else {
+            A[i + (int64_t)j * ld] -= acc[a][b][e];
+          }
+        }
       }
     }
 }
@@ -714,6 +840,12 @@ __host__ __device__ __forceinline__ int step_tasks(int F, int dim, int p) {
 }
 
 struct StepTask { int32_t clique; int32_t task; };
+// Schur-step tasks pack (tile, K slice, number of K slices): a front with too few tiles to fill the machine splits the
+// K = F sum of every tile over several CTAs, whose partial products meet in C through FP64 atomics.
+constexpr int kSchurTileBits = 20, kSchurSliceBits = 5;
+__host__ __device__ __forceinline__ int schur_task(int tile, int slice, int nsplit) {
+  return tile | (slice << kSchurTileBits) | (nsplit << (kSchurTileBits + kSchurSliceBits));
+}
 
 // One warp: Cholesky (upper) of the 32 x 32 block Dh[i * LDP + l] = D(l, i) held in shared memory, in registers with
 // lane = column; rows / columns beyond the front are identity padding.  Also leaves 1 / R(i, i) in dinv_h and the inverses
@@ -1060,13 +1192,28 @@ __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const Ste
   const int F = ci.F, dim = F + ci.S + 1, ld = ci.ld;
   double* A = E.arena + ci.front_off;
   const int nt = (dim - F + TW - 1) / TW;
+  const int tile = me.task & ((1 << kSchurTileBits) - 1), slice = (me.task >> kSchurTileBits) & ((1 << kSchurSliceBits) - 1);
+  const int nsplit = me.task >> (kSchurTileBits + kSchurSliceBits);
   int ty, tx;
-  trapezoid_decode(me.task, nt, ty, tx);
+  trapezoid_decode(tile, nt, ty, tx);
   const bool probe = E.dbg && me.clique == E.dbg_child && threadIdx.x == 0 && (me.task == 0 || me.task == 77);
   long long t0 = 0, g0 = 0;
   if (probe) { t0 = clock64(); asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g0)); }
   // a root's trailing block is the 1 x 1 constant term: nothing reads it
-  if (!(E.debug & 1) && ci.parent >= 0) tile_update(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
+  if (!(E.debug & 1) && ci.parent >= 0) {
+    const int nchunk = (F + NB - 1) / NB;
+    const int ka = nsplit <= 1 ? 0 : (int)((int64_t)nchunk * slice / nsplit) * NB;
+    const int kend = nsplit <= 1 ? F : min(F, (int)((int64_t)nchunk * (slice + 1) / nsplit) * NB);
+    if (ci.flags & kCliqueFuseUp) {
+      const CliqueDev cp = E.cliques[ci.parent];
+      tile_update<2>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm, E.pmap + ci.pmap_off, E.arena + cp.front_off, cp.ld, F,
+                     slice == 0);
+    } else if (nsplit <= 1) {
+      tile_update<0>(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
+    } else {
+      tile_update<1>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm);
+    }
+  }
   if (probe) {
     long long g1;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g1));
@@ -1074,7 +1221,7 @@ __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const Ste
     E.dbg[o] = clock64() - t0;
     E.dbg[o + 1] = g1 - g0;
   }
-  if (me.task == 0) copy_diag_block(A, ld, F, E.dfac + ci.dfac_off, (F + PW - 1) / PW - 1, threadIdx.x);
+  if (tile == 0 && slice == 0) copy_diag_block(A, ld, F, E.dfac + ci.dfac_off, (F + PW - 1) / PW - 1, threadIdx.x);
 }
 
 // ----------------------------------------------------------------------------------------------------

@@ -86,6 +86,9 @@ struct LevelSched {
   std::vector<int32_t> step_count;
   std::vector<int64_t> schur_begin; // per step: tile tasks of the cliques whose Schur-complement step this is
   std::vector<int32_t> schur_count;
+  // Schur complement of this level's point cliques, gathered per camera pair (point_pair_kernel / point_diag_kernel)
+  int64_t pair_seg_begin = 0, diag_seg_begin = 0;
+  int32_t n_pair_seg = 0, n_diag_seg = 0;
 };
 
 }  // namespace gtb
@@ -138,6 +141,7 @@ struct gtb_engine {
   std::vector<int32_t> ld;            // per clique: leading dimension of its front storage (point fronts keep 3 rows: ld = 4)
   std::vector<int32_t> top_list;
   std::vector<uint8_t> is_point;      // per clique: handled by point_front_kernel (star structure, large parent)
+  std::vector<uint8_t> fuse_up;       // per clique: large front whose Schur step adds its Schur complement into the parent itself
   std::vector<int32_t> large_list;    // every large front this rank touches: its own (phase 0) first, then the top
   int32_t n_large_own = 0;
   int64_t top_off = 0, top_doubles = 0, arena_doubles = 0, top_work_begin = 0, top_zero_blocks = 0;
@@ -145,6 +149,10 @@ struct gtb_engine {
   std::vector<int32_t> bs_list, bs_scratch_off;
   int64_t bs_scratch_doubles = 0;
   std::vector<StepTask> step_tasks_list;
+  bool point_pairs = true;            // false (GTB_POINT_ATOMIC=1): point cliques scatter their Schur complement with atomics
+  std::vector<PairSeg> pair_segs;     // segments of both kinds, both phases
+  std::vector<uint2> pair_items;
+  std::vector<uint32_t> diag_items;   // 3 words per item
 
   // ---- device ----
   DevBuf<double> d_state[2][4];
@@ -170,6 +178,9 @@ struct gtb_engine {
   DevBuf<uint8_t> d_own_mask;
   DevBuf<ChildWork> d_child_work;
   DevBuf<StepTask> d_step_tasks;
+  DevBuf<PairSeg> d_pair_segs;
+  DevBuf<uint2> d_pair_items;
+  DevBuf<uint32_t> d_diag_items;
   DevBuf<long long> d_dbg;
   bool linearized = false, factorized = false, solved = false, have_hdiag = false;
 
@@ -316,10 +327,10 @@ struct StageTimer {
 };
 
 // kernel classes for launch counting and optional per-launch event timing
-enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_POINT, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
+enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_POINT, K_PAIR, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
        K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
-                                          "small_front", "thin_front", "point_front", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
+                                          "small_front", "thin_front", "point_front", "point_schur", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
                                           "backsolve", "backsolve_gemv", "retract", "own_delta"};
 
 static void prof_begin(Engine* e, int k) {
@@ -592,6 +603,7 @@ static void push_child_work(Engine* e, int32_t ch) {
   const Plan& pp = e->plan;
   const int32_t par = pp.parent[ch];
   if (is_fused_child(pp.F[ch], pp.F[ch] + pp.S[ch] + 1, pp.F[par], pp.F[par] + pp.S[par] + 1)) return;   // added by the child itself
+  if (e->fuse_up[ch]) return;                                                                             // ... by its Schur step
   const int32_t S1 = e->plan.S[ch] + 1;
   const int32_t nchunk = std::max(1, std::min(64, (int32_t)(((int64_t)S1 * S1 / 2) / 8192)));
   int32_t c0 = 0;
@@ -770,12 +782,24 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
           }
         L.step_count.push_back((int32_t)(e->step_tasks_list.size() - L.step_begin.back()));
         L.schur_begin.push_back((int64_t)e->step_tasks_list.size());
+        // a launch with fewer tiles than the machine holds (2 CTAs per SM) splits K = F over several CTAs per tile
+        int64_t launch_tiles = 0;
+        for (int64_t q = L.large_begin; q < en; ++q) {
+          const int32_t c = lc[q];
+          if (sidx == (p.F[c] + PW - 1) / PW) launch_tiles += step_tasks(p.F[c], p.F[c] + p.S[c] + 1, sidx);
+        }
+        static const int split_target = getenv("GTB_SCHUR_SPLIT") ? atoi(getenv("GTB_SCHUR_SPLIT")) : 2 * 148;
         for (int64_t q = L.large_begin; q < en; ++q) {
           const int32_t c = lc[q];
           const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
           if (sidx != np_c) continue;
           const int n = step_tasks(F, dim, sidx);
-          for (int t = 0; t < n; ++t) e->step_tasks_list.push_back(StepTask{c, t});
+          need(n < (1 << kSchurTileBits), "Schur-step tile count overflow");
+          int nsplit = 1;
+          if (launch_tiles > 0 && launch_tiles < split_target)
+            nsplit = (int)std::max<int64_t>(1, std::min<int64_t>({(split_target + launch_tiles - 1) / launch_tiles, F / 128, 31}));
+          for (int sl = 0; sl < nsplit; ++sl)
+            for (int t = 0; t < n; ++t) e->step_tasks_list.push_back(StepTask{c, schur_task(t, sl, nsplit)});
         }
         L.schur_count.push_back((int32_t)(e->step_tasks_list.size() - L.schur_begin.back()));
       }
@@ -873,6 +897,93 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
   }
 }
 
+// Stable LSD radix sort of records by a 64-bit key (11-bit digits, passes whose digit is constant are skipped).
+template <class R> static void radix_sort_by_key(std::vector<R>& v) {
+  if (v.size() < 2) return;
+  std::vector<R> tmp(v.size());
+  uint64_t all_or = 0, all_and = ~0ull;
+  for (const R& r : v) { all_or |= r.key; all_and &= r.key; }
+  const uint64_t varying = all_or & ~all_and;
+  for (int shift = 0; shift < 64; shift += 11) {
+    if (!((varying >> shift) & 0x7ff)) continue;
+    size_t cnt[2049] = {0};
+    for (const R& r : v) cnt[((r.key >> shift) & 0x7ff) + 1]++;
+    for (int i = 0; i < 2048; ++i) cnt[i + 1] += cnt[i];
+    for (const R& r : v) tmp[cnt[(r.key >> shift) & 0x7ff]++] = r;
+    v.swap(tmp);
+  }
+}
+
+// Camera-pair lists for the Schur complement of the point cliques (eliminate.cuh, point_pair_kernel): for every level
+// and phase, the (parent, block row, block column) groups of all its point cliques, items in list order, cut into
+// segments of at most kPairSeg items, longest segments first.
+static void build_point_pairs(Engine* e) {
+  const Plan& p = e->plan;
+  e->pair_segs.clear();
+  e->pair_items.clear();
+  e->diag_items.clear();
+  if (!e->point_pairs) return;
+  struct OffRec { uint64_t key; uint32_t a, b; };
+  struct DiagRec { uint64_t key; uint32_t y, fac, rhs; };
+  std::vector<OffRec> off;
+  std::vector<DiagRec> dg;
+  for (int ph = 0; ph < 2; ++ph)
+    for (int32_t l = 0; l < p.n_levels; ++l) {
+      LevelSched& L = e->sched[ph][l];
+      off.clear();
+      dg.clear();
+      for (const auto& cl : L.small) {
+        if (cl.kind != 3) continue;
+        for (int64_t q = cl.begin; q < cl.begin + cl.count; ++q) {
+          const int32_t c = e->sched_lists[q], P = p.parent[c];
+          const int k = p.S[c] / 9;
+          const int32_t* pm = p.pmap.data() + p.pmap_off[c];
+          need(e->front_off[c] % 4 == 0 && e->front_off[c] / 4 + 4 + 9 * k < (int64_t)0x7fffffff, "point front offset out of range");
+          need(P < (1 << 22) && pm[9 * k] < (1 << 21), "point pair key overflow");
+          const uint32_t base = (uint32_t)(e->front_off[c] / 4) + 3;   // first separator column, 32-byte units
+          const uint32_t rhs = base + 9 * k;
+          uint32_t fac_of[32];
+          for (int64_t f = p.fac_off[c]; f < p.fac_off[c + 1]; ++f) fac_of[(p.slots[f].col0 - 3) / 9] = (uint32_t)e->g_index[p.slots[f].factor];
+          for (int b1 = 0; b1 < k; ++b1) {
+            const uint64_t A = (uint64_t)pm[9 * b1];
+            dg.push_back(DiagRec{((uint64_t)P << 42) | (A << 21), base + 9 * b1, fac_of[b1], rhs | (b1 == 0 ? 0x80000000u : 0u)});
+            for (int b2 = b1 + 1; b2 < k; ++b2) {
+              const uint64_t B = (uint64_t)pm[9 * b2];
+              if (A < B) off.push_back(OffRec{((uint64_t)P << 42) | (A << 21) | B, base + 9 * b1, base + 9 * b2});
+              else off.push_back(OffRec{((uint64_t)P << 42) | (B << 21) | A, base + 9 * b2, base + 9 * b1});
+            }
+          }
+        }
+      }
+      if (dg.empty()) continue;
+      radix_sort_by_key(off);
+      radix_sort_by_key(dg);
+      auto emit = [&](auto& recs, bool diag, int64_t& seg_begin, int32_t& n_seg) {
+        std::vector<PairSeg> segs;
+        const int64_t item0 = diag ? (int64_t)e->diag_items.size() / 3 : (int64_t)e->pair_items.size();
+        for (size_t i = 0; i < recs.size();) {
+          size_t j = i;
+          while (j < recs.size() && recs[j].key == recs[i].key) ++j;
+          const int32_t P = (int32_t)(recs[i].key >> 42), A = (int32_t)((recs[i].key >> 21) & 0x1fffff), B = (int32_t)(recs[i].key & 0x1fffff);
+          const int32_t ldp = e->ld[P], NP = p.F[P] + p.S[P];
+          const int64_t dst = e->front_off[P] + A + (int64_t)(diag ? A : B) * ldp;
+          for (size_t s0 = i; s0 < j; s0 += kPairSeg)
+            segs.push_back(PairSeg{dst, ldp, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(kPairSeg, j - s0), NP - A});
+          i = j;
+        }
+        need(item0 + (int64_t)recs.size() < INT32_MAX, "point pair list overflow");
+        std::stable_sort(segs.begin(), segs.end(), [](const PairSeg& x, const PairSeg& y) { return x.count > y.count; });
+        seg_begin = (int64_t)e->pair_segs.size();
+        n_seg = (int32_t)segs.size();
+        e->pair_segs.insert(e->pair_segs.end(), segs.begin(), segs.end());
+      };
+      emit(off, false, L.pair_seg_begin, L.n_pair_seg);
+      for (const OffRec& r : off) e->pair_items.push_back(make_uint2(r.a, r.b));
+      emit(dg, true, L.diag_seg_begin, L.n_diag_seg);
+      for (const DiagRec& r : dg) { e->diag_items.push_back(r.y); e->diag_items.push_back(r.fac); e->diag_items.push_back(r.rhs); }
+    }
+}
+
 static void install_plan(Engine* e) {
   const Plan& p = e->plan;
   const int32_t C = p.n_cliques;
@@ -888,11 +999,42 @@ static void install_plan(Engine* e) {
     if (par >= 0 && is_fused_child(p.F[c], p.F[c] + p.S[c] + 1, p.F[par], p.F[par] + p.S[par] + 1) && is_star_clique(e, c, 22))
       e->is_point[c] = 1;
   }
+  // a large child of a large parent on the same rank and phase adds its Schur complement during its own Schur step
+  {
+    const char* fu = getenv("GTB_FUSE_UP");
+    const bool on = !(fu && !atoi(fu));
+    e->fuse_up.assign(C, 0);
+    for (int32_t c = 0; c < C && on; ++c) {
+      const int32_t par = p.parent[c];
+      if (par < 0 || is_small_front(p.F[c], p.F[c] + p.S[c] + 1) || is_small_front(p.F[par], p.F[par] + p.S[par] + 1)) continue;
+      if (e->owner[c] == e->owner[par]) e->fuse_up[c] = 1;
+    }
+  }
   std::vector<int32_t> lc;
   lc.reserve(C);
   build_phase(e, 0, lc);
   build_phase(e, 1, lc);
   e->sched_lists = lc;
+  if (getenv("GTB_DUMP_SCHED")) {   // the large-front schedule, one line per level and per Schur-step launch
+    for (int ph = 0; ph < 2; ++ph)
+      for (int32_t l = 0; l < p.n_levels; ++l) {
+        const LevelSched& L = e->sched[ph][l];
+        if (!L.n_large) continue;
+        fprintf(stderr, "phase %d level %d: %d large fronts:", ph, l, L.n_large);
+        for (int64_t q = L.large_begin; q < L.large_begin + L.n_large; ++q) fprintf(stderr, " (F=%d S=%d)", p.F[lc[q]], p.S[lc[q]]);
+        fprintf(stderr, "\n");
+        for (size_t sx = 0; sx < L.step_count.size(); ++sx)
+          if (L.schur_count[sx]) {
+            double fl = 0;
+            for (int64_t q = L.large_begin; q < L.large_begin + L.n_large; ++q) {
+              const int32_t c = lc[q];
+              if ((int)sx == (p.F[c] + PW - 1) / PW) fl += (double)p.F[c] * (p.S[c] + 1) * (p.S[c] + 2);
+            }
+            fprintf(stderr, "  schur launch after step %zu: %d CTAs, %.3f GFLOP (%.1f us at 35 TF/s); panel-step CTAs before it: %d\n", sx, L.schur_count[sx], fl / 1e9,
+                    fl / 35e6, sx > 0 ? L.step_count[sx - 1] : 0);
+          }
+      }
+  }
   // the shared top: fronts relocated to one contiguous tail of the arena (identical on every rank) so that the fan-in
   // is a single reduction; assembled before it from own factors (rank 0) and from the subtree children each rank owns
   // Front storage.  The plan's layout gives every clique a full (N+1)^2 front; a point front only ever stores its three
@@ -921,6 +1063,11 @@ static void install_plan(Engine* e) {
       e->top_zero_blocks = std::max<int64_t>(e->top_zero_blocks, (sz / 2 + 255) / 256);
     }
   e->top_zero_blocks = std::min<int64_t>(e->top_zero_blocks, 64);
+  {
+    const char* pa = getenv("GTB_POINT_ATOMIC");
+    e->point_pairs = !(pa && atoi(pa));
+  }
+  build_point_pairs(e);
   e->large_list.clear();
   for (int32_t c = 0; c < C; ++c)
     if (e->owner[c] == e->rank && !is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) e->large_list.push_back(c);
@@ -954,7 +1101,7 @@ static void install_plan(Engine* e) {
     d.first_key_var = p.vars[p.vars_off[c]];
     d.dfac_off = 0;
     d.pad = 0;
-    d.flags = is_star_clique(e, c, 15) ? kCliqueStar : 0;
+    d.flags = (is_star_clique(e, c, 15) ? kCliqueStar : 0) | (e->fuse_up[c] ? kCliqueFuseUp : 0);
     if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
       dfac_total += (int64_t)((p.F[c] + PW - 1) / PW) * PW * PW;
@@ -980,6 +1127,9 @@ static void install_plan(Engine* e) {
   e->d_bs_scratch_off.upload(e->bs_scratch_off, st);
   e->d_bs_scratch.alloc((size_t)e->bs_scratch_doubles + 1);
   e->d_step_tasks.upload(e->step_tasks_list, st);
+  e->d_pair_segs.upload(e->pair_segs, st);
+  e->d_pair_items.upload(e->pair_items, st);
+  e->d_diag_items.upload(e->diag_items, st);
   e->d_dbg.alloc(16);
   e->d_fail.alloc(1);
   e->d_dfac.alloc((size_t)dfac_total + PW * PW);
@@ -1128,7 +1278,7 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
     for (const auto& c : L.small) {
       if (c.kind == 3)
         LAUNCH(e, K_POINT, point_front_kernel<<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
-                               E, lists + c.begin, c.count, c.group_doubles));
+                               E, lists + c.begin, c.count, c.group_doubles, e->point_pairs ? 0 : 1));
       else if (c.kind == 0)
         LAUNCH(e, K_THIN, thin_front_kernel<true><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
                               E, lists + c.begin, c.count, c.group_doubles));
@@ -1138,6 +1288,12 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
       else
         LAUNCH(e, K_SMALL, small_front_kernel<<<c.count, c.threads, c.smem, st>>>(E, lists + c.begin));
     }
+    if (L.n_pair_seg)
+      LAUNCH(e, K_PAIR, point_pair_kernel<<<(3 * L.n_pair_seg + 127) / 128, 128, 0, st>>>(E, e->d_pair_segs.p + L.pair_seg_begin, L.n_pair_seg,
+                                                                                          e->d_pair_items.p));
+    if (L.n_diag_seg)
+      LAUNCH(e, K_PAIR, point_diag_kernel<<<(4 * L.n_diag_seg + 127) / 128, 128, 0, st>>>(E, e->d_pair_segs.p + L.diag_seg_begin, L.n_diag_seg,
+                                                                                          e->d_diag_items.p));
     if (!L.n_large) continue;
     if (L.n_work) {
       LAUNCH(e, K_LCHILD, launch_pdl(large_children_kernel, L.n_work, 256, 0, st, E, e->d_child_work.p + L.work_begin));
