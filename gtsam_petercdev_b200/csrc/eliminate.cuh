@@ -544,6 +544,13 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
 // into segments whose partial sums meet in the parent through atomics (81 per segment instead of 81 per item).
 // ----------------------------------------------------------------------------------------------------
 constexpr int kPairSeg = 32;
+// one 32-byte column of a point front in a single request (LDG.256, read-only path)
+struct Col4 { double x, y, z, w; };
+__device__ __forceinline__ Col4 ld_col(const double* p) {
+  Col4 c;
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(c.x), "=d"(c.y), "=d"(c.z), "=d"(c.w) : "l"(p));
+  return c;
+}
 struct PairSeg { int64_t dst; int32_t ld; int32_t begin; int32_t count; int32_t ncol; };   // ncol: columns from the block to the parent's rhs column
 __global__ void __launch_bounds__(128) point_pair_kernel(ElimDev E, const PairSeg* __restrict__ segs, int nseg,
                                                          const uint2* __restrict__ items) {
@@ -557,19 +564,16 @@ __global__ void __launch_bounds__(128) point_pair_kernel(ElimDev E, const PairSe
   const double* arena = E.arena;
   for (int q = sg.begin; q < sg.begin + sg.count; ++q) {
     const uint2 it = __ldg(items + q);
-    const double2* ya = reinterpret_cast<const double2*>(arena + (int64_t)it.x * 4);
-    const double2* yb = reinterpret_cast<const double2*>(arena + (int64_t)it.y * 4) + 6 * slab;
-    double b0[3], b1[3], b2[3];
+    const double* ya = arena + (int64_t)it.x * 4;
+    const double* yb = arena + (int64_t)it.y * 4 + 12 * slab;
+    Col4 b[3];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const double2 u = __ldg(yb + 2 * c), v = __ldg(yb + 2 * c + 1);
-      b0[c] = u.x; b1[c] = u.y; b2[c] = v.x;
-    }
+    for (int c = 0; c < 3; ++c) b[c] = ld_col(yb + 4 * c);
 #pragma unroll
     for (int i = 0; i < 9; ++i) {
-      const double2 u = __ldg(ya + 2 * i), v = __ldg(ya + 2 * i + 1);
+      const Col4 u = ld_col(ya + 4 * i);
 #pragma unroll
-      for (int c = 0; c < 3; ++c) acc[i][c] += u.x * b0[c] + u.y * b1[c] + v.x * b2[c];
+      for (int c = 0; c < 3; ++c) acc[i][c] += u.x * b[c].x + u.y * b[c].y + u.z * b[c].z;
     }
   }
   double* dst = E.arena + sg.dst + (int64_t)(3 * slab) * sg.ld;
@@ -595,35 +599,41 @@ __global__ void __launch_bounds__(128) point_diag_kernel(ElimDev E, const PairSe
   const double* Ab = E.Ab[2];
   for (int q = sg.begin; q < sg.begin + sg.count; ++q) {
     const uint32_t iy = __ldg(items + 3 * (int64_t)q), ifac = __ldg(items + 3 * (int64_t)q + 1), ir = __ldg(items + 3 * (int64_t)q + 2);
-    const double2* ya = reinterpret_cast<const double2*>(arena + (int64_t)iy * 4);
-    const double* f = Ab + (int64_t)ifac * 26;
+    const double* ya = arena + (int64_t)iy * 4;
+    // the factor's two rows [J_c (9) | J_p (3) | b]: 26 doubles, 16-byte aligned; J_c and b as 13 16-byte loads
+    const double2* f2 = reinterpret_cast<const double2*>(Ab + (int64_t)ifac * 26);
+    double r0[14], r1[14];   // r0[i] = f[i], r1[i] = f[13 + i - 1 + 1]: rows 0 and 1 (row 1 starts at the odd offset 13)
+#pragma unroll
+    for (int h = 0; h < 5; ++h) { const double2 v = __ldg(f2 + h); r0[2 * h] = v.x; r0[2 * h + 1] = v.y; }
+    { const double2 v = __ldg(f2 + 6); r0[12] = v.x; r1[0] = v.y; }   // f[12] = b_0, f[13] = J_c(1, 0)
+#pragma unroll
+    for (int h = 0; h < 4; ++h) { const double2 v = __ldg(f2 + 7 + h); r1[1 + 2 * h] = v.x; r1[2 + 2 * h] = v.y; }   // f[14..21]
+    const double br1 = __ldg(Ab + (int64_t)ifac * 26 + 25);
     if (slab < 3) {
-      double b0[3], b1[3], b2[3], j0[3], j1[3];
+      Col4 b[3];
+      double j0[3], j1[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const double2 u = __ldg(ya + 6 * slab + 2 * c), v = __ldg(ya + 6 * slab + 2 * c + 1);
-        b0[c] = u.x; b1[c] = u.y; b2[c] = v.x;
-        j0[c] = __ldg(f + 3 * slab + c); j1[c] = __ldg(f + 13 + 3 * slab + c);
+        b[c] = ld_col(ya + 12 * slab + 4 * c);
+        j0[c] = slab == 0 ? r0[c] : (slab == 1 ? r0[3 + c] : r0[6 + c]);
+        j1[c] = slab == 0 ? r1[c] : (slab == 1 ? r1[3 + c] : r1[6 + c]);
       }
 #pragma unroll
       for (int i = 0; i < 9; ++i) {
-        const double2 u = __ldg(ya + 2 * i), v = __ldg(ya + 2 * i + 1);
-        const double a0 = __ldg(f + i), a1 = __ldg(f + 13 + i);
+        const Col4 u = ld_col(ya + 4 * i);
 #pragma unroll
-        for (int c = 0; c < 3; ++c) acc[i][c] += (a0 * j0[c] + a1 * j1[c]) - (u.x * b0[c] + u.y * b1[c] + v.x * b2[c]);
+        for (int c = 0; c < 3; ++c) acc[i][c] += (r0[i] * j0[c] + r1[i] * j1[c]) - (u.x * b[c].x + u.y * b[c].y + u.z * b[c].z);
       }
     } else {
-      const double2* yr = reinterpret_cast<const double2*>(arena + (int64_t)(ir & 0x7fffffffu) * 4);
-      const double2 ru = __ldg(yr), rv = __ldg(yr + 1);
-      const double br0 = __ldg(f + 12), br1 = __ldg(f + 25);
+      const Col4 r = ld_col(arena + (int64_t)(ir & 0x7fffffffu) * 4);
+      const double br0 = r0[12];
 #pragma unroll
       for (int i = 0; i < 9; ++i) {
-        const double2 u = __ldg(ya + 2 * i), v = __ldg(ya + 2 * i + 1);
-        const double a0 = __ldg(f + i), a1 = __ldg(f + 13 + i);
-        acc[i][0] += (a0 * br0 + a1 * br1) - (u.x * ru.x + u.y * ru.y + v.x * rv.x);
+        const Col4 u = ld_col(ya + 4 * i);
+        acc[i][0] += (r0[i] * br0 + r1[i] * br1) - (u.x * r.x + u.y * r.y + u.z * r.z);
       }
       cst += br0 * br0 + br1 * br1;
-      if (ir >> 31) cst -= ru.x * ru.x + ru.y * ru.y + rv.x * rv.x;
+      if (ir >> 31) cst -= r.x * r.x + r.y * r.y + r.z * r.z;
     }
   }
   if (slab < 3) {
@@ -733,7 +743,8 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 constexpr int kStages = 3;
 // MODE 0: C -= product in place.  MODE 1: the same through atomics (K split over several CTAs).  MODE 2: the updated tile
 // (C itself only when add_c: one K slice carries it) is added into the parent front PA through the child -> parent
-// column map pm instead: the extend-add of a large child fused into its Schur-complement step.
+// column map pm instead: the extend-add of a large child fused into its Schur-complement step (a plain read-modify-write
+// for an only child measured 10 % slower than the atomics).
 template <int MODE = 0>
 __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int dim, int r0, int c0, int re, int ka,
                                             int kend, double* sm, const int32_t* __restrict__ pm = nullptr,
@@ -870,14 +881,18 @@ __device__ __noinline__ bool potrf32_warp(double* Dh, double* dinv_h, double* Ws
     d[k] *= rinv;                       // lane == k: pk * rinv = sqrt(pk); lanes < k: unused
     if (lane == k) myinv = rinv;
     const double ukl = d[k];
-    rb[lane] = ukl;
-    __syncwarp();
+    // The next pivot D(k+1, k+1) - R(k, k+1)^2 lives entirely in lane k+1 (its own ukl IS R(k, k+1)): the dependent chain
+    // pivot -> rsqrt -> scale -> update -> shuffle never goes through the shared-memory row broadcast, which only feeds
+    // the rest of the rank-1 update.  (A 4-pass body rotated through registers to fit the instruction cache measured
+    // 15 % slower: the chain, not instruction fetch, sets the time.)
     double pk_next = 1.0, rinv_next = 1.0;
     if (k + 1 < NB) {
-      d[k + 1] -= rb[k + 1] * ukl;
-      pk_next = __shfl_sync(0xffffffffu, d[k + 1], k + 1);
+      pk_next = __shfl_sync(0xffffffffu, d[k + 1] - ukl * ukl, k + 1);
       rinv_next = rsqrt(pk_next);
     }
+    rb[lane] = ukl;
+    __syncwarp();
+    if (k + 1 < NB) d[k + 1] -= rb[k + 1] * ukl;
 #pragma unroll
     for (int i = k + 2; i < NB; ++i) d[i] -= rb[i] * ukl;
     pk = pk_next;
@@ -1230,6 +1245,7 @@ __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const Ste
 // WARP = false: one CTA per clique; blocked TRSV, 32 pivots per step, diagonal block solved by warp 0 in registers
 // ----------------------------------------------------------------------------------------------------
 constexpr int kBsWarps = 8;
+constexpr int kBsCtaThreads = 512;
 constexpr int kBsWarpDoubles = 32 + 160 + 32;   // rhs, xs, reduction scratch per warp
 
 // S x_S for CTA-class cliques, spread over many CTAs: blockIdx.x = clique slot, y = 128-row block, z = 128-column
@@ -1279,7 +1295,7 @@ backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t
 }
 
 template <bool WARP>
-__global__ void __launch_bounds__(WARP ? kBsWarps * 32 : 512)
+__global__ void __launch_bounds__(WARP ? kBsWarps * 32 : kBsCtaThreads)
 backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta,
                  const int32_t* __restrict__ scratch_off, const double* __restrict__ scratch) {
   extern __shared__ double sh[];
@@ -1352,77 +1368,117 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
     }
   }
   gsync();
-  // blocked back-substitution with R (upper triangular), bottom block first.  CTA variant: the next diagonal block is
-  // fetched into shared memory by the whole CTA while the current block's update runs, and every row issues its 32
-  // loads of the update before the first multiply (the loop is latency-bound: one SM streams R once).
-  double* dblk = xblk + 32;   // CTA only: dblk[k * 33 + l] = R(b0 + l, b0 + k)
-  if (!WARP) {
-    const int b0 = ((F - 1) / 32) * 32, kb = F - b0;
-    for (int q = gtid; q < 1024; q += gsize) {
-      const int k = q >> 5, l = q & 31;
-      dblk[k * 33 + l] = (k < kb && l <= k) ? A[(b0 + l) + (int64_t)(b0 + k) * ld] : 1.0;
-    }
-    __syncthreads();
-  }
-  for (int b0 = ((F - 1) / 32) * 32; b0 >= 0; b0 -= 32) {
-    const int kb = min(32, F - b0);
-    if (WARP || warp == 0) {
-      double r[32];
+  // blocked back-substitution with R (upper triangular), bottom block first
+  if (WARP) {
+    // F <= 32: a single block
+    const int kb = F;
+    double r[32];
 #pragma unroll
-      for (int k = 0; k < 32; ++k) {
-        if (WARP) r[k] = (k < kb && lane <= k && lane < kb) ? A[(b0 + lane) + (int64_t)(b0 + k) * ld] : 1.0;
-        else r[k] = dblk[k * 33 + lane];
+    for (int k = 0; k < 32; ++k) r[k] = (k < kb && lane <= k && lane < kb) ? A[lane + (int64_t)k * ld] : 1.0;
+    double my = (lane < kb) ? rhs[lane] : 0.0;
+    // reciprocal of this lane's diagonal entry: one division per lane instead of a chain of 32
+    double dg = 1.0;
+#pragma unroll
+    for (int k = 0; k < 32; ++k)
+      if (k == lane) dg = r[k];
+    const double rd = 1.0 / dg;
+#pragma unroll
+    for (int k = 31; k >= 0; --k) {
+      if (k < kb) {
+        const double xk = __shfl_sync(0xffffffffu, my, k) * __shfl_sync(0xffffffffu, rd, k);
+        if (lane == k) my = xk;
+        else if (lane < k) my -= r[k] * xk;
       }
-      double my = (lane < kb) ? rhs[b0 + lane] : 0.0;
-      // reciprocal of this lane's diagonal entry: one division per lane instead of a chain of 32
-      double dg = 1.0;
+    }
+    if (lane < kb) rhs[lane] = my;
+  } else {
+    // CTA variant, software-pipelined over the 32-row blocks: ONE barrier per block.  Warp 0 walks the dependent chain
+    // alone: solve block b in registers, publish x_b, and fold x_b's contribution to block b-1 (the 32 x 32 block
+    // R[b-1, b], prefetched into registers before the solve) into its next right-hand side itself.  The other warps run
+    // one block behind: after the barrier they apply x_b to every row above block b-1 (32 loads in flight per row) and
+    // stage the diagonal block warp 0 needs two steps later, while warp 0 is already solving block b-1.  A row's sum
+    // still runs over the blocks in descending order, as in the plain right-looking loop.
+    double* xbuf = xblk;             // [2][32]: x of the block just solved (double-buffered)
+    double* dblk = xblk + 64;        // [2][32 * 33]: dblk[k * 33 + l] = R(b0 + l, b0 + k) of the block to solve
+    const int nb = (F + 31) / 32;
+    auto stage_diag = [&](int bq, int t0, int nt) {   // diagonal block bq -> dblk[bq & 1], by threads t0 .. t0 + nt - 1
+      const int q0 = bq * 32, kq = min(32, F - q0);
+      double* dst = dblk + (bq & 1) * (32 * 33);
+      for (int q = gtid - t0; q < 1024; q += nt) {
+        const int k = q >> 5, l = q & 31;
+        dst[k * 33 + l] = (k < kq && l <= k) ? A[(q0 + l) + (int64_t)(q0 + k) * ld] : 1.0;
+      }
+    };
+    stage_diag(nb - 1, 0, gsize);
+    if (nb >= 2) stage_diag(nb - 2, 0, gsize);
+    __syncthreads();
+    double carry = 0.0;   // warp 0: (R[b, b+1] x_{b+1})(lane)
+    for (int bi = nb - 1; bi >= 0; --bi) {
+      const int b0 = bi * 32, kb = min(32, F - b0);
+      double w[32];       // warp 0: R[b-1, b], row b0 - 32 + lane; other warps: their first row of this block's update.
+                          // Loaded before the solve / the barrier: in flight while warp 0 solves block b.
+      const int i1 = warp == 0 ? b0 - 32 + lane : gtid - 32;
+      const bool have = warp == 0 ? bi >= 1 : i1 < b0 - 32;
+      {
+        const double* row = A + (have ? i1 : 0) + (int64_t)b0 * ld;
 #pragma unroll
-      for (int k = 0; k < 32; ++k)
-        if (k == lane) dg = r[k];
-      const double rd = 1.0 / dg;
+        for (int k = 0; k < 32; ++k) w[k] = (have && k < kb) ? row[(int64_t)k * ld] : 0.0;
+      }
+      if (warp == 0) {
+        const double* db = dblk + (bi & 1) * (32 * 33);
+        double my = (lane < kb) ? rhs[b0 + lane] - carry : 0.0;
+        const double rd = 1.0 / db[lane * 33 + lane];   // reciprocal of this lane's diagonal entry (1.0 on the padding)
+        double rk = db[31 * 33 + lane];
 #pragma unroll
-      for (int k = 31; k >= 0; --k) {
-        if (k < kb) {
-          const double xk = __shfl_sync(0xffffffffu, my, k) * __shfl_sync(0xffffffffu, rd, k);
-          if (lane == k) my = xk;
-          else if (lane < k) my -= r[k] * xk;
+        for (int k = 31; k >= 0; --k) {
+          const double rk_next = db[(k > 0 ? k - 1 : 0) * 33 + lane];   // one step ahead of its use
+          if (k < kb) {
+            const double xk = __shfl_sync(0xffffffffu, my, k) * __shfl_sync(0xffffffffu, rd, k);
+            if (lane == k) my = xk;
+            else if (lane < k) my -= rk * xk;
+          }
+          rk = rk_next;
         }
-      }
-      if (lane < kb) rhs[b0 + lane] = my;
-      if (!WARP) xblk[lane] = (lane < kb) ? my : 0.0;
-    }
-    if (WARP) break;   // F <= 32: single block
-    __syncthreads();
-    // next diagonal block (full: only the bottom block can be ragged)
-    double dn[2] = {1.0, 1.0};
-    if (b0 >= 32) {
+        if (lane < kb) rhs[b0 + lane] = my;
+        double* xb = xbuf + (bi & 1) * 32;
+        xb[lane] = (lane < kb) ? my : 0.0;
+        __syncwarp();
+        double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int q = gtid + h * gsize, k = q >> 5, l = q & 31;
-        if (q < 1024 && l <= k) dn[h] = A[(b0 - 32 + l) + (int64_t)(b0 - 32 + k) * ld];
+        for (int k = 0; k < 32; k += 2) {
+          a0 += w[k] * xb[k];
+          a1 += w[k + 1] * xb[k + 1];
+        }
+        carry = a0 + a1;
+      }
+      __syncthreads();   // x_b is published; the other warps have finished applying x_{b+1} and staging block b-1
+      if (warp > 0) {
+        const double* xb = xbuf + (bi & 1) * 32;
+        if (have) {
+          double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+          for (int k = 0; k < 32; k += 2) {
+            a0 += w[k] * xb[k];
+            a1 += w[k + 1] * xb[k + 1];
+          }
+          rhs[i1] -= a0 + a1;
+        }
+        for (int i = i1 + gsize - 32; i < b0 - 32; i += gsize - 32) {
+          const double* row = A + i + (int64_t)b0 * ld;
+          double u[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) u[k] = (k < kb) ? row[(int64_t)k * ld] : 0.0;
+          double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+          for (int k = 0; k < 32; k += 2) {
+            a0 += u[k] * xb[k];
+            a1 += u[k + 1] * xb[k + 1];
+          }
+          rhs[i] -= a0 + a1;
+        }
+        if (bi >= 2) stage_diag(bi - 2, 32, gsize - 32);   // into the buffer of block b, which warp 0 has left
       }
     }
-    for (int i = gtid; i < b0; i += gsize) {
-      const double* row = A + i + (int64_t)b0 * ld;
-      double v[32];
-#pragma unroll
-      for (int k = 0; k < 32; ++k) v[k] = (k < kb) ? row[(int64_t)k * ld] : 0.0;
-      double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-      for (int k = 0; k < 32; k += 2) {
-        a0 += v[k] * xblk[k];
-        a1 += v[k + 1] * xblk[k + 1];
-      }
-      rhs[i] -= a0 + a1;
-    }
-    if (b0 >= 32) {   // nobody reads dblk between the two barriers (warp 0 took its copy before the first one)
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int q = gtid + h * gsize;
-        if (q < 1024) dblk[(q >> 5) * 33 + (q & 31)] = dn[h];
-      }
-    }
-    __syncthreads();
   }
   gsync();
   for (int i = gtid; i < F; i += gsize) delta[g[i]] = rhs[i];

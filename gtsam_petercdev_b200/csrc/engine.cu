@@ -841,7 +841,7 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       need(off < INT32_MAX, "back-substitution scratch overflow");
       e->bs_scratch_doubles = std::max(e->bs_scratch_doubles, off);
     }
-    L.bs_cta_smem = (maxN + 512 + 32 + 32 * 33) * (int32_t)sizeof(double);
+    L.bs_cta_smem = (maxN + kBsCtaThreads + 64 + 2 * 32 * 33) * (int32_t)sizeof(double);
 
     // re-sort the small part of the level by dimension and cut into thread classes
     auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
@@ -972,7 +972,13 @@ static void build_point_pairs(Engine* e) {
           i = j;
         }
         need(item0 + (int64_t)recs.size() < INT32_MAX, "point pair list overflow");
-        std::stable_sort(segs.begin(), segs.end(), [](const PairSeg& x, const PairSeg& y) { return x.count > y.count; });
+        // Longest first, but only inside windows of the key order: neighbouring groups share a camera, so its points'
+        // conditional rows stay in L2 across them, while the warps of a window still get segments of similar length.
+        static const int64_t window = getenv("GTB_PAIR_WINDOW") ? atoll(getenv("GTB_PAIR_WINDOW")) : 4096;
+        for (size_t w0 = 0; w0 < segs.size(); w0 += (window > 0 ? (size_t)window : segs.size())) {
+          const size_t w1 = window > 0 ? std::min(segs.size(), w0 + (size_t)window) : segs.size();
+          std::stable_sort(segs.begin() + w0, segs.begin() + w1, [](const PairSeg& x, const PairSeg& y) { return x.count > y.count; });
+        }
         seg_begin = (int64_t)e->pair_segs.size();
         n_seg = (int32_t)segs.size();
         e->pair_segs.insert(e->pair_segs.end(), segs.begin(), segs.end());
@@ -1390,7 +1396,7 @@ static void backsolve_levels(Engine* e, const ElimDev& E, int phase) {
                                        dim3(L.n_bs_cta, (L.bs_max_F + kGemvRows - 1) / kGemvRows, (L.bs_max_S + kGemvCols - 1) / kGemvCols),
                                        kGemvRows, 0, e->stream, E, bl + L.n_bs_warp, so + L.n_bs_warp, (const double*)e->d_delta.p,
                                        e->d_bs_scratch.p));
-      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<false>, L.n_bs_cta, 512, L.bs_cta_smem, e->stream, E, bl + L.n_bs_warp,
+      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<false>, L.n_bs_cta, kBsCtaThreads, L.bs_cta_smem, e->stream, E, bl + L.n_bs_warp,
                                         L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, (const double*)e->d_bs_scratch.p));
     }
   }
