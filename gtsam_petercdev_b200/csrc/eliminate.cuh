@@ -412,8 +412,10 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
 // goes straight into the parent front through the child -> parent column map (FP64 atomics).  One warp per point,
 // 2.4 KB of shared memory per warp at k = 5 instead of 13 KB: four times the warps in flight of the generic thin kernel.
 // ----------------------------------------------------------------------------------------------------
-__host__ __device__ __forceinline__ int point_front_doubles(int kmax) {
+constexpr int kPointMaxCams = 64;   // most cameras of a point clique on the point path (pair-gathered Schur complement)
+__host__ __device__ __forceinline__ int point_front_doubles(int kmax, bool schur) {
   const int nmax = 9 * kmax + 1;
+  if (!schur) return 26 * kmax + ((2 * kmax + 2) >> 1) + 2;                       // ab | scol, sfac (ints) | pad
   return 26 * kmax + 3 * nmax + ((nmax + 2) >> 1) + ((2 * kmax + 2) >> 1) + 2;   // ab | Y | pm (ints) | scol, sfac (ints) | pad
 }
 __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count,
@@ -423,10 +425,10 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
   const int slot = blockIdx.x * kThinWarps + warp;
   if (slot >= count) return;
   const int nmax = 9 * kmax + 1;
-  double* ab = sh + warp * point_front_doubles(kmax);   // ab[26 s + 13 r + col]: rows of factor s
-  double* Y = ab + 26 * kmax;                           // Y[a * nmax + j] = y_j[a]
+  double* ab = sh + warp * point_front_doubles(kmax, schur != 0);   // ab[26 s + 13 r + col]: rows of factor s
+  double* Y = ab + 26 * kmax;                           // Y[a * nmax + j] = y_j[a]   (Y and pm_s only when schur)
   int* pm_s = reinterpret_cast<int*>(Y + 3 * nmax);     // parent column of separator scalar q (and of the rhs)
-  int* scol = pm_s + ((nmax + 2) & ~1);                 // separator-relative first column of factor s's camera
+  int* scol = schur ? pm_s + ((nmax + 2) & ~1) : reinterpret_cast<int*>(Y);   // separator-relative first column of factor s's camera
   int* sfac = scol + kmax;                              // camera block index -> factor
   const int c = list[slot];
   const CliqueDev ci = E.cliques[c];
@@ -438,7 +440,8 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
     ab[t] = E.Ab[2][(int64_t)sl.index * 26 + r];
     if (r == 0) { scol[s] = sl.col0 - 3; sfac[(sl.col0 - 3) / 9] = s; }
   }
-  for (int q = lane; q < n; q += 32) pm_s[q] = E.pmap[ci.pmap_off + q];
+  if (schur)
+    for (int q = lane; q < n; q += 32) pm_s[q] = E.pmap[ci.pmap_off + q];
   __syncwarp();
   // frontal block and its right-hand side, factors in gather order (deterministic sums); every lane keeps a copy
   double v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0, g0 = 0, g1 = 0, g2 = 0, bb = 0;
@@ -495,7 +498,7 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
     const double y0 = w0 * d0;
     const double y1 = (w1 - r01 * y0) * d1;
     const double y2 = (w2 - r02 * y0 - r12 * y1) * d2;
-    Y[j] = y0; Y[nmax + j] = y1; Y[2 * nmax + j] = y2;
+    if (schur) { Y[j] = y0; Y[nmax + j] = y1; Y[2 * nmax + j] = y2; }
     double* col3 = dst + (int64_t)(3 + j) * ci.ld;
     col3[0] = y0; col3[1] = y1; col3[2] = y2;
   }

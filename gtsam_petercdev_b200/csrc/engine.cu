@@ -602,7 +602,7 @@ static void finalize_problem(Engine* e) {
 static void push_child_work(Engine* e, int32_t ch) {
   const Plan& pp = e->plan;
   const int32_t par = pp.parent[ch];
-  if (is_fused_child(pp.F[ch], pp.F[ch] + pp.S[ch] + 1, pp.F[par], pp.F[par] + pp.S[par] + 1)) return;   // added by the child itself
+  if (is_fused_child(pp.F[ch], pp.F[ch] + pp.S[ch] + 1, pp.F[par], pp.F[par] + pp.S[par] + 1) || e->is_point[ch]) return;   // added by the child itself
   if (e->fuse_up[ch]) return;                                                                             // ... by its Schur step
   const int32_t S1 = e->plan.S[ch] + 1;
   const int32_t nchunk = std::max(1, std::min(64, (int32_t)(((int64_t)S1 * S1 / 2) / 8192)));
@@ -720,10 +720,10 @@ static void compute_partition(const Plan& p, int world, std::vector<int32_t>& ow
 
 // A point eliminated alone, every factor a projection (bucket 2) from a distinct camera, at most kmax of them
 // (15: what the thin kernel's staging area holds; 22: the largest thin front, for the point kernel).
-static bool is_star_clique(const Engine* e, int32_t c, int kmax) {
+static bool is_star_clique(const Engine* e, int32_t c, int kmax, bool any_dim = false) {
   const Plan& p = e->plan;
   const int64_t f0 = p.fac_off[c], f1 = p.fac_off[c + 1];
-  bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= kmax && is_thin_front(p.F[c], p.F[c] + p.S[c] + 1) &&
+  bool star = p.F[c] == 3 && f1 > f0 && f1 - f0 <= kmax && (any_dim || is_thin_front(p.F[c], p.F[c] + p.S[c] + 1)) &&
               p.S[c] == 9 * (f1 - f0) && p.child_off[c + 1] == p.child_off[c];
   for (int64_t f = f0; star && f < f1; ++f) {
     const FactorSlot& fs = p.slots[f];
@@ -746,11 +746,15 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
     const int64_t pb = p.level_off[l], pns = p.level_n_small[l], pen = p.level_off[l + 1];
     const int64_t b = (int64_t)lc.size();
     int64_t ns = 0;
+    // (a point clique with more cameras than a thin front holds is large by its dimensions but runs on the point path)
+    auto small_q = [&](int64_t q) { return q < pb + pns || e->is_point[p.level_cliques[q]]; };
     for (int64_t q = pb; q < pen; ++q)
-      if (mine(p.level_cliques[q])) {
+      if (mine(p.level_cliques[q]) && small_q(q)) {
         lc.push_back(p.level_cliques[q]);
-        if (q < pb + pns) ++ns;
+        ++ns;
       }
+    for (int64_t q = pb; q < pen; ++q)
+      if (mine(p.level_cliques[q]) && !small_q(q)) lc.push_back(p.level_cliques[q]);
     const int64_t en = (int64_t)lc.size();
     L.n_all = (int32_t)(en - b);
     L.large_begin = b + ns;
@@ -818,7 +822,7 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
     for (int pass = 0; pass < 2; ++pass)
       for (int64_t q = b; q < en; ++q) {
         const int32_t c = lc[q];
-        const bool warp_class = p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kDenseMaxDim;
+        const bool warp_class = (p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kDenseMaxDim) || e->is_point[c];
         if (warp_class != (pass == 0)) continue;
         e->bs_list.push_back(c);
         if (warp_class) L.n_bs_warp++;
@@ -863,7 +867,7 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       LevelSched::Cls cl;
       cl.begin = q0; cl.count = (int32_t)(q - q0); cl.kind = 3; cl.threads = kThinWarps * 32;
       cl.group_doubles = mk;
-      cl.smem = point_front_doubles(mk) * (int32_t)sizeof(double) * kThinWarps;
+      cl.smem = point_front_doubles(mk, !e->point_pairs) * (int32_t)sizeof(double) * kThinWarps;
       L.small.push_back(cl);
     }
     // thin classes are cut adaptively so that the shared memory of a class (sized by its largest member) stays within
@@ -942,7 +946,7 @@ static void build_point_pairs(Engine* e) {
           need(P < (1 << 22) && pm[9 * k] < (1 << 21), "point pair key overflow");
           const uint32_t base = (uint32_t)(e->front_off[c] / 4) + 3;   // first separator column, 32-byte units
           const uint32_t rhs = base + 9 * k;
-          uint32_t fac_of[32];
+          uint32_t fac_of[kPointMaxCams];
           for (int64_t f = p.fac_off[c]; f < p.fac_off[c + 1]; ++f) fac_of[(p.slots[f].col0 - 3) / 9] = (uint32_t)e->g_index[p.slots[f].factor];
           for (int b1 = 0; b1 < k; ++b1) {
             const uint64_t A = (uint64_t)pm[9 * b1];
@@ -994,6 +998,10 @@ static void install_plan(Engine* e) {
   const Plan& p = e->plan;
   const int32_t C = p.n_cliques;
   compute_partition(p, e->world, e->owner);
+  {
+    const char* pa = getenv("GTB_POINT_ATOMIC");
+    e->point_pairs = !(pa && atoi(pa));
+  }
   e->child_work.clear();
   e->bs_list.clear();
   e->bs_scratch_off.clear();
@@ -1002,7 +1010,11 @@ static void install_plan(Engine* e) {
   e->is_point.assign(C, 0);
   for (int32_t c = 0; c < C; ++c) {
     const int32_t par = p.parent[c];
-    if (par >= 0 && is_fused_child(p.F[c], p.F[c] + p.S[c] + 1, p.F[par], p.F[par] + p.S[par] + 1) && is_star_clique(e, c, 22))
+    if (par < 0 || is_small_front(p.F[par], p.F[par] + p.S[par] + 1)) continue;
+    // with the pair-gathered Schur complement the point kernel only produces the conditional rows: any camera count
+    // up to kPointMaxCams, also points whose front would be large by its dimensions
+    if (e->point_pairs ? is_star_clique(e, c, kPointMaxCams, true)
+                       : (is_thin_front(p.F[c], p.F[c] + p.S[c] + 1) && is_star_clique(e, c, 22)))
       e->is_point[c] = 1;
   }
   // a large child of a large parent on the same rank and phase adds its Schur complement during its own Schur step
@@ -1012,7 +1024,7 @@ static void install_plan(Engine* e) {
     e->fuse_up.assign(C, 0);
     for (int32_t c = 0; c < C && on; ++c) {
       const int32_t par = p.parent[c];
-      if (par < 0 || is_small_front(p.F[c], p.F[c] + p.S[c] + 1) || is_small_front(p.F[par], p.F[par] + p.S[par] + 1)) continue;
+      if (par < 0 || e->is_point[c] || is_small_front(p.F[c], p.F[c] + p.S[c] + 1) || is_small_front(p.F[par], p.F[par] + p.S[par] + 1)) continue;
       if (e->owner[c] == e->owner[par]) e->fuse_up[c] = 1;
     }
   }
@@ -1069,14 +1081,10 @@ static void install_plan(Engine* e) {
       e->top_zero_blocks = std::max<int64_t>(e->top_zero_blocks, (sz / 2 + 255) / 256);
     }
   e->top_zero_blocks = std::min<int64_t>(e->top_zero_blocks, 64);
-  {
-    const char* pa = getenv("GTB_POINT_ATOMIC");
-    e->point_pairs = !(pa && atoi(pa));
-  }
   build_point_pairs(e);
   e->large_list.clear();
   for (int32_t c = 0; c < C; ++c)
-    if (e->owner[c] == e->rank && !is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) e->large_list.push_back(c);
+    if (e->owner[c] == e->rank && !e->is_point[c] && !is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) e->large_list.push_back(c);
   e->n_large_own = (int32_t)e->large_list.size();
   e->large_list.insert(e->large_list.end(), e->top_list.begin(), e->top_list.end());
   e->top_doubles = tail - e->top_off;
@@ -1108,7 +1116,7 @@ static void install_plan(Engine* e) {
     d.dfac_off = 0;
     d.pad = 0;
     d.flags = (is_star_clique(e, c, 15) ? kCliqueStar : 0) | (e->fuse_up[c] ? kCliqueFuseUp : 0);
-    if (!is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
+    if (!e->is_point[c] && !is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
       dfac_total += (int64_t)((p.F[c] + PW - 1) / PW) * PW * PW;
       need(dfac_total < INT32_MAX, "diagonal-block side buffer overflow");

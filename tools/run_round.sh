@@ -1,7 +1,5 @@
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r10_pytest.log
-python bench.py --no-cpu-baseline > gpurun_out/r10_bench_c3.json 2> gpurun_out/r10_bench_c3.err
-python bench.py --workload c4 --ordering metis --steps 5 --no-cpu-baseline > gpurun_out/r10_bench_c4.json 2> gpurun_out/r10_bench_c4.err
-python bench.py --workload c2 --ordering metis --no-cpu-baseline > gpurun_out/r10_bench_c2.json 2> gpurun_out/r10_bench_c2.err
-GTB_DEBUG=8 python tools/launch_trace.py c3 metis 2>&1 | tail -12 > gpurun_out/r10_trace_tail.txt
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r14_pytest.log
+python bench.py --no-cpu-baseline > gpurun_out/r14_bench_c3.json 2> gpurun_out/r14_bench_c3.err
+python bench.py --workload c4 --ordering metis --steps 5 --no-cpu-baseline > gpurun_out/r14_bench_c4.json 2> gpurun_out/r14_bench_c4.err
