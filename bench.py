@@ -101,6 +101,15 @@ def clocks_stop(proc, path, device):
     return out
 
 
+_JSON_OUT = None
+
+
+def emit(obj):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(obj) + "\n")
+    out.flush()
+
+
 def run_reference(args, rank, world):
     """The reference's own CPU implementation of the step (oracle/_ref/ref_tool mode=time: unmodified GTSAM 4.3a0
     linked from oracle/_ref/libgtsam_ref.so), rank 0 only."""
@@ -112,7 +121,7 @@ def run_reference(args, rank, world):
             "data": "synthetic", "config": {"workload": WORKLOADS[args.workload], "ordering": args.ordering,
                                             "lambda": args.lam}}
     if not os.path.exists(tool):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_tool not built (needs /root/reference)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/ref_tool not built (needs /root/reference)"})
         return
     p = make_problem(args.workload)
     o = ordering_for(p, args.workload, args.ordering)
@@ -141,7 +150,7 @@ def run_reference(args, rank, world):
                                   "wall_s": wall},
                  "e2e": {"value": 1.0 / t_iter, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
-    print(json.dumps(base))
+    emit(base)
 
 
 def main():
@@ -158,6 +167,12 @@ def main():
                     help="N > 1: 'tree' = ONE problem, elimination tree cut across the GPUs (fan-in over NCCL, strong "
                          "scaling); 'replicas' = one independent problem per GPU (weak scaling, no collective)")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: everything else that libraries print there (NCCL's version banner, the
+    # reference tool's progress) goes to stderr
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -344,7 +359,7 @@ def main():
     else:
         line["cpu_baseline"] = {"value": None, "unit": "iter/s", "cores": 0, "kind": "reference",
                                 "sample": "skipped (multi-GPU run, --no-cpu-baseline, or oracle/_ref missing)"}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

@@ -69,6 +69,21 @@ _SIGS = {
     "gtb_set_robust": (C.c_int, [_P, C.c_int, C.c_int, C.c_double]),
     "gtb_set_distributed": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P]),
     "gtb_partition_get": (C.c_int, [_P, _P, _P]),
+    "gtb_dataset_read_g2o": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_P)]),
+    "gtb_dataset_read_bal": (C.c_int, [C.c_char_p, C.POINTER(_P)]),
+    "gtb_dataset_free": (None, [_P]),
+    "gtb_dataset_last_error": (C.c_char_p, []),
+    "gtb_dataset_num_variables": (C.c_int64, [_P, C.c_int]),
+    "gtb_dataset_variable_keys": (_P, [_P, C.c_int]),
+    "gtb_dataset_variable_state": (_P, [_P, C.c_int]),
+    "gtb_dataset_num_factors": (C.c_int64, [_P, C.c_int]),
+    "gtb_dataset_factor_keys": (_P, [_P, C.c_int]),
+    "gtb_dataset_factor_z": (_P, [_P, C.c_int]),
+    "gtb_dataset_factor_noise_kind": (_P, [_P, C.c_int]),
+    "gtb_dataset_factor_noise": (_P, [_P, C.c_int]),
+    "gtb_dataset_robust": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "gtb_dataset_apply": (C.c_int, [_P, _P]),
+    "gtb_write_g2o": (C.c_int, [C.c_char_p, C.c_int64, _P, _P, C.c_int64, _P, _P, C.c_int64, _P, _P, _P, C.c_int64, _P, _P, _P]),
 }
 
 # int (*gtb_comm_fn)(void* user, int op, void* buf, int64_t count, void* stream)

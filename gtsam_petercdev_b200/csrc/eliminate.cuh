@@ -67,6 +67,14 @@ __device__ __forceinline__ int frexp_exp(double x) {
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// one 32-byte column of a point front in a single request (LDG.256, read-only path)
+struct Col4 { double x, y, z, w; };
+__device__ __forceinline__ Col4 ld_col(const double* p) {
+  Col4 c;
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(c.x), "=d"(c.y), "=d"(c.z), "=d"(c.w) : "l"(p));
+  return c;
+}
+
 // ----------------------------------------------------------------------------------------------------
 // small fronts: one CTA per clique, the whole front lives in shared memory
 // ----------------------------------------------------------------------------------------------------
@@ -432,7 +440,6 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
   int* sfac = scol + kmax;                              // camera block index -> factor
   const int c = list[slot];
   const CliqueDev ci = E.cliques[c];
-  const CliqueDev cp = E.cliques[ci.parent];
   const int k = ci.fac_end - ci.fac_begin, n = ci.S + 1, nc = ci.S;   // nc = 9 k camera scalars, column nc is the rhs
   for (int t = lane; t < 26 * k; t += 32) {
     const int s = t / 26, r = t - s * 26;
@@ -505,6 +512,7 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
   if (!schur) return;   // the Schur complement is gathered per camera pair by point_pair_kernel / point_diag_kernel
   __syncwarp();
   // Schur complement entries (i <= j over the separator scalars and the rhs) straight into the parent
+  const CliqueDev cp = E.cliques[ci.parent];
   double* pdst = E.arena + cp.front_off;
   const int pld = cp.ld;
   const int total = (n * (n + 1)) >> 1;
@@ -547,13 +555,6 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
 // into segments whose partial sums meet in the parent through atomics (81 per segment instead of 81 per item).
 // ----------------------------------------------------------------------------------------------------
 constexpr int kPairSeg = 32;
-// one 32-byte column of a point front in a single request (LDG.256, read-only path)
-struct Col4 { double x, y, z, w; };
-__device__ __forceinline__ Col4 ld_col(const double* p) {
-  Col4 c;
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(c.x), "=d"(c.y), "=d"(c.z), "=d"(c.w) : "l"(p));
-  return c;
-}
 struct PairSeg { int64_t dst; int32_t ld; int32_t begin; int32_t count; int32_t ncol; };   // ncol: columns from the block to the parent's rhs column
 __global__ void __launch_bounds__(128) point_pair_kernel(ElimDev E, const PairSeg* __restrict__ segs, int nseg,
                                                          const uint2* __restrict__ items) {
@@ -1333,8 +1334,8 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
     double a0 = 0.0, a1 = 0.0, a2 = 0.0;
     for (int j = lane; j < S; j += 32) {
       const double x = delta[g[3 + j]];
-      const double* col = A + (int64_t)(3 + j) * 4;
-      a0 += col[0] * x; a1 += col[1] * x; a2 += col[2] * x;
+      const Col4 col = ld_col(A + (int64_t)(3 + j) * 4);   // one 32-byte request per column
+      a0 += col.x * x; a1 += col.y * x; a2 += col.z * x;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

@@ -6,6 +6,8 @@ C2  sphere_shape()  50 x 50 Pose3 on a sphere, ring + meridian edges, prior on p
 C3  ba_shape(1723, 156000)   Ladybug-scale bundle adjustment (~679k GeneralSFMFactor<Cal3Bundler>)
 C4  ba_shape(1778, 993000, mean_obs=5.03)  Venice-scale
 """
+import os
+
 import numpy as np
 from .problem import Problem, symbol
 
@@ -301,3 +303,99 @@ def read_bal(path):
     p.set_variables("point", pkeys, pts)
     p.set_factors("sfm", np.stack([ckeys[cam_idx[o]], pkeys[pt_idx[o]]], axis=1), uv[o], 1, np.array([[1.0]]))
     return p
+
+
+# ---- native ingestion (csrc/ingest.cpp behind the C ABI): files straight to the flat tables -----------------------
+class DatasetError(ValueError):
+    pass
+
+
+def _dataset_to_problem(h):
+    import ctypes as C
+    from . import capi
+    from .problem import BUCKETS, BUCKET_Z, BUCKET_DIM, BUCKET_NKEYS, VTYPES, VTYPE_STATE, LOSSES
+    lib = capi.lib()
+
+    def arr(ptr, n, ctype, dtype):
+        if n == 0 or not ptr:
+            return np.zeros(0, dtype=dtype)
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(n,)).astype(dtype, copy=True)
+    p = Problem()
+    for t, name in enumerate(VTYPES):
+        n = lib.gtb_dataset_num_variables(h, t)
+        if n > 0:
+            p.set_variables(name, arr(lib.gtb_dataset_variable_keys(h, t), n, C.c_uint64, np.uint64),
+                            arr(lib.gtb_dataset_variable_state(h, t), n * VTYPE_STATE[t], C.c_double, np.float64).reshape(n, VTYPE_STATE[t]))
+    for b, name in enumerate(BUCKETS):
+        n = lib.gtb_dataset_num_factors(h, b)
+        if n > 0:
+            d = BUCKET_DIM[b]
+            p.set_factors(name, arr(lib.gtb_dataset_factor_keys(h, b), n * BUCKET_NKEYS[b], C.c_uint64, np.uint64).reshape(n, BUCKET_NKEYS[b]),
+                          arr(lib.gtb_dataset_factor_z(h, b), n * BUCKET_Z[b], C.c_double, np.float64).reshape(n, BUCKET_Z[b]),
+                          arr(lib.gtb_dataset_factor_noise_kind(h, b), n, C.c_int32, np.int32),
+                          arr(lib.gtb_dataset_factor_noise(h, b), n * d * d, C.c_double, np.float64).reshape(n, d * d))
+    k = C.c_double(0.0)
+    loss = lib.gtb_dataset_robust(h, C.byref(k))
+    if loss:
+        p.set_robust("between2", LOSSES[loss], k.value)
+    return p
+
+
+def _read_native(fn, *args):
+    import ctypes as C
+    from . import capi
+    lib = capi.lib()
+    h = C.c_void_p()
+    st = getattr(lib, fn)(*args, C.byref(h))
+    if st != capi.OK:
+        raise DatasetError(lib.gtb_dataset_last_error().decode())
+    try:
+        return _dataset_to_problem(h)
+    finally:
+        lib.gtb_dataset_free(h)
+
+
+def read_g2o(path, is3d=False, kernel="none"):
+    """gtsam::readG2o(file, is3D, kernelFunctionType) (slam/dataset.cpp:621-633) -> Problem, parsed by the native
+    reader (gtb_dataset_read_g2o).  kernel: "none" | "huber" | "tukey"."""
+    from .problem import LOSSES
+    return _read_native("gtb_dataset_read_g2o", os.fsencode(path), int(bool(is3d)), LOSSES.index(kernel))
+
+
+def read_bal_native(path):
+    """SfmData::FromBalFile + the projection factors of SFMExample_bal (gtb_dataset_read_bal) -> Problem."""
+    return _read_native("gtb_dataset_read_bal", os.fsencode(path))
+
+
+def write_g2o(path, problem):
+    """gtsam::writeG2o (slam/dataset.cpp:636-735) for the poses and between factors of a Problem."""
+    from . import capi
+    from .problem import resolve_noise
+    lib = capi.lib()
+    a = problem.a
+
+    def get(name, dtype, cols):
+        v = a.get(name)
+        if v is None or len(v) == 0:
+            return np.zeros((0, cols), dtype=dtype)
+        return np.ascontiguousarray(v, dtype=dtype).reshape(len(v), cols)
+
+    def info(bucket, d):
+        nk, noise = a.get(bucket + "_nk"), a.get(bucket + "_noise")
+        if nk is None or len(nk) == 0:
+            return np.zeros((0, d * d))
+        out = np.zeros((len(nk), d * d))
+        for i in range(len(nk)):
+            kind, R = resolve_noise(int(nk[i]), np.asarray(noise[i], dtype=np.float64), d)
+            Rm = np.eye(d) if kind == 0 else (np.eye(d) * R[0] if kind == 1 else (np.diag(R[:d]) if kind == 2 else np.asarray(R).reshape(d, d)))
+            out[i] = (Rm.T @ Rm).reshape(-1)
+        return out
+    p2k, p2 = get("pose2_keys", np.uint64, 1), get("pose2", np.float64, 3)
+    p3k, p3 = get("pose3_keys", np.uint64, 1), get("pose3", np.float64, 12)
+    b2k, b2z, b2i = get("between2_keys", np.uint64, 2), get("between2_z", np.float64, 3), info("between2", 3)
+    b3k, b3z, b3i = get("between3_keys", np.uint64, 2), get("between3_z", np.float64, 12), info("between3", 6)
+    ptr = lambda x: x.ctypes.data if x.size else None   # noqa: E731
+    st = lib.gtb_write_g2o(os.fsencode(path), len(p2k), ptr(p2k), ptr(p2), len(p3k), ptr(p3k), ptr(p3),
+                           len(b2k), ptr(b2k), ptr(b2z), ptr(b2i), len(b3k), ptr(b3k), ptr(b3z), ptr(b3i))
+    if st != capi.OK:
+        raise DatasetError(lib.gtb_dataset_last_error().decode())

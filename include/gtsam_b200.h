@@ -188,6 +188,42 @@ gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double relativ
 #define GTB_LOSS_L2WITHDEADZONE 8
 gtb_status gtb_set_robust(gtb_engine* e, int bucket, int loss, double k);
 
+/* ---- dataset ingestion straight to struct-of-arrays --------------------------------------
+ * Replaces the file readers that sit in front of the path: readG2o / load2D / load3D (slam/dataset.cpp:621-633,
+ * :505-570, :922-946) and SfmData::FromBalFile (sfm/SfmData.cpp:189-247) plus the graph construction loop of
+ * examples/SFMExample_bal.cpp:52-63.  A dataset owns flat tables in exactly the layout gtb_set_variables /
+ * gtb_set_factors take (variables in ascending key order, factors in file / track order); gtb_dataset_apply pushes
+ * them into an engine (the caller still adds priors and calls gtb_finalize_problem).  Errors: GTB_ERR_INVALID with the
+ * message in gtb_dataset_last_error() (missing file, malformed record, landmark records that have no device type). */
+typedef struct gtb_dataset gtb_dataset;
+/* readG2o(file, is3D, kernelFunctionType): kernel = GTB_LOSS_NONE | GTB_LOSS_HUBER (k = 1.345) | GTB_LOSS_TUKEY
+ * (k = 4.6851), 2D only, as in the reference.  Also reads the TORO tags (VERTEX2 / EDGE2 / VERTEX3 / EDGE3).          */
+gtb_status gtb_dataset_read_g2o(const char* path, int is3d, int kernel, gtb_dataset** out);
+/* SfmData::FromBalFile + one GeneralSFMFactor<Cal3Bundler> per measurement, Unit noise, cameras keyed 0..n-1, points
+ * P(j) (tests/testGeneralSFMFactorB.cpp:44-58).                                                                      */
+gtb_status gtb_dataset_read_bal(const char* path, gtb_dataset** out);
+void gtb_dataset_free(gtb_dataset* d);
+const char* gtb_dataset_last_error(void);
+int64_t gtb_dataset_num_variables(const gtb_dataset* d, int vtype);
+const uint64_t* gtb_dataset_variable_keys(const gtb_dataset* d, int vtype);
+const double* gtb_dataset_variable_state(const gtb_dataset* d, int vtype);
+int64_t gtb_dataset_num_factors(const gtb_dataset* d, int bucket);
+const uint64_t* gtb_dataset_factor_keys(const gtb_dataset* d, int bucket);
+const double* gtb_dataset_factor_z(const gtb_dataset* d, int bucket);
+const int32_t* gtb_dataset_factor_noise_kind(const gtb_dataset* d, int bucket);
+const double* gtb_dataset_factor_noise(const gtb_dataset* d, int bucket);
+int gtb_dataset_robust(const gtb_dataset* d, double* k);      /* m-estimator the file was read with (between factors) */
+gtb_status gtb_dataset_apply(const gtb_dataset* d, gtb_engine* e);
+/* writeG2o (slam/dataset.cpp:636-735): VERTEX_SE2 / VERTEX_SE3:QUAT for the poses, EDGE_SE2 / EDGE_SE3:QUAT for the
+ * between factors; *_information holds R^T R of each factor's Gaussian model (d x d, row-major, GTSAM's (R, t) order
+ * for Pose3; written in g2o's (t, R) order).  Default stream formatting, as the reference.                            */
+gtb_status gtb_write_g2o(const char* path, int64_t n_pose2, const uint64_t* pose2_keys, const double* pose2,
+                         int64_t n_pose3, const uint64_t* pose3_keys, const double* pose3,
+                         int64_t n_between2, const uint64_t* between2_keys, const double* between2_z,
+                         const double* between2_information,
+                         int64_t n_between3, const uint64_t* between3_keys, const double* between3_z,
+                         const double* between3_information);
+
 /* ---- several GPUs: one engine per process / GPU ---------------------------------------------
  * The reference parallelises elimination over the children of a clique with TBB tasks
  * (inference/ClusterTree-inst.h:286-318).  Across GPUs the same tree is cut instead: every rank holds the whole

@@ -34,6 +34,8 @@
 #include <gtsam/nonlinear/internal/LevenbergMarquardtState.h>
 #include <gtsam/slam/BetweenFactor.h>
 #include <gtsam/slam/GeneralSFMFactor.h>
+#include <gtsam/sfm/SfmData.h>
+#include <gtsam/slam/dataset.h>
 
 #include <chrono>
 #include <fstream>
@@ -320,6 +322,98 @@ static GaussianFactorGraph damp(const GaussianFactorGraph& gfg, const Values& va
   return st.buildDampedSystem(gfg, sq);
 }
 
+// mode=readg2o is3d=0|1 kernel=none|huber|tukey / mode=readbal: argv[1] is the DATA file; the reference's own readers
+// (readG2o, SfmData::FromBalFile + the graph of tests/testGeneralSFMFactorB.cpp:44-58) build graph and values, which
+// are dumped in the problem schema (+ *_info = R^T R of every Gaussian model, pose2_cs = (cos, sin)).
+// mode=writeg2o: reads the file with readG2o and writes it back with the reference's writeG2o to <out>.
+static int dataset_mode(const std::string& data, const std::string& outpath) {
+  const std::string mode = opt("mode", "");
+  gtbio::File out;
+  NonlinearFactorGraph graph;
+  Values values;
+  if (mode == "readbal") {
+    SfmData db = SfmData::FromBalFile(data);
+    for (size_t j = 0; j < db.numberTracks(); j++)
+      for (const SfmMeasurement& m : db.tracks[j].measurements)
+        graph.emplace_shared<SfmFactor>(m.second, noiseModel::Unit::Create(2), m.first, Symbol('p', j));
+    size_t i = 0, j = 0;
+    for (const SfmCamera& camera : db.cameras) values.insert(i++, camera);
+    for (const SfmTrack& track : db.tracks) values.insert(Symbol('p', j++), track.p);
+  } else {
+    const bool is3d = opt("is3d", "0") == "1";
+    const std::string k = opt("kernel", "none");
+    const KernelFunctionType kt = k == "huber" ? KernelFunctionTypeHUBER : (k == "tukey" ? KernelFunctionTypeTUKEY : KernelFunctionTypeNONE);
+    auto gv = readG2o(data, is3d, kt);
+    graph = *gv.first;
+    values = *gv.second;
+    if (mode == "writeg2o") {
+      writeG2o(graph, values, outpath);
+      return 0;
+    }
+  }
+  std::vector<uint64_t> k2, k3, kc, kp;
+  std::vector<double> v2, v2cs, v3, vc, vp;
+  for (const auto& kv : values.extract<Pose2>()) {
+    k2.push_back(kv.first);
+    v2.insert(v2.end(), {kv.second.x(), kv.second.y(), kv.second.theta()});
+    v2cs.insert(v2cs.end(), {kv.second.r().c(), kv.second.r().s()});
+  }
+  auto push_pose3 = [](std::vector<double>& v, const Pose3& p) {
+    const Matrix3 R = p.rotation().matrix();
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) v.push_back(R(r, c));
+    v.insert(v.end(), {p.x(), p.y(), p.z()});
+  };
+  for (const auto& kv : values.extract<Pose3>()) { k3.push_back(kv.first); push_pose3(v3, kv.second); }
+  for (const auto& kv : values.extract<Camera>()) {
+    kc.push_back(kv.first);
+    push_pose3(vc, kv.second.pose());
+    const Cal3Bundler& K = kv.second.calibration();
+    vc.insert(vc.end(), {K.fx(), K.k1(), K.k2(), K.px(), K.py()});
+  }
+  for (const auto& kv : values.extract<Point3>()) { kp.push_back(kv.first); vp.insert(vp.end(), {kv.second.x(), kv.second.y(), kv.second.z()}); }
+  std::vector<uint64_t> b2k, b3k, sk;
+  std::vector<double> b2z, b2cs, b2i, b3z, b3i, sz;
+  auto info_of = [](const SharedNoiseModel& m, std::vector<double>& dst) {
+    SharedNoiseModel base = m;
+    if (auto rob = std::dynamic_pointer_cast<noiseModel::Robust>(m)) base = rob->noise();
+    auto g = std::dynamic_pointer_cast<noiseModel::Gaussian>(base);
+    const Matrix I = g->R().transpose() * g->R();
+    for (int r = 0; r < I.rows(); ++r) for (int c = 0; c < I.cols(); ++c) dst.push_back(I(r, c));
+  };
+  for (const auto& f : graph) {
+    if (auto b = std::dynamic_pointer_cast<BetweenFactor<Pose2>>(f)) {
+      b2k.insert(b2k.end(), {b->key<1>(), b->key<2>()});
+      b2z.insert(b2z.end(), {b->measured().x(), b->measured().y(), b->measured().theta()});
+      b2cs.insert(b2cs.end(), {b->measured().r().c(), b->measured().r().s()});
+      info_of(b->noiseModel(), b2i);
+    } else if (auto b3 = std::dynamic_pointer_cast<BetweenFactor<Pose3>>(f)) {
+      b3k.insert(b3k.end(), {b3->key<1>(), b3->key<2>()});
+      push_pose3(b3z, b3->measured());
+      info_of(b3->noiseModel(), b3i);
+    } else if (auto sf = std::dynamic_pointer_cast<SfmFactor>(f)) {
+      sk.insert(sk.end(), {sf->key<1>(), sf->key<2>()});
+      sz.insert(sz.end(), {sf->measured().x(), sf->measured().y()});
+    }
+  }
+  out.put_u64("pose2_keys", k2); out.put_f64("pose2", v2, {k2.size(), 3}); out.put_f64("pose2_cs", v2cs, {k2.size(), 2});
+  out.put_u64("pose3_keys", k3); out.put_f64("pose3", v3, {k3.size(), 12});
+  out.put_u64("cam_keys", kc); out.put_f64("cam", vc, {kc.size(), 17});
+  out.put_u64("point_keys", kp); out.put_f64("point", vp, {kp.size(), 3});
+  out.put_u64("between2_keys", b2k, {b2k.size() / 2, 2}); out.put_f64("between2_z", b2z, {b2k.size() / 2, 3});
+  out.put_f64("between2_cs", b2cs, {b2k.size() / 2, 2}); out.put_f64("between2_info", b2i, {b2k.size() / 2, 9});
+  out.put_u64("between3_keys", b3k, {b3k.size() / 2, 2}); out.put_f64("between3_z", b3z, {b3k.size() / 2, 12});
+  out.put_f64("between3_info", b3i, {b3k.size() / 2, 36});
+  out.put_u64("sfm_keys", sk, {sk.size() / 2, 2}); out.put_f64("sfm_z", sz, {sk.size() / 2, 2});
+  try {
+    out.put_f64("error0", {graph.error(values)});
+  } catch (const std::exception&) {   // files without vertices (load3D does not create them)
+    out.put_f64("error0", {-1.0});
+  }
+  out.put_i64("n_factors", {(int64_t)graph.size()});
+  out.save(outpath);
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) { std::cerr << "usage: ref_tool problem.gtb out.gtb key=value...\n"; return 2; }
   for (int i = 3; i < argc; ++i) {
@@ -328,6 +422,7 @@ int main(int argc, char** argv) {
     if (p != std::string::npos) g_opt[a.substr(0, p)] = a.substr(p + 1);
   }
   try {
+    if (opt("mode", "solve").rfind("read", 0) == 0 || opt("mode", "solve") == "writeg2o") return dataset_mode(argv[1], argv[2]);
     gtbio::File P, out;
     P.load(argv[1]);
     Built B = build(P);
