@@ -20,6 +20,7 @@
 
 #include "../../include/gtsam_b200.h"
 #include "eliminate.cuh"
+#include "marginals.cuh"
 #include "factors.cuh"
 #include "plan.h"
 
@@ -182,6 +183,16 @@ struct gtb_engine {
   DevBuf<uint2> d_pair_items;
   DevBuf<uint32_t> d_diag_items;
   DevBuf<long long> d_dbg;
+  // marginal covariances (marginals.cuh): built on first use for the installed plan
+  std::vector<MargClique> marg_cliques;
+  std::vector<int32_t> marg_lists;            // per level: cliques with F + S <= 256 first, then the others
+  std::vector<int64_t> marg_level_off;        // [n_levels + 1]
+  std::vector<int32_t> marg_level_small;      // [n_levels]
+  std::vector<int32_t> var_clique, var_foff;  // per variable: the clique it is a frontal of, its scalar offset there
+  DevBuf<MargClique> d_marg_cliques;
+  DevBuf<int32_t> d_marg_lists;
+  DevBuf<double> d_sigma, d_marg_scratch;
+  bool marg_built = false, marg_valid = false;
   bool linearized = false, factorized = false, solved = false, have_hdiag = false;
 
   bool profiling = false;
@@ -328,10 +339,10 @@ struct StageTimer {
 
 // kernel classes for launch counting and optional per-launch event timing
 enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_POINT, K_PAIR, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
-       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_NUM };
+       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_MARGINAL, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
                                           "small_front", "thin_front", "point_front", "point_schur", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
-                                          "backsolve", "backsolve_gemv", "retract", "own_delta"};
+                                          "backsolve", "backsolve_gemv", "retract", "own_delta", "marginals"};
 
 static void prof_begin(Engine* e, int k) {
   if (!e->profiling) return;
@@ -1151,6 +1162,7 @@ static void install_plan(Engine* e) {
   if (e->world > 1) e->d_delta_own.alloc((size_t)e->n_scalars + 2);
   CK(cudaStreamSynchronize(st));
   e->factorized = e->solved = false;
+  e->marg_built = e->marg_valid = false;
 }
 
 static void set_ordering_ids(Engine* e, const std::vector<int32_t>& order) {
@@ -1386,6 +1398,7 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   tm.stop();
   e->factorized = (fail == INT_MAX);
   e->solved = false;
+  e->marg_valid = false;
   return fail == INT_MAX ? -1 : fail;
 }
 
@@ -1428,6 +1441,100 @@ static void backsolve(Engine* e) {
   }
   tm.stop();
   e->solved = true;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// marginal covariances (Marginals::marginalCovariance, nonlinear/Marginals.cpp:108-150)
+// ------------------------------------------------------------------------------------------------------
+static void marginals_build(Engine* e) {
+  const Plan& p = e->plan;
+  const int32_t C = p.n_cliques;
+  e->marg_cliques.assign(C, MargClique());
+  int64_t soff = 0;
+  for (int32_t c = 0; c < C; ++c) {
+    MargClique& m = e->marg_cliques[c];
+    const bool leaf = p.child_off[c + 1] == p.child_off[c];
+    m.sld = leaf ? p.F[c] : p.F[c] + p.S[c];
+    m.sigma_off = soff;
+    soff += ((int64_t)m.sld * m.sld + 1) & ~(int64_t)1;
+  }
+  e->marg_lists.clear();
+  e->marg_level_off.assign(p.n_levels + 1, 0);
+  e->marg_level_small.assign(p.n_levels, 0);
+  int64_t scratch_max = 0;
+  for (int32_t l = 0; l < p.n_levels; ++l) {
+    e->marg_level_off[l] = (int64_t)e->marg_lists.size();
+    int64_t sc = 0;
+    for (int pass = 0; pass < 2; ++pass)
+      for (int64_t q = p.level_off[l]; q < p.level_off[l + 1]; ++q) {
+        const int32_t c = p.level_cliques[q];
+        const bool small = p.F[c] + p.S[c] <= 256;
+        if (small != (pass == 0)) continue;
+        e->marg_lists.push_back(c);
+        if (small) e->marg_level_small[l]++;
+        e->marg_cliques[c].scratch_off = sc;
+        sc += (int64_t)p.F[c] * p.F[c] + 2 * (int64_t)p.F[c] * p.S[c];
+      }
+    scratch_max = std::max(scratch_max, sc);
+  }
+  e->marg_level_off[p.n_levels] = (int64_t)e->marg_lists.size();
+  e->var_clique.assign(e->vkeys.size(), -1);
+  e->var_foff.assign(e->vkeys.size(), 0);
+  for (int32_t c = 0; c < C; ++c) {
+    int32_t off = 0;
+    for (int32_t k = 0; k < p.n_frontal_vars[c]; ++k) {
+      const int32_t v = p.vars[p.vars_off[c] + k];
+      e->var_clique[v] = c;
+      e->var_foff[v] = off;
+      off += e->vdim[v];
+    }
+  }
+  e->d_marg_cliques.upload(e->marg_cliques, e->stream);
+  e->d_marg_lists.upload(e->marg_lists, e->stream);
+  e->d_sigma.alloc((size_t)soff + 2);
+  e->d_marg_scratch.alloc((size_t)scratch_max + 2);
+  CK(cudaStreamSynchronize(e->stream));
+  e->marg_built = true;
+}
+
+static void marginals_compute(Engine* e) {
+  need_device(e);
+  need(e->factorized, "gtb_marginals_compute needs gtb_linearize and a successful gtb_factorize (lambda = 0) first");
+  need(e->world == 1, "marginal covariances are computed on one GPU");
+  if (!e->marg_built) marginals_build(e);
+  const ElimDev E = elim_dev(e, false);
+  for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
+    const int64_t b = e->marg_level_off[l];
+    const int32_t ns = e->marg_level_small[l], nb = (int32_t)(e->marg_level_off[l + 1] - b) - ns;
+    if (ns) LAUNCH(e, K_MARGINAL, marginal_kernel<<<ns, 128, 0, e->stream>>>(E, e->d_marg_cliques.p, e->d_marg_lists.p + b, e->d_sigma.p, e->d_marg_scratch.p));
+    if (nb) LAUNCH(e, K_MARGINAL, marginal_kernel<<<nb, 1024, 0, e->stream>>>(E, e->d_marg_cliques.p, e->d_marg_lists.p + b + ns, e->d_sigma.p, e->d_marg_scratch.p));
+  }
+  CK(cudaStreamSynchronize(e->stream));
+  e->marg_valid = true;
+}
+
+static void marginal_covariance(Engine* e, int64_t n, const uint64_t* keys, double* out) {
+  need_device(e);
+  need(e->marg_valid && e->factorized, "gtb_marginal_covariance needs gtb_marginals_compute after the last gtb_factorize");
+  std::vector<MargQuery> q((size_t)n);
+  int64_t dst = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const auto it = std::lower_bound(e->vkeys.begin(), e->vkeys.end(), keys[i]);
+    if (it == e->vkeys.end() || *it != keys[i]) throw StatusError(GTB_ERR_KEY_MISSING, "marginalCovariance: key is not in the problem");
+    const int32_t v = (int32_t)(it - e->vkeys.begin()), c = e->var_clique[v];
+    need(c >= 0, "variable is not a frontal of any clique");
+    const MargClique& m = e->marg_cliques[c];
+    q[i] = MargQuery{m.sigma_off + e->var_foff[v] + (int64_t)e->var_foff[v] * m.sld, dst, m.sld, e->vdim[v]};
+    dst += (int64_t)e->vdim[v] * e->vdim[v];
+  }
+  if (!n) return;
+  DevBuf<MargQuery> dq;
+  DevBuf<double> dout;
+  dq.upload(q, e->stream);
+  dout.alloc((size_t)dst);
+  LAUNCH(e, K_MARGINAL, marginal_gather_kernel<<<(unsigned)n, 32, 0, e->stream>>>(dq.p, e->d_sigma.p, dout.p));
+  CK(cudaMemcpyAsync(out, dout.p, (size_t)dst * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
 }
 
 template <int VT> static void launch_retract(Engine* e) {
@@ -1796,6 +1903,14 @@ gtb_status gtb_get_conditionals(gtb_engine* e, double* out) {
       for (int j = 0; j < dim; ++j) o[(int64_t)i * dim + j] = (j >= i) ? A[i + (int64_t)j * ld] : 0.0;
   }
   GTB_CATCH(e)
+}
+gtb_status gtb_marginals_compute(gtb_engine* e) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e) marginals_compute(e); GTB_CATCH(e)
+}
+gtb_status gtb_marginal_covariance(gtb_engine* e, int64_t n, const uint64_t* keys, double* out) {
+  if (!e || n < 0 || (n > 0 && (!keys || !out))) return GTB_ERR_INVALID;
+  GTB_TRY(e) marginal_covariance(e, n, keys, out); GTB_CATCH(e)
 }
 gtb_status gtb_linear_errors(gtb_engine* e, double* e0, double* e1) {
   if (!e || !e0 || !e1) return GTB_ERR_INVALID;

@@ -228,6 +228,23 @@ class Engine:
         return dict(initial_error=r.initial_error, final_error=r.final_error, iterations=r.iterations)
 
     # ---- instrumentation --------------------------------------------------------------------------
+    def marginal_covariances(self, keys):
+        """Marginals(graph, values).marginalCovariance(key) for every key (nonlinear/Marginals.cpp:108): list of d x d
+        arrays.  Needs linearize() + factorize(0.0) on the current values."""
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        self._ck(self.lib.gtb_marginals_compute(self.h))
+        _, vt, _, dims = self.problem.variables()
+        kk, _, _, _ = self.problem.variables()
+        dim_of = dict(zip(kk.tolist(), dims.tolist()))
+        ds = [dim_of.get(int(k), 0) for k in keys]
+        out = np.zeros(int(sum(d * d for d in ds)) + 1)
+        self._ck(self.lib.gtb_marginal_covariance(self.h, len(keys), _ptr(keys), _ptr(out)))
+        res, o = [], 0
+        for d in ds:
+            res.append(out[o:o + d * d].reshape(d, d).copy())
+            o += d * d
+        return res
+
     def kernel_launches(self):
         return int(self.lib.gtb_kernel_launches(self.h))
 

@@ -224,6 +224,17 @@ gtb_status gtb_write_g2o(const char* path, int64_t n_pose2, const uint64_t* pose
                          int64_t n_between3, const uint64_t* between3_keys, const double* between3_z,
                          const double* between3_information);
 
+/* ---- marginal covariances from the device Bayes tree ------------------------------------
+ * Marginals(graph, values).marginalCovariance(key) (nonlinear/Marginals.cpp:35-150): the reference re-linearises,
+ * eliminates into a Bayes tree and, per query, builds the marginal factor through shortcuts (inference/BayesTree-inst.h).
+ * Here: gtb_linearize + gtb_factorize(lambda = 0) as usual, then gtb_marginals_compute sweeps the resident [R S d]
+ * blocks once from the roots to the leaves (selective inversion), after which any number of d x d covariance blocks
+ * can be read.  `out` receives the blocks back to back (dim(key)^2 doubles each, symmetric) in the order of `keys`.
+ * Errors: GTB_ERR_KEY_MISSING for an unknown key; GTB_ERR_INVALID before a successful factorisation or with
+ * several ranks.                                                                                                    */
+gtb_status gtb_marginals_compute(gtb_engine* e);
+gtb_status gtb_marginal_covariance(gtb_engine* e, int64_t n, const uint64_t* keys, double* out);
+
 /* ---- several GPUs: one engine per process / GPU ---------------------------------------------
  * The reference parallelises elimination over the children of a clique with TBB tasks
  * (inference/ClusterTree-inst.h:286-318).  Across GPUs the same tree is cut instead: every rank holds the whole

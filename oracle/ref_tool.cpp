@@ -28,6 +28,7 @@
 #include <gtsam/linear/VectorValues.h>
 #include <gtsam/nonlinear/GaussNewtonOptimizer.h>
 #include <gtsam/nonlinear/LevenbergMarquardtOptimizer.h>
+#include <gtsam/nonlinear/Marginals.h>
 #include <gtsam/nonlinear/NonlinearFactorGraph.h>
 #include <gtsam/nonlinear/PriorFactor.h>
 #include <gtsam/nonlinear/Values.h>
@@ -433,6 +434,21 @@ int main(int argc, char** argv) {
     if (mode == "ordering") {
       Ordering ord = make_ordering(P, B);
       dump_ordering(ord, out);
+    } else if (mode == "marginals") {
+      // Marginals(graph, values).marginalCovariance(key) for every variable, ascending key (nonlinear/Marginals.cpp)
+      Marginals marginals(B.graph, B.values);
+      std::vector<uint64_t> mk;
+      std::vector<double> mv;
+      std::vector<int64_t> md;
+      for (const auto& kv : B.values) {
+        const Matrix Cv = marginals.marginalCovariance(kv.key);
+        mk.push_back(kv.key);
+        md.push_back(Cv.rows());
+        for (int r = 0; r < Cv.rows(); ++r) for (int c = 0; c < Cv.cols(); ++c) mv.push_back(Cv(r, c));
+      }
+      out.put_u64("marginal_keys", mk);
+      out.put_i64("marginal_dims", md);
+      out.put_f64("marginal_cov", mv);
     } else if (mode == "linearize") {
       auto gfg = B.graph.linearize(B.values);
       dump_jacobians(B, *gfg, out);
