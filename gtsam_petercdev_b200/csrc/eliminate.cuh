@@ -135,26 +135,36 @@ __global__ void small_front_kernel(ElimDev E, const int32_t* __restrict__ list) 
   __syncthreads();
   assemble_front(E, ci, A, lds);
 
-  // right-looking partial Cholesky over the F frontal pivots: A = R^T R on the frontal block, S = R^-T B,
-  // C -= S^T S  (base/cholesky.cpp:125-142)
+  // partial Cholesky over the F frontal pivots: A = R^T R on the frontal block, S = R^-T B, C -= S^T S
+  // (base/cholesky.cpp:125-142).  The pivot loop only touches the F frontal rows (2-D thread grid, no integer division,
+  // two barriers per pivot); the Schur complement is one barrier-free pass in which every entry subtracts its F products
+  // in pivot order, which is the rounding sequence of a right-looking update of the whole trailing matrix.
   bool ok = true;
+  const int tx = tid & 31, ty = tid >> 5, ny = T >> 5;
   for (int k = 0; k < F; ++k) {
+    __syncthreads();                           // the update by pivot k-1 (or the assembly) is complete
     const double piv = A[k + k * lds];
-    if (!(piv > 0.0)) { ok = false; break; }  // Eigen LLT: NumericalIssue when the pivot is <= 0
+    if (!(piv > 0.0)) { ok = false; break; }  // Eigen LLT: NumericalIssue when the pivot is <= 0 (uniform: all threads leave)
     const double r = sqrt(piv);
-    __syncthreads();
     for (int j = k + 1 + tid; j < dim; j += T) A[k + j * lds] /= r;
+    __syncthreads();                           // row k is scaled and everybody has read the pivot
     if (tid == 0) A[k + k * lds] = r;
-    __syncthreads();
-    const int cnt = dim - k - 1;
-    for (int idx = tid; idx < cnt * cnt; idx += T) {
-      const int jj = idx / cnt, ii = idx - jj * cnt;
-      if (ii > jj) continue;
-      const int i = k + 1 + ii, j = k + 1 + jj;
-      A[i + j * lds] -= A[k + i * lds] * A[k + j * lds];
+    for (int i = k + 1 + ty; i < F; i += ny) {
+      const double aki = A[k + i * lds];
+      for (int j = i + tx; j < dim; j += 32) A[i + j * lds] -= aki * A[k + j * lds];
     }
-    __syncthreads();
   }
+  __syncthreads();
+  if (ok) {
+    for (int j = F + ty; j < dim; j += ny) {
+      for (int i = F + tx; i <= j; i += 32) {
+        double acc = A[i + j * lds];
+        for (int k = 0; k < F; ++k) acc -= A[k + i * lds] * A[k + j * lds];
+        A[i + j * lds] = acc;
+      }
+    }
+  }
+  __syncthreads();
   if (ok) {
     // ill-conditioning test on the last two pivots' binary exponents (base/cholesky.cpp:146-158)
     if (F >= 2) ok = frexp_exp(A[(F - 2) + (F - 2) * lds]) - frexp_exp(A[(F - 1) + (F - 1) * lds]) < 12;
@@ -540,6 +550,88 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
     atomicAdd(pdst + a + (int64_t)b * pld, v);
     i += 32;
     while (i > j) { i -= j + 1; ++j; }
+  }
+}
+
+// Conditional rows only (the Schur complement is gathered per camera pair, below): LPP lanes per point.  LPP = 8 packs four
+// points into a warp (up to 8 cameras each: the frontal 3 x 3 block, its Cholesky and the descriptor loads are per point,
+// not per lane, and 9 k + 1 <= 73 columns keep eight lanes busy), LPP = 32 takes the points with more cameras.  Same
+// arithmetic and summation order as point_front_kernel.
+__host__ __device__ __forceinline__ int point_rows_doubles(int kmax) { return 26 * kmax + ((kmax + 1) >> 1) + 1; }
+template <int LPP>
+__global__ void __launch_bounds__(kThinWarps * 32) point_rows_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int kmax) {
+  extern __shared__ double sh[];
+  constexpr int PPW = 32 / LPP;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sl = lane % LPP, sw = lane / LPP;
+  const int slot = (blockIdx.x * kThinWarps + warp) * PPW + sw;
+  if (slot >= count) return;
+  double* ab = sh + (warp * PPW + sw) * point_rows_doubles(kmax);   // ab[26 s + 13 r + col]: rows of factor s
+  int* sfac = reinterpret_cast<int*>(ab + 26 * kmax);               // camera block index -> factor
+  const int c = list[slot];
+  const CliqueDev ci = E.cliques[c];
+  const int k = ci.fac_end - ci.fac_begin, n = ci.S + 1, nc = ci.S;
+  for (int t = sl; t < 26 * k; t += LPP) {
+    const int s = t / 26, r = t - s * 26;
+    const SlotDev sd = E.slots[ci.fac_begin + s];
+    ab[t] = E.Ab[2][(int64_t)sd.index * 26 + r];
+    if (r == 0) sfac[(sd.col0 - 3) / 9] = s;
+  }
+  __syncwarp();
+  double v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0, g0 = 0, g1 = 0, g2 = 0;
+  for (int s = 0; s < k; ++s) {
+    const double* f = ab + 26 * s;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const double p0 = f[13 * r + 9], p1 = f[13 * r + 10], p2 = f[13 * r + 11], br = f[13 * r + 12];
+      v00 += p0 * p0; v01 += p0 * p1; v02 += p0 * p2; v11 += p1 * p1; v12 += p1 * p2; v22 += p2 * p2;
+      g0 += p0 * br; g1 += p1 * br; g2 += p2 * br;
+    }
+  }
+  if (E.damp) {
+    const int32_t* g = E.gidx + ci.gidx_off;
+    v00 += E.damp[g[0]]; v11 += E.damp[g[1]]; v22 += E.damp[g[2]];
+  }
+  bool ok = v00 > 0.0;
+  const double i0 = rsqrt(v00);
+  const double r00 = v00 * i0, r01 = v01 * i0, r02 = v02 * i0;
+  v11 -= r01 * r01; v12 -= r01 * r02; v22 -= r02 * r02;
+  ok = ok && v11 > 0.0;
+  const double i1 = rsqrt(v11);
+  const double r11 = v11 * i1, r12 = v12 * i1;
+  v22 -= r12 * r12;
+  ok = ok && v22 > 0.0;
+  const double i2 = rsqrt(v22);
+  const double r22 = v22 * i2;
+  if (ok) ok = frexp_exp(r11) - frexp_exp(r22) < 12;
+  if (!ok) {
+    if (sl == 0) atomicMin(E.fail, c);
+    return;
+  }
+  const double d0 = 1.0 / r00, d1 = 1.0 / r11, d2 = 1.0 / r22;
+  double2* dst = reinterpret_cast<double2*>(E.arena + ci.front_off);   // ld = 4: one 32-byte column = two 16-byte stores
+  if (sl == 0) {
+    dst[0] = make_double2(r00, 0.0);
+    dst[2] = make_double2(r01, r11);
+    dst[4] = make_double2(r02, r12);
+    dst[5] = make_double2(r22, 0.0);
+  }
+  for (int j = sl; j < n; j += LPP) {
+    double w0, w1, w2;
+    if (j < nc) {
+      const int blk = j / 9, col = j - blk * 9;
+      const double* f = ab + 26 * sfac[blk];
+      const double c0 = f[col], c1 = f[13 + col];
+      w0 = f[9] * c0 + f[22] * c1;
+      w1 = f[10] * c0 + f[23] * c1;
+      w2 = f[11] * c0 + f[24] * c1;
+    } else {
+      w0 = g0; w1 = g1; w2 = g2;
+    }
+    const double y0 = w0 * d0;
+    const double y1 = (w1 - r01 * y0) * d1;
+    const double y2 = (w2 - r02 * y0 - r12 * y1) * d2;
+    dst[2 * (3 + j)] = make_double2(y0, y1);
+    dst[2 * (3 + j) + 1] = make_double2(y2, 0.0);
   }
 }
 

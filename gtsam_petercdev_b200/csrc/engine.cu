@@ -878,7 +878,8 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       LevelSched::Cls cl;
       cl.begin = q0; cl.count = (int32_t)(q - q0); cl.kind = 3; cl.threads = kThinWarps * 32;
       cl.group_doubles = mk;
-      cl.smem = point_front_doubles(mk, !e->point_pairs) * (int32_t)sizeof(double) * kThinWarps;
+      cl.smem = e->point_pairs ? point_rows_doubles(mk) * (int32_t)sizeof(double) * kThinWarps * (mk <= 8 ? 4 : 1)
+                               : point_front_doubles(mk, true) * (int32_t)sizeof(double) * kThinWarps;
       L.small.push_back(cl);
     }
     // thin classes are cut adaptively so that the shared memory of a class (sized by its largest member) stays within
@@ -1302,9 +1303,15 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
   for (int32_t l = 0; l < e->plan.n_levels; ++l) {
     const LevelSched& L = e->sched[phase][l];
     for (const auto& c : L.small) {
-      if (c.kind == 3)
+      if (c.kind == 3 && e->point_pairs && c.group_doubles <= 8)
+        LAUNCH(e, K_POINT, point_rows_kernel<8><<<(c.count + 4 * kThinWarps - 1) / (4 * kThinWarps), c.threads, c.smem, st>>>(
+                               E, lists + c.begin, c.count, c.group_doubles));
+      else if (c.kind == 3 && e->point_pairs)
+        LAUNCH(e, K_POINT, point_rows_kernel<32><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
+                               E, lists + c.begin, c.count, c.group_doubles));
+      else if (c.kind == 3)
         LAUNCH(e, K_POINT, point_front_kernel<<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
-                               E, lists + c.begin, c.count, c.group_doubles, e->point_pairs ? 0 : 1));
+                               E, lists + c.begin, c.count, c.group_doubles, 1));
       else if (c.kind == 0)
         LAUNCH(e, K_THIN, thin_front_kernel<true><<<(c.count + kThinWarps - 1) / kThinWarps, c.threads, c.smem, st>>>(
                               E, lists + c.begin, c.count, c.group_doubles));
@@ -1360,6 +1367,8 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     CK(cudaFuncSetAttribute(small_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(thin_front_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(point_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(point_rows_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(point_rows_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(thin_front_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(front_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem));
     CK(cudaFuncSetAttribute(schur_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmemTile));

@@ -436,6 +436,7 @@ int main(int argc, char** argv) {
       dump_ordering(ord, out);
     } else if (mode == "marginals") {
       // Marginals(graph, values).marginalCovariance(key) for every variable, ascending key (nonlinear/Marginals.cpp)
+      const auto tm0 = std::chrono::steady_clock::now();
       Marginals marginals(B.graph, B.values);
       std::vector<uint64_t> mk;
       std::vector<double> mv;
@@ -446,6 +447,7 @@ int main(int argc, char** argv) {
         md.push_back(Cv.rows());
         for (int r = 0; r < Cv.rows(); ++r) for (int c = 0; c < Cv.cols(); ++c) mv.push_back(Cv(r, c));
       }
+      out.put_f64("t_marginals", {std::chrono::duration<double>(std::chrono::steady_clock::now() - tm0).count()});
       out.put_u64("marginal_keys", mk);
       out.put_i64("marginal_dims", md);
       out.put_f64("marginal_cov", mv);
