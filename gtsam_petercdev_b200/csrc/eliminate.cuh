@@ -210,7 +210,7 @@ __device__ __forceinline__ int tri_col(int idx) {
 }
 
 template <bool WARP>
-__global__ void __launch_bounds__(WARP ? kThinWarps * 32 : 128)
+__global__ void __launch_bounds__(WARP ? kThinWarps * 32 : 512)
 thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int group_doubles) {
   extern __shared__ double sh[];
   __shared__ unsigned char s_star[2 * 91];   // divergent indexing of a __constant__ table serialises: keep a copy here

@@ -893,13 +893,17 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       while (q < b + ns && thin(lc[q]) && dim_of(lc[q]) <= hi) { md = std::max(md, dim_of(lc[q])); ++q; }
       LevelSched::Cls cl;
       cl.begin = q0; cl.count = (int32_t)(q - q0); cl.kind = warp_kind ? 0 : 1;
-      cl.threads = warp_kind ? kThinWarps * 32 : 128;
+      // CTA kind: the front's passes (zero fill, children, write-out with the Schur update) are element-parallel over up to
+      // 21 k packed entries and shared memory already limits a big front to one or two CTAs per SM: more threads per CTA
+      static const int thin_threads = getenv("GTB_THIN_THREADS") ? atoi(getenv("GTB_THIN_THREADS")) : 0;
+      cl.threads = warp_kind ? kThinWarps * 32 : (thin_threads ? thin_threads : (d0 >= 128 ? 512 : (d0 >= 80 ? 256 : 128)));
       cl.group_doubles = ((md * (md + 1) / 2) + 1) & ~1;
       cl.smem = (cl.group_doubles + kThinStage) * (int32_t)sizeof(double) * (warp_kind ? kThinWarps : 1);
       L.small.push_back(cl);
     }
     const int32_t bounds[4] = {32, 64, 96, kDenseMaxDim};
-    const int32_t threads[4] = {32, 64, 128, 256};
+    static const int small_mul = getenv("GTB_SMALL_MUL") ? atoi(getenv("GTB_SMALL_MUL")) : 2;
+    const int32_t threads[4] = {32 * small_mul, 64 * small_mul, 128 * small_mul, 256 * small_mul};
     for (int k = 0; k < 4; ++k) {
       const int64_t q0 = q;
       int32_t md = 0;
