@@ -1,8 +1,13 @@
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -8 > gpurun_out/r18_pytest.log
-for cfg in "c1 metis" "c1 colamd" "c2 metis" "c2 colamd"; do
+python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > gpurun_out/pytest_gpu.log
+python bench.py > gpurun_out/bench_c3_full.json 2> gpurun_out/bench_c3_full.err
+for cfg in "c3 colamd" "c3 schur" "c1 colamd" "c1 metis" "c2 colamd" "c2 metis"; do
   set -- $cfg
-  python bench.py --workload $1 --ordering $2 --steps 10 --no-cpu-baseline > gpurun_out/r18_bench_$1_$2.json 2>/dev/null
-  GTB_THIN_THREADS=128 GTB_SMALL_MUL=1 python bench.py --workload $1 --ordering $2 --steps 10 --no-cpu-baseline > gpurun_out/r18_bench_$1_$2_old.json 2>/dev/null
+  python bench.py --workload $1 --ordering $2 --steps 10 > gpurun_out/bench_$1_$2.json 2> gpurun_out/bench_$1_$2.err
 done
+python bench.py --workload c4 --ordering metis --steps 5 --no-cpu-baseline > gpurun_out/bench_c4_metis.json 2> gpurun_out/bench_c4_metis.err
+python bench.py --impl reference --workload c4 --steps 1 --warmup 0 > gpurun_out/bench_c4_ref.json 2> gpurun_out/bench_c4_ref.err
+GTB_DEBUG=8 python tools/launch_trace.py c3 metis > gpurun_out/launch_trace_c3_metis.txt 2>&1
+tail -2 gpurun_out/smoke.log
