@@ -883,34 +883,51 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       L.small.push_back(cl);
     }
     // thin classes are cut adaptively so that the shared memory of a class (sized by its largest member) stays within
-    // ~20 % of what its smallest member needs: occupancy is limited by shared memory
+    // ~20 % of what its smallest member needs (occupancy is limited by shared memory) -- but only once a class fills the
+    // machine: the launches of a level run one after the other, and a pose-graph level cut into 30 classes of 40 fronts is
+    // 30 launch latencies for an almost empty GPU.  Warp and CTA kinds stay apart (different kernels).
+    constexpr int kMinClass = 2 * 148;   // fronts (CTA kind) or CTAs of 8 fronts (warp kind) before a class may be cut
     while (q < b + ns && thin(lc[q])) {
       const int64_t q0 = q;
       const int d0 = dim_of(lc[q]);
       const bool warp_kind = d0 <= 48;
+      const int kind_max = warp_kind ? 48 : kThinMaxDim;
       const int hi = warp_kind ? (d0 <= 32 ? 32 : (d0 <= 40 ? 40 : 48)) : std::max(d0 + 8, d0 * 6 / 5);
       int32_t md = 0;
-      while (q < b + ns && thin(lc[q]) && dim_of(lc[q]) <= hi) { md = std::max(md, dim_of(lc[q])); ++q; }
+      while (q < b + ns && thin(lc[q]) && dim_of(lc[q]) <= kind_max &&
+             (dim_of(lc[q]) <= hi || (q - q0) < (int64_t)kMinClass * (warp_kind ? kThinWarps : 1))) {
+        md = std::max(md, dim_of(lc[q]));
+        ++q;
+      }
       LevelSched::Cls cl;
       cl.begin = q0; cl.count = (int32_t)(q - q0); cl.kind = warp_kind ? 0 : 1;
       // CTA kind: the front's passes (zero fill, children, write-out with the Schur update) are element-parallel over up to
       // 21 k packed entries and shared memory already limits a big front to one or two CTAs per SM: more threads per CTA
       static const int thin_threads = getenv("GTB_THIN_THREADS") ? atoi(getenv("GTB_THIN_THREADS")) : 0;
-      cl.threads = warp_kind ? kThinWarps * 32 : (thin_threads ? thin_threads : (d0 >= 128 ? 512 : (d0 >= 80 ? 256 : 128)));
+      cl.threads = warp_kind ? kThinWarps * 32 : (thin_threads ? thin_threads : (md >= 128 ? 512 : (md >= 80 ? 256 : 128)));
       cl.group_doubles = ((md * (md + 1) / 2) + 1) & ~1;
       cl.smem = (cl.group_doubles + kThinStage) * (int32_t)sizeof(double) * (warp_kind ? kThinWarps : 1);
       L.small.push_back(cl);
     }
-    const int32_t bounds[4] = {32, 64, 96, kDenseMaxDim};
+    // dense small fronts: thread classes by dimension, merged while a class does not fill the machine
     static const int small_mul = getenv("GTB_SMALL_MUL") ? atoi(getenv("GTB_SMALL_MUL")) : 2;
+    const int32_t bounds[4] = {32, 64, 96, kDenseMaxDim};
     const int32_t threads[4] = {32 * small_mul, 64 * small_mul, 128 * small_mul, 256 * small_mul};
-    for (int k = 0; k < 4; ++k) {
+    while (q < b + ns) {
       const int64_t q0 = q;
       int32_t md = 0;
-      while (q < b + ns && dim_of(lc[q]) <= bounds[k]) { md = std::max(md, dim_of(lc[q])); ++q; }
-      if (q == q0) continue;
+      int kcls = 0;
+      while (q < b + ns) {
+        const int d = dim_of(lc[q]);
+        int kq = 0;
+        while (kq < 3 && d > bounds[kq]) ++kq;
+        if (q > q0 && kq != kcls && (q - q0) >= kMinClass) break;
+        kcls = std::max(kcls, kq);
+        md = std::max(md, d);
+        ++q;
+      }
       LevelSched::Cls cl;
-      cl.begin = q0; cl.count = (int32_t)(q - q0); cl.threads = threads[k]; cl.kind = 2; cl.group_doubles = 0;
+      cl.begin = q0; cl.count = (int32_t)(q - q0); cl.threads = threads[kcls]; cl.kind = 2; cl.group_doubles = 0;
       cl.smem = (md | 1) * md * (int32_t)sizeof(double);
       L.small.push_back(cl);
     }
