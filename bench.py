@@ -285,9 +285,9 @@ def main():
     work = {
         "front_step": ("tensor", (st["flops_large"] - st["flops_syrk_schur"]) / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
         "schur_step": ("tensor", st["flops_syrk_schur"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
-        "small_front": ("hbm", (st["bytes_small"] - st["bytes_thin"]) / 1e9, hbm, "GB/s"),
+        "small_front": ("hbm", st["bytes_dense_small"] / 1e9, hbm, "GB/s"),
         "thin_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
-        "point_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
+        "point_front": ("hbm", st["bytes_point"] / 1e9, hbm, "GB/s"),
         "linearize": ("hbm", st["bytes_linearize"] / 1e9, hbm, "GB/s"),
         "backsolve": ("hbm", st["bytes_backsolve"] / 1e9, hbm, "GB/s"),
     }

@@ -1829,7 +1829,7 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
   const Plan& p = e->plan;
   out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)(e->arena_doubles ? e->arena_doubles : p.arena_doubles);
   out[4] = (double)p.n_small; out[5] = (double)p.n_large; out[6] = p.flops_large; out[7] = p.assembly_bytes;
-  double thin_bytes = 0;
+  double thin_bytes = 0, point_bytes = 0, dense_bytes = 0;
   out[8] = p.flops_syrk_frontal; out[9] = p.flops_syrk_schur; out[10] = p.bytes_backsolve;
   {
     // small fronts also read the whitened rows of their own factors
@@ -1843,12 +1843,19 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
     double bt = 0;
     for (int32_t c = 0; c < p.n_cliques; ++c) {
       const int dim = p.F[c] + p.S[c] + 1;
-      if (!is_thin_front(p.F[c], dim)) continue;
-      bt += 8.0 * 0.5 * dim * (dim + 1);
-      for (int64_t q = p.fac_off[c]; q < p.fac_off[c + 1]; ++q) bt += 8.0 * kMW[e->g_bucket[p.slots[q].factor]];
+      if (!e->is_point.empty() && e->is_point[c]) {
+        // point clique: its factors' whitened rows read, the three conditional rows (32-byte columns) written
+        for (int64_t q = p.fac_off[c]; q < p.fac_off[c + 1]; ++q) point_bytes += 8.0 * kMW[e->g_bucket[p.slots[q].factor]];
+        point_bytes += 32.0 * dim;
+        continue;
+      }
+      if (!is_small_front(p.F[c], dim)) continue;
+      double& acc = is_thin_front(p.F[c], dim) ? bt : dense_bytes;
+      acc += 8.0 * 0.5 * dim * (dim + 1);
+      for (int64_t q = p.fac_off[c]; q < p.fac_off[c + 1]; ++q) acc += 8.0 * kMW[e->g_bucket[p.slots[q].factor]];
       for (int64_t q = p.child_off[c]; q < p.child_off[c + 1]; ++q) {
         const double s1 = p.S[p.children[q]] + 1;
-        bt += 8.0 * 0.5 * s1 * (s1 + 1);
+        acc += 8.0 * 0.5 * s1 * (s1 + 1);
       }
     }
     thin_bytes = bt;
@@ -1862,7 +1869,7 @@ gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
                                   8.0 * kM[k] * kW[k]);
     out[12] = b;
   }
-  out[13] = thin_bytes; out[14] = out[15] = 0;
+  out[13] = thin_bytes; out[14] = point_bytes; out[15] = dense_bytes;
   return GTB_OK;
 }
 

@@ -134,7 +134,7 @@ class Engine:
         stats = np.zeros(16)
         self._ck(self.lib.gtb_plan_stats(self.h, _ptr(stats)))
         names = ["levels", "max_front", "flops", "arena_doubles", "n_small", "n_large", "flops_large", "assembly_bytes",
-                 "flops_syrk_frontal", "flops_syrk_schur", "bytes_backsolve", "bytes_small", "bytes_linearize", "bytes_thin"]
+                 "flops_syrk_frontal", "flops_syrk_schur", "bytes_backsolve", "bytes_small", "bytes_linearize", "bytes_thin", "bytes_point", "bytes_dense_small"]
         return dict(clique_nfrontal=nfrontal, clique_nkeys=nkeys, clique_keys=keys, clique_parent=parent,
                     n_conditional_doubles=ncond.value, n_scalars=ns.value, stats=dict(zip(names, stats.tolist())))
 

@@ -98,7 +98,8 @@ gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, 
  * doubles, [4]=small-front cliques, [5]=large-front cliques, [6]=flops in large fronts, [7]=assembly bytes,
  * [8]=flops of the frontal trailing updates of large fronts, [9]=flops of their Schur updates, [10]=algorithmic
  * bytes of back-substitution, [11]=algorithmic bytes of small-front elimination, [12]=algorithmic bytes of
- * linearize (SURVEY 8d formula), [13..15]=0                                                                */
+ * linearize (SURVEY 8d formula), [13]=the part of [11] in thin fronts, [14]=algorithmic bytes of point cliques
+ * (factor rows read, three conditional rows written), [15]=the part of [11] in dense small fronts            */
 gtb_status gtb_plan_stats(const gtb_engine* e, double* out16);
 
 /* ---- per outer iteration ---------------------------------------------------------------------------- */

@@ -6,7 +6,7 @@ import re
 import sys
 from collections import defaultdict
 
-CLASS = {"front_step_kernel": "front_step", "schur_step_kernel": "schur_step", "thin_front_kernel": "thin_front", "point_front_kernel": "point_front",
+CLASS = {"front_step_kernel": "front_step", "schur_step_kernel": "schur_step", "thin_front_kernel": "thin_front", "point_front_kernel": "point_front", "point_rows_kernel": "point_front",
          "point_pair_kernel": "point_schur", "point_diag_kernel": "point_schur",
          "small_front_kernel": "small_front", "large_children_kernel": "large_children", "large_zero_kernel": "large_zero",
          "large_factors_kernel": "large_factors", "backsolve_kernel": "backsolve", "backsolve_gemv_kernel": "backsolve_gemv",
