@@ -1390,10 +1390,57 @@ backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t
   scratch[scratch_off[blockIdx.x] + (int64_t)blockIdx.z * F + i] = (a0 + a1) + (a2 + a3);
 }
 
+// Inverses of the 32 x 32 diagonal blocks of R of the CTA-class cliques, one warp per block, once per factorisation:
+// with them a block of the back-substitution is a 32 x 32 matrix-vector product instead of a chain of 32 dependent
+// pivots.  task = (clique, block, destination block); out block layout [column k][row l], 1024 doubles, zero below
+// the diagonal, identity on the padding of a ragged last block.  Lane j solves R x = e_j from the bottom up with 32
+// running sums (right-looking), so the dependent chain is one multiply-add per row.
+constexpr int kInvWarps = 4;
+__global__ void __launch_bounds__(kInvWarps * 32)
+diag_inverse_kernel(ElimDev E, const int32_t* __restrict__ tasks, int count, double* __restrict__ rinv) {
+  __shared__ double us[kInvWarps][32 * 33 + 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int t = blockIdx.x * kInvWarps + warp;
+  pdl_trigger();
+  if (t >= count) return;
+  const int32_t c = tasks[3 * t], bi = tasks[3 * t + 1], dstb = tasks[3 * t + 2];
+  const CliqueDev ci = E.cliques[c];
+  pdl_wait();
+  const int ld = ci.ld, b0 = bi * 32, kb = min(32, ci.F - b0);
+  const double* A = E.arena + ci.front_off;
+  double* u = us[warp];            // u[k * 33 + i] = R(b0 + i, b0 + k), i <= k
+  double* rd = u + 32 * 33;        // reciprocal diagonal
+  for (int k = 0; k < 32; ++k) {
+    double v = (k == lane) ? 1.0 : 0.0;
+    if (k < kb && lane <= k) v = A[(b0 + lane) + (int64_t)(b0 + k) * ld];
+    u[k * 33 + lane] = v;
+    if (k == lane) rd[lane] = 1.0 / v;
+  }
+  __syncwarp();
+  double sum[32], x[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) sum[i] = 0.0;
+#pragma unroll
+  for (int k = 31; k >= 0; --k) {
+    const double xk = ((k == lane ? 1.0 : 0.0) - sum[k]) * rd[k];
+    x[k] = (k <= lane) ? xk : 0.0;
+#pragma unroll
+    for (int i = 0; i < k; ++i) sum[i] += u[k * 33 + i] * x[k];
+  }
+  // column `lane` of the inverse -> out[lane * 32 + i], through shared memory so that the stores are coalesced
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) u[lane * 33 + i] = x[i];
+  __syncwarp();
+  double* out = rinv + (int64_t)dstb * 1024;
+  for (int k = 0; k < 32; ++k) out[k * 32 + lane] = u[k * 33 + lane];
+}
+
 template <bool WARP>
 __global__ void __launch_bounds__(WARP ? kBsWarps * 32 : kBsCtaThreads)
 backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta,
-                 const int32_t* __restrict__ scratch_off, const double* __restrict__ scratch) {
+                 const int32_t* __restrict__ scratch_off, const double* __restrict__ scratch,
+                 const int32_t* __restrict__ rinv_off, const double* __restrict__ rinv) {
   extern __shared__ double sh[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = WARP ? blockIdx.x * kBsWarps + warp : blockIdx.x;
@@ -1489,30 +1536,28 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
     if (lane < kb) rhs[lane] = my;
   } else {
     // CTA variant, software-pipelined over the 32-row blocks: ONE barrier per block.  Warp 0 walks the dependent chain
-    // alone: solve block b in registers, publish x_b, and fold x_b's contribution to block b-1 (the 32 x 32 block
-    // R[b-1, b], prefetched into registers before the solve) into its next right-hand side itself.  The other warps run
-    // one block behind: after the barrier they apply x_b to every row above block b-1 (32 loads in flight per row) and
-    // stage the diagonal block warp 0 needs two steps later, while warp 0 is already solving block b-1.  A row's sum
-    // still runs over the blocks in descending order, as in the plain right-looking loop.
+    // alone: x_b = inv(R[b, b]) r_b with the inverse block diag_inverse_kernel left (a 32 x 32 matrix-vector product,
+    // no pivot chain), publish x_b, and fold x_b's contribution to block b-1 (the 32 x 32 block R[b-1, b], prefetched
+    // into registers before the barrier) into its next right-hand side itself.  The other warps run one block behind:
+    // after the barrier they apply x_b to every row above block b-1 (32 loads in flight per row) and stage the inverse
+    // block warp 0 needs two steps later (its loads are issued before the barrier too), while warp 0 is already on
+    // block b-1.  A row's sum still runs over the blocks in descending order, as in the plain right-looking loop.
     double* xbuf = xblk;             // [2][32]: x of the block just solved (double-buffered)
-    double* dblk = xblk + 64;        // [2][32 * 33]: dblk[k * 33 + l] = R(b0 + l, b0 + k) of the block to solve
+    double* dblk = xblk + 64;        // [2][32 * 33]: dblk[k * 33 + l] = inv(R[b, b])(l, k) of the block to solve
     const int nb = (F + 31) / 32;
-    auto stage_diag = [&](int bq, int t0, int nt) {   // diagonal block bq -> dblk[bq & 1], by threads t0 .. t0 + nt - 1
-      const int q0 = bq * 32, kq = min(32, F - q0);
+    const double* inv = rinv + (int64_t)rinv_off[slot] * 1024;
+    constexpr int kStagePer = (1024 + kBsCtaThreads - 32 - 1) / (kBsCtaThreads - 32);   // elements per staging thread
+    for (int bq = nb - 1; bq >= max(0, nb - 2); --bq) {
       double* dst = dblk + (bq & 1) * (32 * 33);
-      for (int q = gtid - t0; q < 1024; q += nt) {
-        const int k = q >> 5, l = q & 31;
-        dst[k * 33 + l] = (k < kq && l <= k) ? A[(q0 + l) + (int64_t)(q0 + k) * ld] : 1.0;
-      }
-    };
-    stage_diag(nb - 1, 0, gsize);
-    if (nb >= 2) stage_diag(nb - 2, 0, gsize);
+      for (int q = gtid; q < 1024; q += gsize) dst[(q >> 5) * 33 + (q & 31)] = inv[(int64_t)bq * 1024 + q];
+    }
     __syncthreads();
     double carry = 0.0;   // warp 0: (R[b, b+1] x_{b+1})(lane)
     for (int bi = nb - 1; bi >= 0; --bi) {
       const int b0 = bi * 32, kb = min(32, F - b0);
       double w[32];       // warp 0: R[b-1, b], row b0 - 32 + lane; other warps: their first row of this block's update.
-                          // Loaded before the solve / the barrier: in flight while warp 0 solves block b.
+                          // Loaded before the barrier: in flight while warp 0 is on block b.
+      double sd[kStagePer];   // other warps: their elements of the inverse block b-2
       const int i1 = warp == 0 ? b0 - 32 + lane : gtid - 32;
       const bool have = warp == 0 ? bi >= 1 : i1 < b0 - 32;
       {
@@ -1520,21 +1565,25 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
 #pragma unroll
         for (int k = 0; k < 32; ++k) w[k] = (have && k < kb) ? row[(int64_t)k * ld] : 0.0;
       }
+      if (warp > 0 && bi >= 2) {
+#pragma unroll
+        for (int n = 0; n < kStagePer; ++n) {
+          const int q = gtid - 32 + n * (kBsCtaThreads - 32);
+          sd[n] = q < 1024 ? inv[(int64_t)(bi - 2) * 1024 + q] : 0.0;
+        }
+      }
       if (warp == 0) {
         const double* db = dblk + (bi & 1) * (32 * 33);
-        double my = (lane < kb) ? rhs[b0 + lane] - carry : 0.0;
-        const double rd = 1.0 / db[lane * 33 + lane];   // reciprocal of this lane's diagonal entry (1.0 on the padding)
-        double rk = db[31 * 33 + lane];
+        const double r = (lane < kb) ? rhs[b0 + lane] - carry : 0.0;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
 #pragma unroll
-        for (int k = 31; k >= 0; --k) {
-          const double rk_next = db[(k > 0 ? k - 1 : 0) * 33 + lane];   // one step ahead of its use
-          if (k < kb) {
-            const double xk = __shfl_sync(0xffffffffu, my, k) * __shfl_sync(0xffffffffu, rd, k);
-            if (lane == k) my = xk;
-            else if (lane < k) my -= rk * xk;
-          }
-          rk = rk_next;
+        for (int k = 0; k < 32; k += 4) {
+          s0 += db[k * 33 + lane] * __shfl_sync(0xffffffffu, r, k);
+          s1 += db[(k + 1) * 33 + lane] * __shfl_sync(0xffffffffu, r, k + 1);
+          s2 += db[(k + 2) * 33 + lane] * __shfl_sync(0xffffffffu, r, k + 2);
+          s3 += db[(k + 3) * 33 + lane] * __shfl_sync(0xffffffffu, r, k + 3);
         }
+        const double my = (s0 + s1) + (s2 + s3);
         if (lane < kb) rhs[b0 + lane] = my;
         double* xb = xbuf + (bi & 1) * 32;
         xb[lane] = (lane < kb) ? my : 0.0;
@@ -1559,6 +1608,14 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
           }
           rhs[i1] -= a0 + a1;
         }
+        if (bi >= 2) {   // into the buffer of block b, which warp 0 has left
+          double* dst = dblk + (bi & 1) * (32 * 33);
+#pragma unroll
+          for (int n = 0; n < kStagePer; ++n) {
+            const int q = gtid - 32 + n * (kBsCtaThreads - 32);
+            if (q < 1024) dst[(q >> 5) * 33 + (q & 31)] = sd[n];
+          }
+        }
         for (int i = i1 + gsize - 32; i < b0 - 32; i += gsize - 32) {
           const double* row = A + i + (int64_t)b0 * ld;
           double u[32];
@@ -1572,7 +1629,6 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
           }
           rhs[i] -= a0 + a1;
         }
-        if (bi >= 2) stage_diag(bi - 2, 32, gsize - 32);   // into the buffer of block b, which warp 0 has left
       }
     }
   }

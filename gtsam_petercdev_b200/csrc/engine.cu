@@ -149,6 +149,11 @@ struct gtb_engine {
   int32_t n_top_work = 0;
   std::vector<int32_t> bs_list, bs_scratch_off;
   int64_t bs_scratch_doubles = 0;
+  // inverse diagonal blocks of the CTA-class cliques (diag_inverse_kernel): first block per list slot, (clique, block,
+  // destination) tasks per phase
+  std::vector<int32_t> bs_rinv_off, rinv_tasks;
+  int64_t rinv_blocks = 0;
+  int64_t rinv_task_begin[2] = {0, 0}, rinv_task_count[2] = {0, 0};
   std::vector<StepTask> step_tasks_list;
   bool point_pairs = true;            // false (GTB_POINT_ATOMIC=1): point cliques scatter their Schur complement with atomics
   std::vector<PairSeg> pair_segs;     // segments of both kinds, both phases
@@ -173,8 +178,8 @@ struct gtb_engine {
   DevBuf<int32_t> d_inc_bucket, d_inc_index, d_inc_slot, d_var_goff, d_var_dim;
   DevBuf<CliqueDev> d_cliques;
   DevBuf<SlotDev> d_slots;
-  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list, d_bs_scratch_off;
-  DevBuf<double> d_bs_scratch, d_delta_own;
+  DevBuf<int32_t> d_children, d_pmap, d_gidx, d_level_cliques, d_fail, d_bs_list, d_bs_scratch_off, d_bs_rinv_off, d_rinv_tasks;
+  DevBuf<double> d_bs_scratch, d_bs_rinv, d_delta_own;
   DevBuf<int32_t> d_top_list, d_large_list;
   DevBuf<uint8_t> d_own_mask;
   DevBuf<ChildWork> d_child_work;
@@ -750,6 +755,7 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
   const Plan& p = e->plan;
   std::vector<LevelSched>& sched = e->sched[ph];
   sched.assign(p.n_levels, LevelSched());
+  e->rinv_task_begin[ph] = (int64_t)e->rinv_tasks.size() / 3;
   auto mine = [&](int32_t c) { return ph == 0 ? e->owner[c] == e->rank : e->owner[c] < 0; };
   for (int32_t l = 0; l < p.n_levels; ++l) {
     LevelSched& L = sched[l];
@@ -848,11 +854,19 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
     {
       int64_t off = 0;
       e->bs_scratch_off.resize(e->bs_list.size(), 0);
+      e->bs_rinv_off.resize(e->bs_list.size(), 0);
       for (int64_t q = L.bs_begin + L.n_bs_warp; q < (int64_t)e->bs_list.size(); ++q) {
         const int32_t c = e->bs_list[q];
         e->bs_scratch_off[q] = (int32_t)off;
         off += (int64_t)p.F[c] * ((p.S[c] + kGemvCols - 1) / kGemvCols);
+        e->bs_rinv_off[q] = (int32_t)e->rinv_blocks;
+        for (int32_t bi = 0; bi < (p.F[c] + 31) / 32; ++bi) {
+          e->rinv_tasks.push_back(c);
+          e->rinv_tasks.push_back(bi);
+          e->rinv_tasks.push_back((int32_t)e->rinv_blocks++);
+        }
       }
+      need(e->rinv_blocks < INT32_MAX / 2, "back-substitution inverse blocks overflow");
       need(off < INT32_MAX, "back-substitution scratch overflow");
       e->bs_scratch_doubles = std::max(e->bs_scratch_doubles, off);
     }
@@ -1039,6 +1053,9 @@ static void install_plan(Engine* e) {
   e->bs_list.clear();
   e->bs_scratch_off.clear();
   e->bs_scratch_doubles = 0;
+  e->bs_rinv_off.clear();
+  e->rinv_tasks.clear();
+  e->rinv_blocks = 0;
   e->step_tasks_list.clear();
   e->is_point.assign(C, 0);
   for (int32_t c = 0; c < C; ++c) {
@@ -1065,6 +1082,8 @@ static void install_plan(Engine* e) {
   lc.reserve(C);
   build_phase(e, 0, lc);
   build_phase(e, 1, lc);
+  e->rinv_task_count[0] = e->rinv_task_begin[1] - e->rinv_task_begin[0];
+  e->rinv_task_count[1] = (int64_t)e->rinv_tasks.size() / 3 - e->rinv_task_begin[1];
   e->sched_lists = lc;
   if (getenv("GTB_DUMP_SCHED")) {   // the large-front schedule, one line per level and per Schur-step launch
     for (int ph = 0; ph < 2; ++ph)
@@ -1173,6 +1192,9 @@ static void install_plan(Engine* e) {
   e->d_bs_list.upload(e->bs_list, st);
   e->d_bs_scratch_off.upload(e->bs_scratch_off, st);
   e->d_bs_scratch.alloc((size_t)e->bs_scratch_doubles + 1);
+  e->d_bs_rinv_off.upload(e->bs_rinv_off, st);
+  e->d_rinv_tasks.upload(e->rinv_tasks, st);
+  e->d_bs_rinv.alloc((size_t)e->rinv_blocks * 1024 + 1);
   e->d_step_tasks.upload(e->step_tasks_list, st);
   e->d_pair_segs.upload(e->pair_segs, st);
   e->d_pair_items.upload(e->pair_items, st);
@@ -1433,14 +1455,19 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
 }
 
 static void backsolve_levels(Engine* e, const ElimDev& E, int phase) {
+  if (e->rinv_task_count[phase] > 0)
+    LAUNCH(e, K_BACKSOLVE, launch_pdl(diag_inverse_kernel, (int)((e->rinv_task_count[phase] + kInvWarps - 1) / kInvWarps), kInvWarps * 32, 0,
+                                      e->stream, E, (const int32_t*)e->d_rinv_tasks.p + 3 * e->rinv_task_begin[phase],
+                                      (int)e->rinv_task_count[phase], e->d_bs_rinv.p));
   for (int32_t l = e->plan.n_levels - 1; l >= 0; --l) {
     const LevelSched& L = e->sched[phase][l];
     const int32_t* bl = e->d_bs_list.p + L.bs_begin;
     const int32_t* so = e->d_bs_scratch_off.p + L.bs_begin;
+    const int32_t* ro = e->d_bs_rinv_off.p + L.bs_begin;
     if (L.n_bs_warp)
       LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<true>, (L.n_bs_warp + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
                                         kBsWarps * kBsWarpDoubles * sizeof(double), e->stream, E, bl, L.n_bs_warp, e->d_delta.p,
-                                        so, (const double*)e->d_bs_scratch.p));
+                                        so, (const double*)e->d_bs_scratch.p, ro, (const double*)e->d_bs_rinv.p));
     if (L.n_bs_cta) {
       if (L.bs_max_S > 0)
         LAUNCH(e, K_BSGEMV, launch_pdl(backsolve_gemv_kernel,
@@ -1448,7 +1475,8 @@ static void backsolve_levels(Engine* e, const ElimDev& E, int phase) {
                                        kGemvRows, 0, e->stream, E, bl + L.n_bs_warp, so + L.n_bs_warp, (const double*)e->d_delta.p,
                                        e->d_bs_scratch.p));
       LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<false>, L.n_bs_cta, kBsCtaThreads, L.bs_cta_smem, e->stream, E, bl + L.n_bs_warp,
-                                        L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, (const double*)e->d_bs_scratch.p));
+                                        L.n_bs_cta, e->d_delta.p, so + L.n_bs_warp, (const double*)e->d_bs_scratch.p, ro + L.n_bs_warp,
+                                        (const double*)e->d_bs_rinv.p));
     }
   }
 }
