@@ -1356,6 +1356,18 @@ backsolve_gemv_kernel(ElimDev E, const int32_t* __restrict__ list, const int32_t
   const int F = ci.F, S = ci.S, ld = ci.ld;
   const int i0 = blockIdx.y * kGemvRows, j0 = blockIdx.z * kGemvCols;
   if (i0 >= F || j0 >= S) return;
+  {
+    // The CTA that solves this clique next reads the triangle of R alone, one memory latency per 32-row block: ask L2
+    // for it from here, a few lines per thread over all the CTAs of the clique (R does not depend on the level above,
+    // so this runs before the wait).
+    const int lines = (F + 15) / 16;   // 128-byte lines per column of R
+    const int nz = (S + kGemvCols - 1) / kGemvCols, ny = (F + kGemvRows - 1) / kGemvRows;
+    const double* R = E.arena + ci.front_off;
+    for (int q = (blockIdx.y * nz + blockIdx.z) * kGemvRows + threadIdx.x; q < F * lines; q += ny * nz * kGemvRows) {
+      const int col = q / lines, r0 = (q - col * lines) * 16;
+      if (r0 <= col) asm volatile("prefetch.global.L2 [%0];" ::"l"(R + r0 + (int64_t)col * ld));
+    }
+  }
   pdl_wait();
   __shared__ double xs[kGemvCols];
   const int nj = min(kGemvCols, S - j0);
@@ -1410,14 +1422,18 @@ diag_inverse_kernel(ElimDev E, const int32_t* __restrict__ tasks, int count, dou
   const double* A = E.arena + ci.front_off;
   double* u = us[warp];            // u[k * 33 + i] = R(b0 + i, b0 + k), i <= k
   double* rd = u + 32 * 33;        // reciprocal diagonal
+  double sum[32], x[32];
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {   // all 32 loads in flight before the first store
+    x[k] = (k == lane) ? 1.0 : 0.0;
+    if (k < kb && lane <= k) x[k] = A[(b0 + lane) + (int64_t)(b0 + k) * ld];
+  }
+#pragma unroll
   for (int k = 0; k < 32; ++k) {
-    double v = (k == lane) ? 1.0 : 0.0;
-    if (k < kb && lane <= k) v = A[(b0 + lane) + (int64_t)(b0 + k) * ld];
-    u[k * 33 + lane] = v;
-    if (k == lane) rd[lane] = 1.0 / v;
+    u[k * 33 + lane] = x[k];
+    if (k == lane) rd[lane] = 1.0 / x[k];
   }
   __syncwarp();
-  double sum[32], x[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) sum[i] = 0.0;
 #pragma unroll
@@ -1563,13 +1579,16 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
       {
         const double* row = A + (have ? i1 : 0) + (int64_t)b0 * ld;
 #pragma unroll
-        for (int k = 0; k < 32; ++k) w[k] = (have && k < kb) ? row[(int64_t)k * ld] : 0.0;
+        for (int k = 0; k < 32; ++k) w[k] = row[(int64_t)min(k, kb - 1) * ld];   // plain loads: a select behind each
+                                                                                   // would wait for it here (measured:
+                                                                                   // 3.0k of 4.5k cycles per block);
+                                                                                   // x_b is 0 beyond kb
       }
       if (warp > 0 && bi >= 2) {
 #pragma unroll
         for (int n = 0; n < kStagePer; ++n) {
           const int q = gtid - 32 + n * (kBsCtaThreads - 32);
-          sd[n] = q < 1024 ? inv[(int64_t)(bi - 2) * 1024 + q] : 0.0;
+          sd[n] = inv[(int64_t)(bi - 2) * 1024 + min(q, 1023)];
         }
       }
       if (warp == 0) {
@@ -1620,7 +1639,7 @@ backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double*
           const double* row = A + i + (int64_t)b0 * ld;
           double u[32];
 #pragma unroll
-          for (int k = 0; k < 32; ++k) u[k] = (k < kb) ? row[(int64_t)k * ld] : 0.0;
+          for (int k = 0; k < 32; ++k) u[k] = row[(int64_t)min(k, kb - 1) * ld];
           double a0 = 0.0, a1 = 0.0;
 #pragma unroll
           for (int k = 0; k < 32; k += 2) {
