@@ -875,6 +875,22 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
     if (s < nchunk) fetch(ka + s * NB, s);
     cp_async_commit();
   }
+  // This thread's 16 entries of C are loaded here, behind the first operand copies, and the product is accumulated onto
+  // -C.  Loading them in the epilogue (C[i, j] -= acc) is 16 dependent round trips to L2 per thread: the compiler may
+  // not move an entry's load above the previous entry's store or atomic.
+  if (MODE == 0 || (MODE == 2 && add_c)) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int i = r0 + wr * 32 + a * 8 + g;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = c0 + wc * 16 + b * 8 + 2 * t + e;
+          if (i < re && j < dim && i <= j) acc[a][b][e] = -A[i + (int64_t)j * ld];
+        }
+      }
+  }
   for (int ch = 0; ch < nchunk; ++ch) {
     cp_async_wait<kStages - 2>();   // chunk ch has landed (for this thread's copies)
     __syncthreads();                // ... and for everybody's; also: everybody is done with the buffer refilled below
@@ -908,11 +924,11 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
           if (MODE == 2) {
             int pa = pm[i - F], pb = pm[j - F];
             if (pa > pb) { const int tt = pa; pa = pb; pb = tt; }
-            atomicAdd(PA + pa + (int64_t)pb * pld, (add_c ? A[i + (int64_t)j * ld] : 0.0) - acc[a][b][e]);
+            atomicAdd(PA + pa + (int64_t)pb * pld, -acc[a][b][e]);
           } else if (MODE == 1) {
             atomicAdd(A + i + (int64_t)j * ld, -acc[a][b][e]);
           } else {
-            A[i + (int64_t)j * ld] -= acc[a][b][e];
+            A[i + (int64_t)j * ld] = -acc[a][b][e];
           }
         }
       }
