@@ -878,6 +878,22 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
   // This thread's 16 entries of C are loaded here, behind the first operand copies, and the product is accumulated onto
   // -C.  Loading them in the epilogue (C[i, j] -= acc) is 16 dependent round trips to L2 per thread: the compiler may
   // not move an entry's load above the previous entry's store or atomic.
+  int prow[4], pcol[2][2];   // MODE 2: parent positions of this thread's rows and columns (same reason: 8 loads here
+                             // instead of two in front of every atomic)
+  if (MODE == 2) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      const int i = r0 + wr * 32 + a * 8 + g;
+      prow[a] = i < re ? pm[i - F] : 0;
+    }
+#pragma unroll
+    for (int b = 0; b < 2; ++b)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int j = c0 + wc * 16 + b * 8 + 2 * t + e;
+        pcol[b][e] = j < dim ? pm[j - F] : 0;
+      }
+  }
   if (MODE == 0 || (MODE == 2 && add_c)) {
 #pragma unroll
     for (int a = 0; a < 4; ++a)
@@ -922,7 +938,7 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
         const int j = c0 + wc * 16 + b * 8 + 2 * t + e;
         if (i < re && j < dim && i <= j) {
           if (MODE == 2) {
-            int pa = pm[i - F], pb = pm[j - F];
+            int pa = prow[a], pb = pcol[b][e];
             if (pa > pb) { const int tt = pa; pa = pb; pb = tt; }
             atomicAdd(PA + pa + (int64_t)pb * pld, -acc[a][b][e]);
           } else if (MODE == 1) {
