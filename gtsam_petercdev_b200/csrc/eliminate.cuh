@@ -570,11 +570,45 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_rows_kernel(ElimDev E, 
   const int c = list[slot];
   const CliqueDev ci = E.cliques[c];
   const int k = ci.fac_end - ci.fac_begin, n = ci.S + 1, nc = ci.S;
-  for (int t = sl; t < 26 * k; t += LPP) {
-    const int s = t / 26, r = t - s * 26;
-    const SlotDev sd = E.slots[ci.fac_begin + s];
-    ab[t] = E.Ab[2][(int64_t)sd.index * 26 + r];
-    if (r == 0) sfac[(sd.col0 - 3) / 9] = s;
+  // A lane's time is its chain of dependent round trips: the slot descriptors of the point's factors are loaded by one
+  // lane each (and the positions of its damping terms), then every row load of the point is issued in one batch (and
+  // the damping terms with it).  (A `for t: slot -> row` loop compiles to two round trips per 4 entries and two per
+  // entry of the remainder: 8 instead of 2 for a point seen by 2..4 cameras.)
+  const unsigned gmask = LPP == 32 ? 0xffffffffu : (((1u << LPP) - 1u) << (sw * LPP));
+  const int gbase = sw * LPP;
+  int idx0 = 0, idx1 = 0, gq = 0;
+  if (E.damp) gq = E.gidx[ci.gidx_off + (sl < 3 ? sl : 0)];
+  if (sl < k) {
+    const SlotDev sd = E.slots[ci.fac_begin + sl];
+    idx0 = sd.index;
+    sfac[(sd.col0 - 3) / 9] = sl;
+  }
+  if (LPP == 32 && sl + 32 < k) {
+    const SlotDev sd = E.slots[ci.fac_begin + sl + 32];
+    idx1 = sd.index;
+    sfac[(sd.col0 - 3) / 9] = sl + 32;
+  }
+  const double dq = E.damp ? E.damp[gq] : 0.0;
+  constexpr int kBatch = 13;   // one batch covers a point seen by LPP / 2 cameras
+  for (int tb = 0; tb < 26 * k; tb += kBatch * LPP) {   // same trip count in every lane of the group (shuffles inside)
+    const int t0 = tb + sl;
+    double v[kBatch];
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int t = t0 + u * LPP;
+      const int s = min(t / 26, k - 1), r = t - (t / 26) * 26;
+      int idx = __shfl_sync(gmask, idx0, gbase + (s & (LPP - 1)));
+      if (LPP == 32) {
+        const int hi = __shfl_sync(gmask, idx1, s & 31);
+        if (s >= 32) idx = hi;
+      }
+      v[u] = t < 26 * k ? E.Ab[2][(int64_t)idx * 26 + r] : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int t = t0 + u * LPP;
+      if (t < 26 * k) ab[t] = v[u];
+    }
   }
   __syncwarp();
   double v00 = 0, v01 = 0, v02 = 0, v11 = 0, v12 = 0, v22 = 0, g0 = 0, g1 = 0, g2 = 0;
@@ -587,9 +621,9 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_rows_kernel(ElimDev E, 
       g0 += p0 * br; g1 += p1 * br; g2 += p2 * br;
     }
   }
-  if (E.damp) {
-    const int32_t* g = E.gidx + ci.gidx_off;
-    v00 += E.damp[g[0]]; v11 += E.damp[g[1]]; v22 += E.damp[g[2]];
+  {
+    const double q0 = __shfl_sync(gmask, dq, gbase), q1 = __shfl_sync(gmask, dq, gbase + 1), q2 = __shfl_sync(gmask, dq, gbase + 2);
+    if (E.damp) { v00 += q0; v11 += q1; v22 += q2; }
   }
   bool ok = v00 > 0.0;
   const double i0 = rsqrt(v00);
