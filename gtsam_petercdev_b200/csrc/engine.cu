@@ -1018,8 +1018,14 @@ static void build_point_pairs(Engine* e) {
           const int32_t P = (int32_t)(recs[i].key >> 42), A = (int32_t)((recs[i].key >> 21) & 0x1fffff), B = (int32_t)(recs[i].key & 0x1fffff);
           const int32_t ldp = e->ld[P], NP = p.F[P] + p.S[P];
           const int64_t dst = e->front_off[P] + A + (int64_t)(diag ? A : B) * ldp;
-          for (size_t s0 = i; s0 < j; s0 += kPairSeg)
-            segs.push_back(PairSeg{dst, ldp, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(kPairSeg, j - s0), NP - A});
+          // a thread walks its segment one item at a time (item -> rows: dependent round trips), so the cap sets the
+          // length of the longest chain in the launch; GTB_PAIR_SEG / GTB_DIAG_SEG override it for experiments
+          static const size_t cap_pair = getenv("GTB_PAIR_SEG") ? (size_t)std::max(1, atoi(getenv("GTB_PAIR_SEG"))) : (size_t)kPairSeg;
+          static const size_t cap_diag = getenv("GTB_DIAG_SEG") ? (size_t)std::max(1, atoi(getenv("GTB_DIAG_SEG"))) : (size_t)kPairSeg / 2;   // same-camera lists are long
+                                                                                                                              // (≈400 points a camera): 16 measured best
+          const size_t cap = diag ? cap_diag : cap_pair;
+          for (size_t s0 = i; s0 < j; s0 += cap)
+            segs.push_back(PairSeg{dst, ldp, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(cap, j - s0), NP - A});
           i = j;
         }
         need(item0 + (int64_t)recs.size() < INT32_MAX, "point pair list overflow");
