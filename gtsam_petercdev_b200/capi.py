@@ -69,6 +69,7 @@ _SIGS = {
     "gtb_set_robust": (C.c_int, [_P, C.c_int, C.c_int, C.c_double]),
     "gtb_set_distributed": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P]),
     "gtb_partition_get": (C.c_int, [_P, _P, _P]),
+    "gtb_schedule_check": (C.c_int, [_P, _P]),
     "gtb_marginals_compute": (C.c_int, [_P]),
     "gtb_marginal_covariance": (C.c_int, [_P, C.c_int64, _P, _P]),
     "gtb_dataset_read_g2o": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_P)]),

@@ -969,6 +969,11 @@ template <class R> static void radix_sort_by_key(std::vector<R>& v) {
 // and phase, the (parent, block row, block column) groups of all its point cliques, items in list order, cut into
 // segments of at most kPairSeg items, longest segments first.
 static void build_point_pairs(Engine* e) {
+  // A thread walks its segment one item at a time (item -> rows: dependent round trips), so the cap sets the length of
+  // the longest chain in the launch.  Same-camera lists are long (≈400 points a camera): 16 measured best on C3.
+  // GTB_PAIR_SEG / GTB_DIAG_SEG override the caps for experiments.
+  const size_t cap_pair = getenv("GTB_PAIR_SEG") ? (size_t)std::max(1, atoi(getenv("GTB_PAIR_SEG"))) : (size_t)kPairSeg;
+  const size_t cap_diag = getenv("GTB_DIAG_SEG") ? (size_t)std::max(1, atoi(getenv("GTB_DIAG_SEG"))) : (size_t)kPairSeg / 2;
   const Plan& p = e->plan;
   e->pair_segs.clear();
   e->pair_items.clear();
@@ -1018,11 +1023,6 @@ static void build_point_pairs(Engine* e) {
           const int32_t P = (int32_t)(recs[i].key >> 42), A = (int32_t)((recs[i].key >> 21) & 0x1fffff), B = (int32_t)(recs[i].key & 0x1fffff);
           const int32_t ldp = e->ld[P], NP = p.F[P] + p.S[P];
           const int64_t dst = e->front_off[P] + A + (int64_t)(diag ? A : B) * ldp;
-          // a thread walks its segment one item at a time (item -> rows: dependent round trips), so the cap sets the
-          // length of the longest chain in the launch; GTB_PAIR_SEG / GTB_DIAG_SEG override it for experiments
-          static const size_t cap_pair = getenv("GTB_PAIR_SEG") ? (size_t)std::max(1, atoi(getenv("GTB_PAIR_SEG"))) : (size_t)kPairSeg;
-          static const size_t cap_diag = getenv("GTB_DIAG_SEG") ? (size_t)std::max(1, atoi(getenv("GTB_DIAG_SEG"))) : (size_t)kPairSeg / 2;   // same-camera lists are long
-                                                                                                                              // (≈400 points a camera): 16 measured best
           const size_t cap = diag ? cap_diag : cap_pair;
           for (size_t s0 = i; s0 < j; s0 += cap)
             segs.push_back(PairSeg{dst, ldp, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(cap, j - s0), NP - A});
@@ -1855,6 +1855,134 @@ gtb_status gtb_partition_get(const gtb_engine* e, int32_t* owner, double* out) {
     out[0] = (double)e->top_list.size();
     out[1] = (double)e->top_doubles;
   }
+  return GTB_OK;
+}
+// Host-only self-check of the launch schedule install_plan built (works on an engine without a device): every owned
+// clique is eliminated exactly once and solved exactly once per phase, every class member fits its class's kernel
+// and shared memory, the panel-step / Schur-step task lists hold what step_tasks() says, the inverse-block tasks and
+// the camera-pair segments tile their buffers.  out[0..7] = launch classes, panel-step launches, Schur-step launches,
+// back-substitution launches, inverse blocks, pair segments, same-camera segments, panel + Schur tasks.
+gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
+  if (!e) return GTB_ERR_INVALID;
+  if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
+  const Plan& p = e->plan;
+  int64_t cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  auto fail = [&](const std::string& m) { e->err = "schedule check: " + m; return GTB_ERR_INCONSISTENT; };
+  auto dim_of = [&](int32_t c) { return p.F[c] + p.S[c] + 1; };
+  std::vector<int32_t> seen_elim(p.n_cliques, 0), seen_bs(p.n_cliques, 0);
+  std::vector<uint8_t> rinv_used((size_t)e->rinv_blocks, 0);
+  int64_t pair_items_seen = 0, diag_items_seen = 0;
+  for (int ph = 0; ph < 2; ++ph) {
+    if ((int32_t)e->sched[ph].size() != p.n_levels) return fail("level count");
+    auto mine = [&](int32_t c) { return ph == 0 ? e->owner[c] == e->rank : e->owner[c] < 0; };
+    for (int32_t l = 0; l < p.n_levels; ++l) {
+      const LevelSched& L = e->sched[ph][l];
+      const int64_t ns = L.n_all - L.n_large, b = L.large_begin - ns;
+      int64_t expect = 0;
+      for (int64_t q = p.level_off[l]; q < p.level_off[l + 1]; ++q) expect += mine(p.level_cliques[q]) ? 1 : 0;
+      if (expect != L.n_all) return fail("level " + std::to_string(l) + ": clique count");
+      if (b < 0 || b + L.n_all > (int64_t)e->sched_lists.size()) return fail("level list range");
+      // launch classes tile the small part
+      int64_t q = b;
+      for (const LevelSched::Cls& cl : L.small) {
+        ++cnt[0];
+        if (cl.begin != q || cl.count <= 0) return fail("class ranges do not tile the level");
+        if (cl.smem > 227 * 1024) return fail("class shared memory above 227 KB");
+        for (int64_t k = cl.begin; k < cl.begin + cl.count; ++k) {
+          const int32_t c = e->sched_lists[k];
+          const int32_t d = dim_of(c);
+          const int64_t packed = (int64_t)d * (d + 1) / 2;
+          bool ok = false;
+          switch (cl.kind) {
+            case 3: ok = e->is_point[c] && p.S[c] / 9 <= cl.group_doubles && cl.group_doubles <= kPointMaxCams; break;
+            case 0: ok = !e->is_point[c] && is_thin_front(p.F[c], d) && d <= 48 && packed <= cl.group_doubles && cl.threads == kThinWarps * 32; break;
+            case 1: ok = !e->is_point[c] && is_thin_front(p.F[c], d) && packed <= cl.group_doubles && (cl.threads == 128 || cl.threads == 256 || cl.threads == 512); break;
+            case 2: ok = !e->is_point[c] && d <= kDenseMaxDim && (int64_t)(d | 1) * d * 8 <= cl.smem && cl.threads >= 32 && cl.threads <= 1024; break;
+            default: break;
+          }
+          if (!ok) return fail("clique " + std::to_string(c) + " does not fit its class (kind " + std::to_string(cl.kind) + ")");
+        }
+        q += cl.count;
+      }
+      if (q != b + ns) return fail("classes do not cover the small part of level " + std::to_string(l));
+      for (int64_t k = b; k < b + L.n_all; ++k) {
+        const int32_t c = e->sched_lists[k];
+        if (c < 0 || c >= p.n_cliques || p.level[c] != l || !mine(c)) return fail("foreign clique in a level list");
+        const bool large = k >= L.large_begin;
+        if (large && (e->is_point[c] || is_small_front(p.F[c], dim_of(c)))) return fail("small front in the large part");
+        if (!large && !e->is_point[c] && !is_small_front(p.F[c], dim_of(c))) return fail("large front in the small part");
+        seen_elim[c]++;
+      }
+      // panel-step and Schur-step task lists
+      if (L.n_large) {
+        const int max_np = (L.max_F + PW - 1) / PW;
+        if ((int)L.step_begin.size() != max_np + 1 || (int)L.schur_begin.size() != max_np + 1) return fail("step table size");
+        for (int sidx = 0; sidx <= max_np; ++sidx) {
+          int64_t want = 0, want_schur_min = 0;
+          for (int64_t k = L.large_begin; k < L.large_begin + L.n_large; ++k) {
+            const int32_t c = e->sched_lists[k];
+            const int np_c = (p.F[c] + PW - 1) / PW;
+            if (sidx < np_c) want += step_tasks(p.F[c], dim_of(c), sidx);
+            if (sidx == np_c) want_schur_min += step_tasks(p.F[c], dim_of(c), sidx);
+          }
+          if (want != L.step_count[sidx]) return fail("panel-step task count at level " + std::to_string(l));
+          if (L.schur_count[sidx] < want_schur_min || (want_schur_min == 0) != (L.schur_count[sidx] == 0)) return fail("Schur-step task count");
+          cnt[1] += L.step_count[sidx] > 0;
+          cnt[2] += L.schur_count[sidx] > 0;
+          cnt[7] += L.step_count[sidx] + L.schur_count[sidx];
+          for (int64_t t = L.schur_begin[sidx]; t < L.schur_begin[sidx] + L.schur_count[sidx]; ++t) {
+            const StepTask& st = e->step_tasks_list[t];
+            const int tile = st.task & ((1 << kSchurTileBits) - 1), slice = (st.task >> kSchurTileBits) & ((1 << kSchurSliceBits) - 1);
+            const int nsplit = st.task >> (kSchurTileBits + kSchurSliceBits);
+            if (nsplit < 1 || slice >= nsplit || tile >= step_tasks(p.F[st.clique], dim_of(st.clique), sidx)) return fail("Schur-step task encoding");
+          }
+        }
+      }
+      // back-substitution list: the same cliques, warp class first
+      for (int64_t k = L.bs_begin; k < L.bs_begin + L.n_bs_warp + L.n_bs_cta; ++k) {
+        if (k >= (int64_t)e->bs_list.size()) return fail("back-substitution list range");
+        const int32_t c = e->bs_list[k];
+        if (p.level[c] != l || !mine(c)) return fail("foreign clique in a back-substitution list");
+        const bool warp_class = (p.F[c] <= 32 && dim_of(c) <= kDenseMaxDim) || e->is_point[c];
+        if (warp_class != (k < L.bs_begin + L.n_bs_warp)) return fail("back-substitution class of clique " + std::to_string(c));
+        if (warp_class && !e->is_point[c] && p.S[c] > 160) return fail("warp-class conditional wider than its shared memory");
+        if (!warp_class) {
+          if ((int64_t)(p.F[c] + p.S[c] + kBsCtaThreads + 64 + 2 * 32 * 33) * 8 > L.bs_cta_smem || L.bs_cta_smem > 200 * 1024) return fail("back-substitution shared memory");
+          const int nb = (p.F[c] + 31) / 32;
+          for (int bi = 0; bi < nb; ++bi) {
+            const int64_t dst = (int64_t)e->bs_rinv_off[k] + bi;
+            if (dst < e->rinv_task_begin[ph] || dst >= e->rinv_task_begin[ph] + e->rinv_task_count[ph] || dst >= e->rinv_blocks) return fail("inverse-block range");
+            if (e->rinv_tasks[3 * dst] != c || e->rinv_tasks[3 * dst + 1] != bi || e->rinv_tasks[3 * dst + 2] != dst) return fail("inverse-block task");
+            if (rinv_used[(size_t)dst]++) return fail("inverse block used twice");
+          }
+        }
+        seen_bs[c]++;
+      }
+      if (L.n_bs_warp + L.n_bs_cta != L.n_all) return fail("back-substitution count at level " + std::to_string(l));
+      cnt[3] += (L.n_bs_warp > 0) + (L.n_bs_cta > 0) * (1 + (L.bs_max_S > 0));
+      // camera-pair segments of the level's point cliques
+      for (int pass = 0; pass < 2; ++pass) {
+        const int64_t sb = pass ? L.diag_seg_begin : L.pair_seg_begin, sn = pass ? L.n_diag_seg : L.n_pair_seg;
+        const int64_t nitems = pass ? (int64_t)e->diag_items.size() / 3 : (int64_t)e->pair_items.size();
+        if (sn && sb + sn > (int64_t)e->pair_segs.size()) return fail("segment range");
+        for (int64_t k = sb; k < sb + sn; ++k) {
+          const PairSeg& sg = e->pair_segs[k];
+          if (sg.count < 1 || sg.begin < 0 || (int64_t)sg.begin + sg.count > nitems || sg.ld < 4 || sg.dst < 0) return fail("segment contents");
+          (pass ? diag_items_seen : pair_items_seen) += sg.count;
+        }
+        cnt[pass ? 6 : 5] += sn;
+      }
+    }
+  }
+  for (int32_t c = 0; c < p.n_cliques; ++c) {
+    const int want = (e->owner[c] == e->rank || e->owner[c] < 0) ? 1 : 0;
+    if (seen_elim[c] != want || seen_bs[c] != want) return fail("clique " + std::to_string(c) + " scheduled " + std::to_string(seen_elim[c]) + " / " + std::to_string(seen_bs[c]) + " times");
+  }
+  for (size_t k = 0; k < rinv_used.size(); ++k)
+    if (!rinv_used[k]) return fail("unused inverse block");
+  if (e->point_pairs && (pair_items_seen != (int64_t)e->pair_items.size() || diag_items_seen != (int64_t)e->diag_items.size() / 3)) return fail("segments do not cover the item lists");
+  cnt[4] = e->rinv_blocks;
+  if (out8) std::memcpy(out8, cnt, sizeof(cnt));
   return GTB_OK;
 }
 gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {

@@ -123,6 +123,14 @@ class Engine:
         return dict(owner=owner, n_top=int(st[0]), reduced_doubles=int(st[1]), top_share=float(st[2]),
                     rank_share=st[3:].copy())
 
+    def schedule_check(self):
+        """Host-only invariants of the launch schedule (gtb_schedule_check); raises on a violation."""
+        out = np.zeros(8, dtype=np.int64)
+        self._ck(self.lib.gtb_schedule_check(self.h, _ptr(out)))
+        names = ["launch_classes", "panel_step_launches", "schur_step_launches", "backsolve_launches", "inverse_blocks",
+                 "pair_segments", "diag_segments", "step_tasks"]
+        return dict(zip(names, out.tolist()))
+
     def plan(self):
         nc, nk, ncond, ns = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
         self._ck(self.lib.gtb_plan_sizes(self.h, C.byref(nc), C.byref(nk), C.byref(ncond), C.byref(ns)))

@@ -259,6 +259,14 @@ gtb_status gtb_set_distributed(gtb_engine* e, int32_t rank, int32_t world, gtb_c
  * stats: out[0] = number of top cliques, out[1] = doubles reduced per factorisation, out[2] = cost share of the top
  * (model), out[3 + r] for r < world (at most 13) = cost share of rank r's subtrees.                            */
 gtb_status gtb_partition_get(const gtb_engine* e, int32_t* owner, double* out16);
+/* Host-only self-check of the static launch schedule that replaces the reference's task-parallel tree walk
+ * (inference/ClusterTree-inst.h:286-318, base/treeTraversal-inst.h:156-168): every clique this rank owns is eliminated
+ * exactly once and solved exactly once, every member of a launch class fits the class's kernel and shared memory, the
+ * panel-step / Schur-step task lists, the inverse-block tasks and the camera-pair segments tile their buffers.  Works
+ * on an engine without a device.  GTB_ERR_INCONSISTENT + gtb_last_error on a violated invariant.  out8 (may be NULL):
+ * launch classes, panel-step launches, Schur-step launches, back-substitution launches, inverse blocks, camera-pair
+ * segments, same-camera segments, panel + Schur tasks.                                                            */
+gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8);
 
 /* ---- instrumentation ------------------------------------------------------------------------------- */
 /* Number of engine kernels launched since creation.                                                      */
