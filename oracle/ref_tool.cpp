@@ -14,6 +14,10 @@
 //     lambda=<double> diag=0|1                    (solve: LM damping, 0 => none)
 //     ceres=0|1 maxiter=<n> lambda0=<d>           (lm)
 //     iters=<n>                                   (time)
+//   ref_tool <city10000 file> <out.gtb> mode=isam2 loops=<n> every=<k>
+//     the reference's ISAM2 over a City10000-format file with the update schedule and parameters of
+//     examples/ISAM2_City10000.cpp:62-134 (first hypothesis of every line): estimate after every k-th update,
+//     seconds per update (the oracle and CPU baseline of the ISAM2 row)
 #include <gtsam/geometry/Cal3Bundler.h>
 #include <gtsam/geometry/PinholeCamera.h>
 #include <gtsam/geometry/Point3.h>
@@ -27,6 +31,7 @@
 #include <gtsam/linear/NoiseModel.h>
 #include <gtsam/linear/VectorValues.h>
 #include <gtsam/nonlinear/GaussNewtonOptimizer.h>
+#include <gtsam/nonlinear/ISAM2.h>
 #include <gtsam/nonlinear/LevenbergMarquardtOptimizer.h>
 #include <gtsam/nonlinear/Marginals.h>
 #include <gtsam/nonlinear/NonlinearFactorGraph.h>
@@ -323,6 +328,89 @@ static GaussianFactorGraph damp(const GaussianFactorGraph& gfg, const Values& va
   return st.buildDampedSystem(gfg, sq);
 }
 
+// mode=isam2: argv[1] is a City10000-format file: "EDGE2 <from> <n> <to> <n> <hypotheses> {x y theta}...".  Schedule and
+// parameters follow examples/ISAM2_City10000.cpp:62-134 (no ambiguity: the first hypothesis of every line): prior
+// 1e-4 on pose 0 and one update; then one update per line -- an odometry line (to = from + 1) adds the new pose,
+// initialised by composing the current estimate of `from` with the measurement, and a BetweenFactor with sigmas
+// (1/30, 1/30, 1/100); any other line is a loop closure with sigmas 10, and only those count towards `loops`.
+// Gauss-Newton ISAM2 with wildfire threshold 0, relinearizeThreshold 0.01, relinearizeSkip 1.
+static int isam2_mode(const std::string& data, const std::string& outpath) {
+  const size_t max_loops = (size_t)std::stoll(opt("loops", "1000000000"));
+  const size_t every = (size_t)std::max<long long>(1, std::stoll(opt("every", "100")));
+  std::ifstream in(data);
+  if (!in) { std::cerr << "cannot open " << data << "\n"; return 2; }
+  ISAM2Params params;
+  params.optimizationParams = ISAM2GaussNewtonParams(0.0);
+  params.relinearizeThreshold = 0.01;
+  params.relinearizeSkip = 1;
+  ISAM2 isam(params);
+  const auto prior_model = noiseModel::Diagonal::Sigmas(Vector3(1e-4, 1e-4, 1e-4));
+  const auto odo_model = noiseModel::Diagonal::Sigmas(Vector3(1.0 / 30.0, 1.0 / 30.0, 1.0 / 100.0));
+  const auto loop_model = noiseModel::Diagonal::Sigmas(Vector3(10.0, 10.0, 10.0));
+  NonlinearFactorGraph fresh;
+  Values fresh_values;
+  fresh_values.insert(Symbol('x', 0), Pose2(0, 0, 0));
+  fresh.addPrior<Pose2>(Symbol('x', 0), Pose2(0, 0, 0), prior_model);
+  isam.update(fresh, fresh_values);
+  Values est = isam.calculateBestEstimate();
+  std::vector<double> snap, secs;          // estimates (x, y, theta per pose, poses 0..n-1) at the snapshot updates
+  std::vector<int64_t> snap_update, snap_nposes, snap_off, line_kind;
+  size_t loops = 0, updates = 0, nposes = 1;
+  std::string line;
+  while (loops < max_loops && std::getline(in, line)) {
+    std::istringstream ls(line);
+    std::string tag;
+    long long from, to, d0, d1, nh;
+    if (!(ls >> tag >> from >> d0 >> to >> d1 >> nh) || nh < 1) continue;
+    double x, y, th;
+    ls >> x >> y >> th;
+    const Pose2 z(x, y, th);
+    fresh.resize(0);
+    fresh_values.clear();
+    const bool odometry = from == to - 1;
+    if (odometry) {
+      fresh_values.insert(Symbol('x', to), est.at<Pose2>(Symbol('x', from)) * z);
+      fresh.emplace_shared<BetweenFactor<Pose2>>(Symbol('x', from), Symbol('x', to), z, odo_model);
+      nposes = std::max(nposes, (size_t)to + 1);
+    } else {
+      fresh.emplace_shared<BetweenFactor<Pose2>>(Symbol('x', from), Symbol('x', to), z, loop_model);
+      ++loops;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    isam.update(fresh, fresh_values);
+    est = isam.calculateBestEstimate();
+    secs.push_back(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    line_kind.push_back(odometry ? 0 : 1);
+    ++updates;
+    if (updates % every == 0) {
+      snap_update.push_back((int64_t)updates);
+      snap_nposes.push_back((int64_t)nposes);
+      snap_off.push_back((int64_t)snap.size());
+      for (size_t i = 0; i < nposes; ++i) {
+        const Pose2 q = est.at<Pose2>(Symbol('x', i));
+        snap.push_back(q.x()); snap.push_back(q.y()); snap.push_back(q.theta());
+      }
+    }
+  }
+  gtbio::File out;
+  std::vector<double> fin;
+  for (size_t i = 0; i < nposes; ++i) {
+    const Pose2 q = est.at<Pose2>(Symbol('x', i));
+    fin.push_back(q.x()); fin.push_back(q.y()); fin.push_back(q.theta());
+  }
+  out.put_f64("final", fin, {(uint64_t)nposes, 3});
+  out.put_f64("snapshots", snap);
+  out.put_i64("snapshot_update", snap_update);
+  out.put_i64("snapshot_nposes", snap_nposes);
+  out.put_i64("snapshot_offset", snap_off);
+  out.put_f64("update_seconds", secs);
+  out.put_i64("update_is_loop", line_kind);
+  out.put_i64("counts", {(int64_t)updates, (int64_t)loops, (int64_t)nposes, (int64_t)isam.getFactorsUnsafe().size()});
+  out.put_f64("final_error", {isam.getFactorsUnsafe().error(est)});
+  out.save(outpath);
+  return 0;
+}
+
 // mode=readg2o is3d=0|1 kernel=none|huber|tukey / mode=readbal: argv[1] is the DATA file; the reference's own readers
 // (readG2o, SfmData::FromBalFile + the graph of tests/testGeneralSFMFactorB.cpp:44-58) build graph and values, which
 // are dumped in the problem schema (+ *_info = R^T R of every Gaussian model, pose2_cs = (cos, sin)).
@@ -424,6 +512,7 @@ int main(int argc, char** argv) {
   }
   try {
     if (opt("mode", "solve").rfind("read", 0) == 0 || opt("mode", "solve") == "writeg2o") return dataset_mode(argv[1], argv[2]);
+    if (opt("mode", "solve") == "isam2") return isam2_mode(argv[1], argv[2]);
     gtbio::File P, out;
     P.load(argv[1]);
     Built B = build(P);
