@@ -5,10 +5,11 @@ mode=isam2: gtsam::ISAM2 with the parameters and the update schedule of examples
                                                    examples/Data/T1_city10000_04.txt, so the input travels
   tests/golden/isam2__city10000_200loops.npz       estimate after every 100th update and at the end, counts, error
 
-With --full it also runs the whole file (10,000 poses, 10,686 loop closures; 15-25 minutes on one core) and stores how far
-the result is from the reference's own fixture examples/Data/ISAM2_GT_city10000.txt (the output of that example, written
-with 6 significant digits) plus the per-update latency: the CPU baseline of the row.
-usage: python tests/golden/make_isam2_golden.py [--full]"""
+With --full it also runs the whole file (10,000 poses, 10,688 loop closures; 30 minutes on one core here) and stores how
+far the result is from the ground-truth trajectory the reference ships for this experiment
+(examples/Data/ISAM2_GT_city10000.txt: the noise-free city grid, not an ISAM2 output -- so a sanity bound, not a parity
+pin), a stride-50 sample of the estimate, and the seconds of every update: the CPU baseline of the row.
+usage: python tests/golden/make_isam2_golden.py [--full | --full-from <dump.gtb>]"""
 import os
 import subprocess
 import sys
@@ -40,15 +41,15 @@ def main():
                               "final_error", "update_is_loop")}
     keep["mean_update_seconds_here"] = np.array([d["update_seconds"].mean()])
     path = os.path.join(HERE, "isam2__city10000_200loops.npz")
-    if "--full" in sys.argv:
-        f = run(FULL, every=1000)
+    if "--full" in sys.argv or "--full-from" in sys.argv:
+        # --full-from <out.gtb>: reuse the dump of an earlier whole-file run (30 minutes on one core here)
+        f = gtbio.load(sys.argv[sys.argv.index("--full-from") + 1]) if "--full-from" in sys.argv else run(FULL, every=1000)
         gt = np.loadtxt(GT)
         est = f["final"]
-        dth = np.angle(np.exp(1j * (est[:, 2] - gt[:, 2])))
+        dist = np.linalg.norm(est[:, :2] - gt[:, :2], axis=1)
         keep["full_counts"] = f["counts"]
         keep["full_final_error"] = f["final_error"]
-        keep["full_max_abs_xy_vs_reference_fixture"] = np.array([np.abs(est[:, :2] - gt[:, :2]).max()])
-        keep["full_max_abs_theta_vs_reference_fixture"] = np.array([np.abs(dth).max()])
+        keep["full_xy_distance_to_ground_truth_mean_max"] = np.array([dist.mean(), dist.max()])
         keep["full_update_seconds"] = f["update_seconds"].astype(np.float32)
         keep["full_final_stride50"] = est[::50].copy()
     elif os.path.exists(path):

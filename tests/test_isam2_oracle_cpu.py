@@ -1,8 +1,9 @@
 """The oracle of the ISAM2 row (not built on the device yet): the reference's own
 gtsam::ISAM2 driven by oracle/_ref/ref_tool mode=isam2 with the schedule of examples/ISAM2_City10000.cpp:62-134.
 Checked here: the committed fixture against a fresh run of the reference (when it is built in this container),
-its bookkeeping against an independent reading of the input file, and -- when the generator was run with --full --
-the whole-file result against the reference's own fixture examples/Data/ISAM2_GT_city10000.txt."""
+its bookkeeping against an independent reading of the input file, the reported error against a numpy restatement, and
+-- when the generator was run with --full -- the whole-file result against the ground-truth trajectory the reference
+ships (examples/Data/ISAM2_GT_city10000.txt)."""
 import os
 import subprocess
 
@@ -94,12 +95,16 @@ def test_reference_reproduces_the_fixture(tmp_path):
         assert np.allclose(d[k], g[k], rtol=0, atol=1e-12), k       # serial reference: deterministic
 
 
-def test_whole_file_run_matches_the_reference_fixture():
-    """examples/Data/ISAM2_GT_city10000.txt is the reference's own output of this experiment (6 significant digits)."""
+def test_whole_file_run_stays_on_the_ground_truth():
+    """examples/Data/ISAM2_GT_city10000.txt is the ground-truth trajectory the reference ships for this experiment (the
+    noise-free grid, not an ISAM2 output): after all 20,687 updates the reference's estimate is within a cell of it
+    everywhere, where dead reckoning over the same odometry ends up 33 m off on average."""
     g = dict(np.load(GOLD))
     if "full_counts" not in g:
         pytest.skip("generator was not run with --full")
     updates, loops, nposes, nfactors = g["full_counts"].tolist()
-    assert nposes == 10000 and updates == 20686 and nfactors == updates + 1
-    assert float(g["full_max_abs_xy_vs_reference_fixture"][0]) < 1e-3
-    assert float(g["full_max_abs_theta_vs_reference_fixture"][0]) < 1e-4
+    assert nposes == 10000 and updates == 20687 and loops == 10688 and nfactors == updates + 1
+    mean, worst = g["full_xy_distance_to_ground_truth_mean_max"].tolist()
+    assert mean < 1.0 and worst < 3.0
+    us = g["full_update_seconds"]
+    assert us.size == updates and (us > 0).all()
