@@ -167,6 +167,7 @@ void load_2d(const char* path, gtb_dataset* d) {
   std::vector<std::string> lines;
   read_lines(path, lines);
   std::map<uint64_t, std::vector<double>> poses;   // (x, y, theta)
+  std::map<uint64_t, std::pair<double, double>> chain_cs;   // (cos, sin) of the poses created by chaining odometry
   std::string tag;
   const char* rest;
   // first pass: vertices (slam/dataset.cpp:511-523)
@@ -200,14 +201,21 @@ void load_2d(const char* path, gtb_dataset* d) {
     d->fnk[GTB_BETWEEN2].push_back(GTB_NOISE_INFORMATION);
     d->fnoise[GTB_BETWEEN2].insert(d->fnoise[GTB_BETWEEN2].end(), M, M + 9);
     // pure odometry file: chain the measurement (Pose2::operator*, geometry/Pose2.h:138, Rot2::operator*, Rot2.h:120)
-    if (!poses.count(id1)) poses[id1] = {0.0, 0.0, 0.0};
+    // The reference keeps a rotation as (cos, sin) (geometry/Rot2.h:44), so a chained pose carries the PRODUCT of the
+    // cosines and sines along its chain, not cos / sin of the accumulated angle: kept here next to the pose so that x and
+    // y come out bit-identical along a 20,000-pose chain; theta = atan2(s, c) (Rot2::theta, Rot2.h:190) is what is stored.
+    if (!poses.count(id1)) { poses[id1] = {0.0, 0.0, 0.0}; chain_cs[id1] = {1.0, 0.0}; }
     if (!poses.count(id2)) {
       const std::vector<double>& a = poses[id1];
-      const double c1 = std::cos(a[2]), s1 = std::sin(a[2]), c2 = std::cos(yaw), s2 = std::sin(yaw);
+      const auto it = chain_cs.find(id1);
+      const double c1 = it != chain_cs.end() ? it->second.first : std::cos(a[2]);
+      const double s1 = it != chain_cs.end() ? it->second.second : std::sin(a[2]);
+      const double c2 = std::cos(yaw), s2 = std::sin(yaw);
       double c = c1 * c2 - s1 * s2, s = s1 * c2 + c1 * s2;
-      const double n2 = c * c + s * s;   // Rot2::fromCosSin normalises
-      if (std::abs(n2 - 1.0) > 1e-12) { const double n = 1.0 / std::sqrt(n2); c *= n; s *= n; }
-      poses[id2] = {a[0] + (c1 * x - s1 * y), a[1] + (s1 * x + c1 * y), std::atan2(s, c)};
+      double n2 = c * c + s * s;   // Rot2::fromCosSin -> normalize (geometry/Rot2.cpp:56-64)
+      if (std::abs(n2 - 1.0) > 1e-10) { n2 = 1 / std::sqrt(n2); c *= n2; s *= n2; }
+      poses[id2] = {a[0] + (c1 * x + -s1 * y), a[1] + (s1 * x + c1 * y), std::atan2(s, c)};
+      chain_cs[id2] = {c, s};
     }
   }
   from_map(poses, d->vkeys[GTB_POSE2], d->vstate[GTB_POSE2]);

@@ -25,13 +25,23 @@ def _read(name, kind):
 
 @pytest.mark.parametrize("name,kind", CASES)
 def test_reader_matches_the_reference(name, kind):
-    g = load_golden(_tag(name))
-    p = _read(name, kind)
+    compare_with_reference(_read(name, kind), load_golden(_tag(name)), kind)
+
+
+def compare_with_reference(p, g, kind, chained=False):
+    """p: problem from the native reader; g: arrays dumped by the reference's reader (ref_* keys).  chained: the file
+    has no vertices and the poses were created by chaining odometry: the reference then holds products of cosines and
+    sines (Rot2 keeps (c, s)), the flat tables hold theta = atan2(s, c), so cos(theta) is c up to a rounding."""
     if kind == "g2o2":
         assert np.array_equal(p.a["pose2_keys"], g["ref_pose2_keys"])
         assert np.array_equal(p.a["pose2"][:, :2], g["ref_pose2"][:, :2])
         cs = np.stack([np.cos(p.a["pose2"][:, 2]), np.sin(p.a["pose2"][:, 2])], axis=1)   # what the device keeps
-        assert np.array_equal(cs, g["ref_pose2_cs"])
+        if chained:
+            # the reference renormalises a product only when its norm is off by more than 1e-10 (Rot2.cpp:56-64)
+            np.testing.assert_allclose(cs, g["ref_pose2_cs"], rtol=0, atol=1e-10)
+            assert np.array_equal(p.a["pose2"][:, 2], g["ref_pose2"][:, 2])               # Rot2::theta() of the product
+        else:
+            assert np.array_equal(cs, g["ref_pose2_cs"])
         assert np.array_equal(p.a["between2_keys"], g["ref_between2_keys"])
         assert np.array_equal(p.a["between2_z"][:, :2], g["ref_between2_z"][:, :2])
         zcs = np.stack([np.cos(p.a["between2_z"][:, 2]), np.sin(p.a["between2_z"][:, 2])], axis=1)
@@ -39,8 +49,11 @@ def test_reader_matches_the_reference(name, kind):
         assert np.all(p.a["between2_nk"] == 3)
         np.testing.assert_allclose(p.a["between2_noise"], g["ref_between2_info"], rtol=1e-12, atol=1e-12)
     elif kind == "g2o3":
-        assert np.array_equal(p.a["pose3_keys"], g["ref_pose3_keys"])
-        assert np.array_equal(p.a["pose3"], g["ref_pose3"])            # Eigen's quaternion -> matrix, same operation order
+        if "ref_pose3_keys" in g and len(g["ref_pose3_keys"]):
+            assert np.array_equal(p.a["pose3_keys"], g["ref_pose3_keys"])
+            assert np.array_equal(p.a["pose3"], g["ref_pose3"])        # Eigen's quaternion -> matrix, same operation order
+        else:                                                          # edges only: load3D creates no values
+            assert "pose3_keys" not in p.a or len(p.a["pose3_keys"]) == 0
         assert np.array_equal(p.a["between3_keys"], g["ref_between3_keys"])
         assert np.array_equal(p.a["between3_z"], g["ref_between3_z"])
         scale = np.abs(g["ref_between3_info"]).max()
