@@ -44,6 +44,10 @@ struct gtb_dataset {
   double loss_k = 0.0;
 };
 
+// the reference holds a 2-D rotation as (cos, sin) and prints Rot2::theta() = atan2(sin, cos) (geometry/Rot2.h:190-192):
+// an angle read as 4.71 is written back as -1.57
+static inline double wrap_theta(double th) { return std::atan2(std::sin(th), std::cos(th)); }
+
 namespace {
 
 thread_local std::string g_err;
@@ -469,7 +473,7 @@ gtb_status gtb_write_g2o(const char* path, int64_t n_pose2, const uint64_t* pose
   if (!os) { g_err = std::string("can not open ") + path; return GTB_ERR_INVALID; }
   auto index = [](uint64_t key) { return key & 0x00ffffffffffffffull; };   // Symbol(key).index()
   for (int64_t i = 0; i < n_pose2; ++i)
-    os << "VERTEX_SE2 " << index(pose2_keys[i]) << " " << pose2[3 * i] << " " << pose2[3 * i + 1] << " " << pose2[3 * i + 2] << std::endl;
+    os << "VERTEX_SE2 " << index(pose2_keys[i]) << " " << pose2[3 * i] << " " << pose2[3 * i + 1] << " " << wrap_theta(pose2[3 * i + 2]) << std::endl;
   for (int64_t i = 0; i < n_pose3; ++i) {
     const double* s = pose3 + 12 * i;
     double q[4];
@@ -480,7 +484,7 @@ gtb_status gtb_write_g2o(const char* path, int64_t n_pose2, const uint64_t* pose
   for (int64_t i = 0; i < n_between2; ++i) {
     const double* z = between2_z + 3 * i;
     const double* I = between2_information + 9 * i;
-    os << "EDGE_SE2 " << index(between2_keys[2 * i]) << " " << index(between2_keys[2 * i + 1]) << " " << z[0] << " " << z[1] << " " << z[2];
+    os << "EDGE_SE2 " << index(between2_keys[2 * i]) << " " << index(between2_keys[2 * i + 1]) << " " << z[0] << " " << z[1] << " " << wrap_theta(z[2]);
     for (int r = 0; r < 3; ++r)
       for (int c = r; c < 3; ++c) os << " " << I[r * 3 + c];
     os << std::endl;

@@ -51,3 +51,23 @@ def test_covariance_free_toro_file_is_rejected(tmp_path):
     assert g["between3_keys"].shape[0] == 1 and not g["between3_info"].any()
     with pytest.raises(datasets.DatasetError):
         datasets.read_g2o(path, True)
+
+
+WRITE = [(n, k) for n, k in FILES if k != "bal" and n not in ("w20000.txt", "sphere2500.txt", "sphere2500_groundtruth.txt")]
+
+
+@pytest.mark.parametrize("name,kind", WRITE + [("w20000.txt", "g2o2")])
+def test_writer_matches_the_reference_on_its_own_data(name, kind, tmp_path):
+    """gtb_write_g2o against the reference's writeG2o (slam/dataset.cpp:636-760), record for record; both print 6
+    significant digits."""
+    sys.path.insert(0, ROOT)
+    from gtsam_petercdev_b200 import datasets
+    from test_ingest_cpu import _tokens
+    path = os.path.join(DATA, name)
+    ref_out, my_out = str(tmp_path / "ref.g2o"), str(tmp_path / "mine.g2o")
+    subprocess.run([TOOL, path, ref_out, "mode=writeg2o", "is3d=%d" % (kind == "g2o3")], check=True, timeout=600)
+    datasets.write_g2o(my_out, datasets.read_g2o(path, kind == "g2o3"))
+    mine, ref = _tokens(open(my_out).read()), _tokens(open(ref_out).read())
+    assert [t for t, _ in mine] == [t for t, _ in ref]
+    for (_, a), (_, b) in zip(mine, ref):
+        np.testing.assert_allclose(a, b, rtol=2e-5, atol=2e-6)
