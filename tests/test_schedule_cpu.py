@@ -64,3 +64,24 @@ def test_schedule_check_needs_a_plan():
     e = Engine(golden_problem("pose2_300"), device=-1)
     with pytest.raises(EngineError):
         e.schedule_check()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_schedule_invariants_at_full_size(world):
+    """C3 (Ladybug-scale, the reference's METIS ordering): every rank's schedule of a `world`-GPU cut, and the ranks'
+    subtree cliques together with the shared top cover the tree exactly once."""
+    import bench
+    p = bench.make_problem("c3")
+    keys = bench.ordering_for(p, "c3", "metis")
+    covered = None
+    for rank in range(world):
+        e = Engine(p, device=-1)
+        e.set_distributed(rank, world)
+        e.set_ordering(keys)
+        st = e.schedule_check()
+        assert st["panel_step_launches"] > 0 and st["diag_segments"] > 0
+        owner = e.partition()["owner"]
+        mine = (owner == rank).astype(np.int64)
+        covered = mine if covered is None else covered + mine
+    covered += (owner == -1)
+    assert covered.min() == 1 and covered.max() == 1
