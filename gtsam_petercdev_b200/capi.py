@@ -86,6 +86,9 @@ _SIGS = {
     "gtb_dataset_factor_noise": (_P, [_P, C.c_int]),
     "gtb_dataset_robust": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "gtb_dataset_apply": (C.c_int, [_P, _P]),
+    "gtb_noalloc_setup": (C.c_int, [C.c_int]),
+    "gtb_bucket_error_noalloc": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gtb_noalloc_last_error": (C.c_char_p, []),
     "gtb_write_g2o": (C.c_int, [C.c_char_p, C.c_int64, _P, _P, C.c_int64, _P, _P, C.c_int64, _P, _P, _P, C.c_int64, _P, _P, _P]),
 }
 

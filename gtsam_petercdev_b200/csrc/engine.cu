@@ -2296,3 +2296,138 @@ void gtb_debug_read(gtb_engine* e, long long* out8) {
 void* gtb_stream(gtb_engine* e) { return e ? (void*)e->stream : nullptr; }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// Allocation-free entry point (include/gtsam_b200.h: gtb_bucket_error_noalloc).  No counterpart in the reference:
+// added for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  It is a variant of error_kernel<B> + sum_partials_kernel (nonlinear_error above)
+// whose per-CTA partial sums live in a file-scope __device__ array instead of the engine's cudaMalloc'ed d_partials.
+//
+// The array's NAME is only a host-side stand-in in host code, not a device address: its address is taken once per device,
+// with that device current, through cudaGetSymbolAddress, and that pointer is what the kernels get.  Every GPU that
+// loads the library holds the array (256 KB) until exit.  All calls share it and it keeps the last call's contents:
+// nothing in it has to start at zero (every partial that the final sum reads is written by this call's first kernel), but
+// two calls that overlap on the GPU (different streams, no dependency) race on it.
+// ------------------------------------------------------------------------------------------------------
+namespace gtb {
+
+constexpr int64_t kNoAllocMaxFactors = GTB_NOALLOC_MAX_FACTORS;
+constexpr int kNoAllocPartials = (int)((kNoAllocMaxFactors + kFactorThreads - 1) / kFactorThreads);   // 32,768 doubles = 256 KB
+static __device__ __align__(256) double g_noalloc_partials[kNoAllocPartials];
+
+constexpr int kNoAllocMaxDevices = 64;
+static double* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};   // device address of the array, per device ordinal
+static thread_local std::string g_noalloc_err;
+
+// Restores the caller's current device on scope exit.
+struct DeviceRestore {
+  int prev = -1;
+  bool switched = false;
+  cudaError_t enter(int device) {
+    cudaError_t st = cudaGetDevice(&prev);
+    if (st != cudaSuccess) return st;
+    if (prev != device) {
+      st = cudaSetDevice(device);
+      switched = st == cudaSuccess;
+    }
+    return st;
+  }
+  ~DeviceRestore() { if (switched) cudaSetDevice(prev); }
+};
+
+// Set-up, once per device, with that device current: the device address of the scratch array.
+static gtb_status noalloc_setup(int device, double** out) {
+  if (device < 0 || device >= kNoAllocMaxDevices) {
+    g_noalloc_err = "device ordinal out of range";
+    return GTB_ERR_INVALID;
+  }
+  if (!g_noalloc_ptr[device]) {
+    double* p = nullptr;
+    const cudaError_t st = cudaGetSymbolAddress((void**)&p, g_noalloc_partials);
+    if (st != cudaSuccess || !p) {
+      g_noalloc_err = std::string("cudaGetSymbolAddress(g_noalloc_partials): ") + cudaGetErrorString(st);
+      return st == cudaErrorNoDevice || st == cudaErrorInsufficientDriver ? GTB_ERR_NO_DEVICE : GTB_ERR_CUDA;
+    }
+    g_noalloc_ptr[device] = p;
+  }
+  if (out) *out = g_noalloc_ptr[device];
+  return GTB_OK;
+}
+
+template <int B>
+static cudaError_t noalloc_launch(const BucketDev& bk, const double* s0, const double* s1, double* partials, double* out,
+                                  cudaStream_t st) {
+  const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
+  error_kernel<B><<<grid, kFactorThreads, 0, st>>>(bk, s0, s1, partials);
+  sum_partials_kernel<<<1, 256, 0, st>>>(partials, grid, out);
+  return cudaGetLastError();
+}
+
+}  // namespace gtb
+
+extern "C" {
+
+const char* gtb_noalloc_last_error(void) { return g_noalloc_err.c_str(); }
+
+gtb_status gtb_noalloc_setup(int device) {
+  DeviceRestore guard;
+  if (guard.enter(device) != cudaSuccess) {
+    g_noalloc_err = "cannot make the device current";
+    return GTB_ERR_NO_DEVICE;
+  }
+  return noalloc_setup(device, nullptr);
+}
+
+gtb_status gtb_bucket_error_noalloc(int device, int bucket, int64_t n, const double* state0, const double* state1,
+                                    const int32_t* row0, const int32_t* row1, const double* z, const int8_t* noise_kind,
+                                    const double* noise, double* error_out, void* stream) {
+  if (bucket < 0 || bucket >= GTB_NUM_BUCKETS) { g_noalloc_err = "bad factor bucket"; return GTB_ERR_INVALID; }
+  if (n < 0) { g_noalloc_err = "negative factor count"; return GTB_ERR_INVALID; }
+  if (n > kNoAllocMaxFactors) {
+    char buf[160];
+    snprintf(buf, sizeof buf, "gtb_bucket_error_noalloc: %lld factors exceed the fixed scratch (GTB_NOALLOC_MAX_FACTORS = %lld)",
+             (long long)n, (long long)kNoAllocMaxFactors);
+    g_noalloc_err = buf;
+    return GTB_ERR_INVALID;
+  }
+  if (!error_out || (n > 0 && (!state0 || !row0 || !z)) || (n > 0 && kNKeys[bucket] == 2 && (!state1 || !row1)) ||
+      ((noise_kind == nullptr) != (noise == nullptr))) {
+    g_noalloc_err = "null argument";
+    return GTB_ERR_INVALID;
+  }
+  DeviceRestore guard;
+  if (guard.enter(device) != cudaSuccess) {
+    g_noalloc_err = "cannot make the device current";
+    return GTB_ERR_NO_DEVICE;
+  }
+  double* partials = nullptr;
+  const gtb_status su = noalloc_setup(device, &partials);
+  if (su != GTB_OK) return su;
+  cudaStream_t st = (cudaStream_t)stream;
+  BucketDev bk;
+  std::memset(&bk, 0, sizeof bk);
+  bk.n = (int32_t)n;
+  bk.any_noise = noise_kind ? 1 : 0;
+  bk.row0 = row0; bk.row1 = row1; bk.z = z; bk.nk = noise_kind; bk.noise = noise;
+  cudaError_t err = cudaSuccess;
+  if (n == 0) {
+    err = cudaMemsetAsync(error_out, 0, sizeof(double), st);
+  } else {
+    switch (bucket) {
+      case 0: err = noalloc_launch<0>(bk, state0, state1, partials, error_out, st); break;
+      case 1: err = noalloc_launch<1>(bk, state0, state1, partials, error_out, st); break;
+      case 2: err = noalloc_launch<2>(bk, state0, state1, partials, error_out, st); break;
+      case 3: err = noalloc_launch<3>(bk, state0, state1, partials, error_out, st); break;
+      case 4: err = noalloc_launch<4>(bk, state0, state1, partials, error_out, st); break;
+      case 5: err = noalloc_launch<5>(bk, state0, state1, partials, error_out, st); break;
+      default: err = noalloc_launch<6>(bk, state0, state1, partials, error_out, st); break;
+    }
+  }
+  if (err != cudaSuccess) {
+    g_noalloc_err = std::string("gtb_bucket_error_noalloc launch: ") + cudaGetErrorString(err);
+    return GTB_ERR_CUDA;
+  }
+  return GTB_OK;
+}
+
+}  // extern "C"

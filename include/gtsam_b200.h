@@ -268,6 +268,35 @@ gtb_status gtb_partition_get(const gtb_engine* e, int32_t* owner, double* out16)
  * segments, same-camera segments, panel + Schur tasks.                                                            */
 gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8);
 
+/* ---- allocation-free entry point -------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * A variant of the nonlinear-error pass behind gtb_error (error_kernel + sum_partials_kernel): the error
+ * sum over the n factors of ONE bucket, 0.5 * sum || whiten(h(x) - z) ||^2, whose per-CTA partial sums go to a fixed
+ * file-scope __device__ array (256 KB per GPU that loads the library, held until exit) instead of engine memory.  The
+ * call allocates nothing (no cudaMalloc / cudaFree / allocating library routine), only enqueues two kernels on `stream`
+ * and returns without synchronising.  ALL pointers are caller-owned DEVICE pointers on `device`:
+ *   state0 / state1   type arrays of key 0 / key 1 in the device layout (POSE2 rows are (cos, sin, x, y); others as above);
+ *                     state1, row1 = NULL for the prior buckets
+ *   row0 / row1       int32 row of each factor's key in its type array
+ *   z                 measurements, device layout (BETWEEN2 / PRIOR2: (cos, sin, x, y); others as in gtb_set_factors)
+ *   noise_kind, noise both NULL = every factor Unit; else RESOLVED kinds per factor (0 unit, 1 isotropic: noise[0] = 1/sigma,
+ *                     2 diagonal: noise[0..d) = 1/sigma_i, 3 full: upper-triangular sqrt information, row-major) and d*d
+ *                     doubles per factor
+ *   error_out         one double
+ * Limit: n <= GTB_NOALLOC_MAX_FACTORS, larger counts are rejected with GTB_ERR_INVALID (message in
+ * gtb_noalloc_last_error()).  Every call shares the one scratch array, which keeps the last call's contents (nothing in
+ * it needs to start at zero: each partial read is written by the same call first); calls that OVERLAP on the GPU
+ * (different streams without a dependency, or several host threads) race on it -- order them.
+ * gtb_noalloc_setup(device) resolves the array's device address (cudaGetSymbolAddress, once per device); the first call
+ * on a device does it implicitly, so call it beforehand if the first use is under stream capture.                    */
+#define GTB_NOALLOC_MAX_FACTORS (1 << 22)
+gtb_status gtb_noalloc_setup(int device);
+gtb_status gtb_bucket_error_noalloc(int device, int bucket, int64_t n, const double* state0, const double* state1,
+                                    const int32_t* row0, const int32_t* row1, const double* z, const int8_t* noise_kind,
+                                    const double* noise, double* error_out, void* stream);
+const char* gtb_noalloc_last_error(void);
+
 /* ---- instrumentation ------------------------------------------------------------------------------- */
 /* Number of engine kernels launched since creation.                                                      */
 int64_t gtb_kernel_launches(const gtb_engine* e);
