@@ -5,7 +5,8 @@ import os
 import re
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgtsam_b200.so")
+# GTB_LIB: another build of the same library (A/B timing of two commits on one box); default: the in-tree build
+LIB_PATH = os.environ.get("GTB_LIB") or os.path.join(HERE, "libgtsam_b200.so")
 HEADER = os.path.join(os.path.dirname(HERE), "include", "gtsam_b200.h")
 
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_INDETERMINATE, ERR_KEY_MISSING, ERR_NOISE_MODEL, ERR_INCONSISTENT = range(8)

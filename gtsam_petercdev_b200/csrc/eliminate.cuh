@@ -28,7 +28,7 @@ struct CliqueDev {
   int32_t first_key_var;  // variable id of the first frontal key (failure reporting)
   int32_t dfac_off;       // large fronts: offset of the factored diagonal blocks' side buffer (doubles)
   int32_t flags;          // kCliqueStar: a point clique whose factors are SFM factors of distinct cameras
-  int32_t pad;
+  int32_t flag_off;       // large fronts whose Schur step is split over K: first hand-shake flag of its tiles (ElimDev::tile_flags)
 };
 constexpr int32_t kCliqueStar = 1;
 constexpr int32_t kCliqueFuseUp = 2;   // large front whose Schur-complement step adds C - S^T S straight into its (large) parent
@@ -49,6 +49,12 @@ struct ElimDev {
   long long* dbg;       // optional cycle probe of role A (GTB_DEBUG & 8)
   int32_t dbg_clique, dbg_child;
   int32_t debug;        // experiment switches (GTB_DEBUG env): 1 skip tile tasks, 2 skip role-A column work, 4 skip role A
+  // Ordered hand-over (default): every entry of a large front receives at most ONE contribution per launch, or its
+  // contributions inside a launch are serialised in a fixed order, so that a factorisation repeats bit for bit.
+  int32_t ordered;      // 0 (GTB_HANDOVER_ATOMIC=1): the round-1 behaviour, contributions meet through unordered FP64 atomics
+  int32_t epoch32;      // 32 x the factorisation counter: base value of the K-split hand-shake flags of this factorisation
+  int32_t* tile_flags;  // one flag per tile of every K-split Schur step (CliqueDev::flag_off)
+  double* pair_scratch; // partial 9 x 9 blocks of camera-pair groups that are cut into several segments (kPairSlot doubles each)
 };
 
 __constant__ int c_M[7] = {3, 6, 2, 3, 6, 9, 3};
@@ -66,6 +72,14 @@ __device__ __forceinline__ int frexp_exp(double x) {
 // schedule (task list, clique descriptors), and only then waits for the predecessor grid to finish and flush.
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// Fire-and-forget FP64 add to global memory (RED.E.ADD.F64): the thread does not wait for the result.  Written as PTX
+// because the compiler turns an unused-result atomicAdd into the waiting form (ATOM) as soon as a fence follows it in
+// the same function -- seen in the SASS of schur_step_kernel, where it cost 1.1 ms per step.  A later __threadfence()
+// still orders these adds before whatever the thread writes after it.
+__device__ __forceinline__ void red_add(double* p, double v) {
+  asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
 
 // one 32-byte column of a point front in a single request (LDG.256, read-only path)
 struct Col4 { double x, y, z, w; };
@@ -379,7 +393,9 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
   int32_t* pm_s = reinterpret_cast<int32_t*>(stage);   // S + 1 <= 208 entries; the staging area is free
   if (ci.parent >= 0) {
     const CliqueDev cp = E.cliques[ci.parent];
-    fused = is_fused_child(F, dim, cp.F, cp.F + cp.S + 1);
+    // ordered hand-over: several thin children of one parent may sit in the same launch, so the child keeps its Schur
+    // complement in its own front and extend_add_kernel adds it at the parent's level, child by child
+    fused = !E.ordered && is_fused_child(F, dim, cp.F, cp.F + cp.S + 1);
     if (fused) {
       pdst = E.arena + cp.front_off;
       pld = cp.ld;
@@ -681,7 +697,13 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_rows_kernel(ElimDev E, 
 // into segments whose partial sums meet in the parent through atomics (81 per segment instead of 81 per item).
 // ----------------------------------------------------------------------------------------------------
 constexpr int kPairSeg = 32;
+// ld > 0: the segment is the whole list of its block and adds it to the parent front at arena + dst (one contribution per
+// entry and launch: the order of the sum is the list order).  ld == 0 (ordered hand-over, list cut into several
+// segments): the partial block goes to pair_scratch + dst (compact: entry (i, c) at i + 9 c, rhs column at 81 + i,
+// constant term at 90) and pair_reduce_kernel adds the segments' partials in list order.
+constexpr int kPairSlot = 96;
 struct PairSeg { int64_t dst; int32_t ld; int32_t begin; int32_t count; int32_t ncol; };   // ncol: columns from the block to the parent's rhs column
+struct PairReduce { int64_t dst; int32_t ld, ncol, slot0, count, diag, pad; };
 __global__ void __launch_bounds__(128) point_pair_kernel(ElimDev E, const PairSeg* __restrict__ segs, int nseg,
                                                          const uint2* __restrict__ items) {
   const int gt = blockIdx.x * 128 + threadIdx.x;
@@ -705,6 +727,14 @@ __global__ void __launch_bounds__(128) point_pair_kernel(ElimDev E, const PairSe
 #pragma unroll
       for (int c = 0; c < 3; ++c) acc[i][c] += u.x * b[c].x + u.y * b[c].y + u.z * b[c].z;
     }
+  }
+  if (sg.ld == 0) {
+    double* out = E.pair_scratch + sg.dst + 27 * slab;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int i = 0; i < 9; ++i) out[i + 9 * c] = -acc[i][c];
+    return;
   }
   double* dst = E.arena + sg.dst + (int64_t)(3 * slab) * sg.ld;
 #pragma unroll
@@ -766,6 +796,20 @@ __global__ void __launch_bounds__(128) point_diag_kernel(ElimDev E, const PairSe
       if (ir >> 31) cst -= r.x * r.x + r.y * r.y + r.z * r.z;
     }
   }
+  if (sg.ld == 0) {
+    double* out = E.pair_scratch + sg.dst;
+    if (slab < 3) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int i = 0; i < 9; ++i) out[i + 9 * (3 * slab + c)] = acc[i][c];
+    } else {
+#pragma unroll
+      for (int i = 0; i < 9; ++i) out[81 + i] = acc[i][0];
+      out[90] = cst;
+    }
+    return;
+  }
   if (slab < 3) {
     double* dst = E.arena + sg.dst + (int64_t)(3 * slab) * sg.ld;
 #pragma unroll
@@ -781,17 +825,36 @@ __global__ void __launch_bounds__(128) point_diag_kernel(ElimDev E, const PairSe
   }
 }
 
+// Ordered sum of the partial blocks of a camera-pair (or same-camera) group that was cut into several segments: one
+// thread per block entry adds the segments' partials in list order and hands the sum to the parent once.
+__global__ void __launch_bounds__(2 * kPairSlot) pair_reduce_kernel(ElimDev E, const PairReduce* __restrict__ items, int n) {
+  const int it = blockIdx.x * 2 + threadIdx.x / kPairSlot, e = threadIdx.x % kPairSlot;
+  if (it >= n) return;
+  const PairReduce r = items[it];
+  const int i = e % 9, c = e / 9;
+  int64_t off = 0;
+  bool use = false;
+  if (e < 81) { use = !r.diag || i <= c; off = i + (int64_t)c * r.ld; }
+  else if (e < 90) { use = r.diag != 0; off = (e - 81) + (int64_t)r.ncol * r.ld; }
+  else if (e == 90) { use = r.diag != 0; off = r.ncol + (int64_t)r.ncol * r.ld; }
+  if (!use) return;
+  const double* sp = E.pair_scratch + (int64_t)r.slot0 * kPairSlot + e;
+  double acc = 0.0;
+  for (int k = 0; k < r.count; ++k) acc += sp[(int64_t)k * kPairSlot];
+  red_add(E.arena + r.dst + off, acc);   // the only contribution to this entry in this launch
+}
+
 // ----------------------------------------------------------------------------------------------------
 // large fronts: front in global memory (L2-resident), several CTAs per front
 // ----------------------------------------------------------------------------------------------------
 // zeroing of very large fronts is spread over many CTAs
 __global__ void __launch_bounds__(256) large_zero_kernel(ElimDev E, const int32_t* __restrict__ list) {
-  const int c = list[blockIdx.y];
+  const int c = list[blockIdx.x];   // the front on x: the y extent of a grid stops at 65,535
   const CliqueDev ci = E.cliques[c];
   const int dim = ci.F + ci.S + 1;
   // upper triangle only (nothing reads below the diagonal): column j, rows 0..j, as 16-byte stores (ld is a multiple of 4)
   double* A = E.arena + ci.front_off;
-  for (int j = blockIdx.x; j < dim; j += gridDim.x) {
+  for (int j = blockIdx.y; j < dim; j += gridDim.y) {
     double2* col = reinterpret_cast<double2*>(A + (int64_t)j * ci.ld);
     const int n2 = (j + 2) >> 1;
     for (int i = threadIdx.x; i < n2; i += blockDim.x) col[i] = make_double2(0.0, 0.0);
@@ -824,6 +887,47 @@ __global__ void __launch_bounds__(256) large_children_kernel(ElimDev E, const Ch
       if (a > b) { const int t = a; a = b; b = t; }
       atomicAdd(dst + a + (int64_t)b * cp.ld, col[i]);   // (a plain read-modify-write measured 2.7x slower)
     }
+  }
+}
+
+// Ordered extend-add (default): the Schur complements of the children of a large front that do not hand over by
+// themselves (thin and dense small children, subtree roots owned by this rank under the shared top) are added by the
+// PARENT, child after child in the reference's child order (inference/ClusterTree-inst.h:223-226).  A CTA owns a range of
+// parent columns [col_begin, col_end); for every child it finds the child columns that land there through the child's
+// separator SORTED BY PARENT COLUMN (spm[v] = parent column, sg[v] = child separator index, ascending spm): entry (u, v),
+// u <= v, of the sorted child goes to parent (spm[u], spm[v]), so a parent entry has one owner thread per child and one
+// barrier per child keeps the children in order.  The adds are fire-and-forget reductions.
+struct GatherWork { int32_t parent, col_begin, col_end, list_begin, list_end, pad; };
+__global__ void __launch_bounds__(256) extend_add_kernel(ElimDev E, const GatherWork* __restrict__ work,
+                                                         const int32_t* __restrict__ gchild, const int64_t* __restrict__ gsmap_off,
+                                                         const int32_t* __restrict__ smap) {
+  pdl_trigger();
+  const GatherWork w = work[blockIdx.x];
+  const CliqueDev cp = E.cliques[w.parent];
+  pdl_wait();
+  double* dst = E.arena + cp.front_off;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int q = w.list_begin; q < w.list_end; ++q) {
+    const CliqueDev cc = E.cliques[gchild[q]];
+    const int S1 = cc.S + 1;
+    const int32_t* spm = smap + gsmap_off[q];
+    const int32_t* sg = spm + S1;
+    int lo = 0, hi = S1;   // first sorted position with spm >= col_begin
+    while (lo < hi) { const int m = (lo + hi) >> 1; if (spm[m] < w.col_begin) lo = m + 1; else hi = m; }
+    const int v0 = lo;
+    hi = S1;
+    while (lo < hi) { const int m = (lo + hi) >> 1; if (spm[m] < w.col_end) lo = m + 1; else hi = m; }
+    const int v1 = lo;
+    const double* src = E.arena + cc.front_off + cc.F + (int64_t)cc.F * cc.ld;
+    for (int v = v0 + warp; v < v1; v += nw) {
+      const int pb = spm[v], jv = sg[v];
+      for (int u = lane; u <= v; u += 32) {
+        const int iu = sg[u];
+        const int ci = min(iu, jv), cj = max(iu, jv);
+        red_add(dst + spm[u] + (int64_t)pb * cp.ld, src[ci + (int64_t)cj * cc.ld]);
+      }
+    }
+    __syncthreads();   // the next child's contribution to an entry may come from another thread of this CTA
   }
 }
 
@@ -878,7 +982,8 @@ constexpr int kStages = 3;
 template <int MODE = 0>
 __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int dim, int r0, int c0, int re, int ka,
                                             int kend, double* sm, const int32_t* __restrict__ pm = nullptr,
-                                            double* __restrict__ PA = nullptr, int pld = 0, int F = 0, bool add_c = false) {
+                                            double* __restrict__ PA = nullptr, int pld = 0, int F = 0, bool add_c = false,
+                                            int* flag = nullptr, int turn = 0) {
   double* Xs = sm;                        // [kStages][TW * LDT]
   double* Ys = sm + kStages * TW * LDT;   // [kStages][TW * LDT]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -962,6 +1067,16 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
     }
   }
   cp_async_wait<0>();
+  // Ordered K split: the slices of a tile hand their partial products over one after the other (slice 0 first): a slice
+  // waits until the tile's flag says that its predecessor's adds are visible.  The CTAs of earlier slices come earlier in
+  // the task list, so they are resident (or done) whenever a later slice spins.
+  if (flag && MODE != 0) {
+    if (tid == 0) {
+      while (*reinterpret_cast<volatile int*>(flag) != turn) __nanosleep(40);
+      __threadfence();
+    }
+    __syncthreads();
+  }
 #pragma unroll
   for (int a = 0; a < 4; ++a)
 #pragma unroll
@@ -974,15 +1089,20 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
           if (MODE == 2) {
             int pa = prow[a], pb = pcol[b][e];
             if (pa > pb) { const int tt = pa; pa = pb; pb = tt; }
-            atomicAdd(PA + pa + (int64_t)pb * pld, -acc[a][b][e]);
+            red_add(PA + pa + (int64_t)pb * pld, -acc[a][b][e]);
           } else if (MODE == 1) {
-            atomicAdd(A + i + (int64_t)j * ld, -acc[a][b][e]);
+            red_add(A + i + (int64_t)j * ld, -acc[a][b][e]);
           } else {
             A[i + (int64_t)j * ld] = -acc[a][b][e];
           }
         }
       }
     }
+  if (flag && MODE != 0) {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) *reinterpret_cast<volatile int*>(flag) = turn + 1;
+  }
 }
 
 // number of tile tasks of a trapezoid: nrt tile rows, nct tile columns, only tiles with tx >= ty
@@ -1381,14 +1501,17 @@ __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const Ste
     const int nchunk = (F + NB - 1) / NB;
     const int ka = nsplit <= 1 ? 0 : (int)((int64_t)nchunk * slice / nsplit) * NB;
     const int kend = nsplit <= 1 ? F : min(F, (int)((int64_t)nchunk * (slice + 1) / nsplit) * NB);
+    // hand-shake flag of this tile when its K sum is split (ordered hand-over): value epoch32 + s lets slice s in
+    int* flag = (E.ordered && nsplit > 1) ? E.tile_flags + ci.flag_off + tile : nullptr;
+    if (flag && slice == 0 && threadIdx.x == 0) *reinterpret_cast<volatile int*>(flag) = E.epoch32;   // (no predecessor)
     if (ci.flags & kCliqueFuseUp) {
       const CliqueDev cp = E.cliques[ci.parent];
       tile_update<2>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm, E.pmap + ci.pmap_off, E.arena + cp.front_off, cp.ld, F,
-                     slice == 0);
+                     slice == 0, flag, E.epoch32 + slice);
     } else if (nsplit <= 1) {
       tile_update<0>(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
     } else {
-      tile_update<1>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm);
+      tile_update<1>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm, nullptr, nullptr, 0, 0, false, flag, E.epoch32 + slice);
     }
   }
   if (probe) {

@@ -87,6 +87,14 @@ struct LevelSched {
   std::vector<int32_t> step_count;
   std::vector<int64_t> schur_begin; // per step: tile tasks of the cliques whose Schur-complement step this is
   std::vector<int32_t> schur_count;
+  // ordered hand-over: the Schur-step tasks of a step are cut into one launch per rank among same-level siblings that hand
+  // over to the same parent, so that a parent entry receives at most one contribution per launch
+  struct Run { int64_t begin; int32_t count; };
+  std::vector<std::vector<Run>> schur_runs;
+  int64_t gather_begin = 0;   // ordered extend-add work items of this level's large parents (extend_add_kernel)
+  int32_t n_gather = 0;
+  int64_t red_begin = 0;      // camera-pair groups cut into several segments: ordered sums (pair_reduce_kernel)
+  int32_t n_red = 0;
   // Schur complement of this level's point cliques, gathered per camera pair (point_pair_kernel / point_diag_kernel)
   int64_t pair_seg_begin = 0, diag_seg_begin = 0;
   int32_t n_pair_seg = 0, n_diag_seg = 0;
@@ -133,6 +141,19 @@ struct gtb_engine {
   std::vector<LevelSched> sched[2];   // phase 0: this rank's subtrees, phase 1: the shared top of the tree (rank 0)
   std::vector<int32_t> sched_lists;   // clique lists of both phases, level by level
   std::vector<ChildWork> child_work;
+  // ordered hand-over (default; GTB_HANDOVER_ATOMIC=1 restores the unordered atomics of round 1)
+  bool ordered = true;
+  int32_t epoch = 0;                       // factorisation counter (K-split hand-shake flags)
+  std::vector<GatherWork> gather_work;     // per level, then the top work of this rank
+  std::vector<int32_t> gather_child;       // child lists of the work items
+  std::vector<int64_t> gather_smap_off;    // per list entry: offset of the child's sorted separator map in smap
+  std::vector<int32_t> smap;               // per gathered child: parent columns ascending (S + 1), then the child separator index of each
+  std::vector<int64_t> smap_of;            // per clique: offset in smap or -1
+  int64_t top_gather_begin = 0;
+  int32_t n_top_gather = 0;
+  std::vector<PairReduce> pair_reduce;
+  int64_t pair_slots = 0, tile_flags = 0;
+  std::vector<int32_t> flag_off;           // per clique: first K-split flag or 0
   // ---- distribution over ranks: one process per GPU ----
   int rank = 0, world = 1;
   gtb_comm_fn comm = nullptr;
@@ -183,6 +204,11 @@ struct gtb_engine {
   DevBuf<int32_t> d_top_list, d_large_list;
   DevBuf<uint8_t> d_own_mask;
   DevBuf<ChildWork> d_child_work;
+  DevBuf<GatherWork> d_gather_work;
+  DevBuf<int32_t> d_gather_child, d_smap, d_tile_flags;
+  DevBuf<int64_t> d_gather_smap_off;
+  DevBuf<PairReduce> d_pair_reduce;
+  DevBuf<double> d_pair_scratch;
   DevBuf<StepTask> d_step_tasks;
   DevBuf<PairSeg> d_pair_segs;
   DevBuf<uint2> d_pair_items;
@@ -199,6 +225,8 @@ struct gtb_engine {
   DevBuf<double> d_sigma, d_marg_scratch;
   bool marg_built = false, marg_valid = false;
   bool linearized = false, factorized = false, solved = false, have_hdiag = false;
+  bool retracted = false;          // the scratch copy holds Values::retract(delta) of the current values
+  bool lin_attr[7] = {false, false, false, false, false, false, false}, elim_attr = false;   // cudaFuncSetAttribute done on this engine's device
 
   bool profiling = false;
   std::vector<cudaEvent_t> prof_events;
@@ -413,7 +441,7 @@ static void set_variables(Engine* e, int vt, int64_t n, const uint64_t* keys, co
       else for (int64_t i = 0; i < n; ++i) to_device_state(vt, state + i * kStateIn[vt], hs + i * kStateDev[vt]);
       CK(cudaMemcpyAsync(e->d_state[e->cur][vt].p, hs, v.state.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
       CK(cudaEventRecord(e->stage_ev[vt], e->stream));
-      e->linearized = e->factorized = e->solved = false;
+      e->linearized = e->factorized = e->solved = e->retracted = false;
       e->lm_have_error = false;
     }
     return;
@@ -614,6 +642,40 @@ static void finalize_problem(Engine* e) {
 // ------------------------------------------------------------------------------------------------------
 // symbolic plan -> device
 // ------------------------------------------------------------------------------------------------------
+// Ordered extend-add of the given children (all of one large parent, child order) by the parent: the child's separator
+// sorted by parent column, and work items that own column ranges of the parent of roughly equal triangle area.
+static void push_gather(Engine* e, int32_t par, const std::vector<int32_t>& kids) {
+  if (kids.empty()) return;
+  const Plan& pp = e->plan;
+  const int64_t lb = (int64_t)e->gather_child.size();
+  int64_t entries = 0;
+  for (int32_t ch : kids) {
+    const int32_t S1 = pp.S[ch] + 1;
+    if (e->smap_of[ch] < 0) {
+      e->smap_of[ch] = (int64_t)e->smap.size();
+      const int32_t* pm = pp.pmap.data() + pp.pmap_off[ch];
+      std::vector<std::pair<int32_t, int32_t>> byp(S1);
+      for (int32_t i = 0; i < S1; ++i) byp[i] = {pm[i], i};
+      std::sort(byp.begin(), byp.end());
+      for (int32_t i = 0; i < S1; ++i) e->smap.push_back(byp[i].first);
+      for (int32_t i = 0; i < S1; ++i) e->smap.push_back(byp[i].second);
+    }
+    e->gather_child.push_back(ch);
+    e->gather_smap_off.push_back(e->smap_of[ch]);
+    entries += (int64_t)S1 * (S1 + 1) / 2;
+  }
+  const int64_t le = (int64_t)e->gather_child.size();
+  const int32_t dimP = pp.F[par] + pp.S[par] + 1;
+  const int32_t nchunk = (int32_t)std::max<int64_t>(1, std::min<int64_t>(96, entries / 4096));
+  int32_t c0 = 0;
+  for (int32_t k2 = 1; k2 <= nchunk; ++k2) {
+    int32_t c1 = (k2 == nchunk) ? dimP : (int32_t)std::lround(dimP * std::sqrt((double)k2 / nchunk));
+    c1 = std::max(c1, c0);
+    if (c1 > c0) e->gather_work.push_back(GatherWork{par, c0, c1, (int32_t)lb, (int32_t)le, 0});
+    c0 = c1;
+  }
+}
+
 // extend-add work items of one child: column chunks of roughly equal triangle area
 static void push_child_work(Engine* e, int32_t ch) {
   const Plan& pp = e->plan;
@@ -810,17 +872,49 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
           if (sidx == (p.F[c] + PW - 1) / PW) launch_tiles += step_tasks(p.F[c], p.F[c] + p.S[c] + 1, sidx);
         }
         static const int split_target = getenv("GTB_SCHUR_SPLIT") ? atoi(getenv("GTB_SCHUR_SPLIT")) : 2 * 148;
-        for (int64_t q = L.large_begin; q < en; ++q) {
-          const int32_t c = lc[q];
-          const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
-          if (sidx != np_c) continue;
-          const int n = step_tasks(F, dim, sidx);
-          need(n < (1 << kSchurTileBits), "Schur-step tile count overflow");
-          int nsplit = 1;
-          if (launch_tiles > 0 && launch_tiles < split_target)
-            nsplit = (int)std::max<int64_t>(1, std::min<int64_t>({(split_target + launch_tiles - 1) / launch_tiles, F / 128, 31}));
-          for (int sl = 0; sl < nsplit; ++sl)
-            for (int t = 0; t < n; ++t) e->step_tasks_list.push_back(StepTask{c, schur_task(t, sl, nsplit)});
+        // ordered hand-over: rank of a clique among the same-level siblings that hand over to the same parent by
+        // themselves (fuse_up): one launch per rank (the unordered mode keeps one launch)
+        auto sib_rank = [&](int32_t c) {
+          if (!e->ordered || !e->fuse_up[c]) return 0;
+          int r = 0;
+          const int32_t par = p.parent[c];
+          for (int64_t k = p.child_off[par]; k < p.child_off[par + 1] && p.children[k] != c; ++k) {
+            const int32_t sb = p.children[k];
+            if (e->fuse_up[sb] && p.level[sb] == p.level[c] && mine(sb)) ++r;
+          }
+          return r;
+        };
+        int max_rank = 0;
+        for (int64_t q = L.large_begin; q < en; ++q)
+          if (sidx == (p.F[lc[q]] + PW - 1) / PW) max_rank = std::max(max_rank, sib_rank(lc[q]));
+        L.schur_runs.emplace_back();
+        for (int rk = 0; rk <= max_rank; ++rk) {
+          const int64_t run_begin = (int64_t)e->step_tasks_list.size();
+          int64_t run_tiles = 0;
+          for (int64_t q = L.large_begin; q < en; ++q) {
+            const int32_t c = lc[q];
+            if (sidx == (p.F[c] + PW - 1) / PW && sib_rank(c) == rk) run_tiles += step_tasks(p.F[c], p.F[c] + p.S[c] + 1, sidx);
+          }
+          if (!e->ordered) run_tiles = launch_tiles;
+          for (int64_t q = L.large_begin; q < en; ++q) {
+            const int32_t c = lc[q];
+            const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
+            if (sidx != np_c || sib_rank(c) != rk) continue;
+            const int n = step_tasks(F, dim, sidx);
+            need(n < (1 << kSchurTileBits), "Schur-step tile count overflow");
+            int nsplit = 1;
+            if (run_tiles > 0 && run_tiles < split_target)
+              nsplit = (int)std::max<int64_t>(1, std::min<int64_t>({(split_target + run_tiles - 1) / run_tiles, F / 128, 31}));
+            if (nsplit > 1 && e->ordered) {   // hand-shake flags: the K slices of a tile add one after the other
+              e->flag_off[c] = (int32_t)e->tile_flags;
+              e->tile_flags += n;
+              need(e->tile_flags < INT32_MAX, "K-split flag overflow");
+            }
+            for (int sl = 0; sl < nsplit; ++sl)
+              for (int t = 0; t < n; ++t) e->step_tasks_list.push_back(StepTask{c, schur_task(t, sl, nsplit)});
+          }
+          const int32_t cnt = (int32_t)((int64_t)e->step_tasks_list.size() - run_begin);
+          if (cnt > 0) L.schur_runs.back().push_back(LevelSched::Run{run_begin, cnt});
         }
         L.schur_count.push_back((int32_t)(e->step_tasks_list.size() - L.schur_begin.back()));
       }
@@ -828,12 +922,20 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
     // extend-add work of this level's large parents.  Phase 1 only adds the children that are top cliques themselves:
     // subtree children were added before the reduction by whichever rank owns them (top_work).
     L.work_begin = (int64_t)e->child_work.size();
+    L.gather_begin = (int64_t)e->gather_work.size();
     for (int64_t q = L.large_begin; q < en; ++q) {
       const int32_t c = lc[q];
-      for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k)
-        if (ph == 0 || e->owner[p.children[k]] < 0) push_child_work(e, p.children[k]);
+      std::vector<int32_t> kids;
+      for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k) {
+        const int32_t ch = p.children[k];
+        if (!(ph == 0 || e->owner[ch] < 0)) continue;
+        if (!e->ordered) push_child_work(e, ch);
+        else if (!e->is_point[ch] && !e->fuse_up[ch]) kids.push_back(ch);
+      }
+      push_gather(e, c, kids);
     }
     L.n_work = (int32_t)(e->child_work.size() - L.work_begin);
+    L.n_gather = (int32_t)(e->gather_work.size() - L.gather_begin);
     L.bs_begin = (int64_t)e->bs_list.size();
     int32_t maxN = 0;
     for (int pass = 0; pass < 2; ++pass)
@@ -978,6 +1080,8 @@ static void build_point_pairs(Engine* e) {
   e->pair_segs.clear();
   e->pair_items.clear();
   e->diag_items.clear();
+  e->pair_reduce.clear();
+  e->pair_slots = 0;
   if (!e->point_pairs) return;
   struct OffRec { uint64_t key; uint32_t a, b; };
   struct DiagRec { uint64_t key; uint32_t y, fac, rhs; };
@@ -1014,6 +1118,8 @@ static void build_point_pairs(Engine* e) {
       if (dg.empty()) continue;
       radix_sort_by_key(off);
       radix_sort_by_key(dg);
+      int64_t level_slots = 0;
+      L.red_begin = (int64_t)e->pair_reduce.size();
       auto emit = [&](auto& recs, bool diag, int64_t& seg_begin, int32_t& n_seg) {
         std::vector<PairSeg> segs;
         const int64_t item0 = diag ? (int64_t)e->diag_items.size() / 3 : (int64_t)e->pair_items.size();
@@ -1024,8 +1130,17 @@ static void build_point_pairs(Engine* e) {
           const int32_t ldp = e->ld[P], NP = p.F[P] + p.S[P];
           const int64_t dst = e->front_off[P] + A + (int64_t)(diag ? A : B) * ldp;
           const size_t cap = diag ? cap_diag : cap_pair;
-          for (size_t s0 = i; s0 < j; s0 += cap)
-            segs.push_back(PairSeg{dst, ldp, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(cap, j - s0), NP - A});
+          if (e->ordered && j - i > cap) {
+            // several segments: their partial blocks go to scratch slots and are summed in list order
+            const int32_t nsg = (int32_t)((j - i + cap - 1) / cap);
+            e->pair_reduce.push_back(PairReduce{dst, ldp, NP - A, (int32_t)level_slots, nsg, diag ? 1 : 0, 0});
+            for (size_t s0 = i; s0 < j; s0 += cap)
+              segs.push_back(PairSeg{(level_slots++) * kPairSlot, 0, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(cap, j - s0), NP - A});
+            need(level_slots < INT32_MAX / kPairSlot, "pair scratch overflow");
+          } else {
+            for (size_t s0 = i; s0 < j; s0 += cap)
+              segs.push_back(PairSeg{dst, ldp, (int32_t)(item0 + s0), (int32_t)std::min<size_t>(cap, j - s0), NP - A});
+          }
           i = j;
         }
         need(item0 + (int64_t)recs.size() < INT32_MAX, "point pair list overflow");
@@ -1044,6 +1159,8 @@ static void build_point_pairs(Engine* e) {
       for (const OffRec& r : off) e->pair_items.push_back(make_uint2(r.a, r.b));
       emit(dg, true, L.diag_seg_begin, L.n_diag_seg);
       for (const DiagRec& r : dg) { e->diag_items.push_back(r.y); e->diag_items.push_back(r.fac); e->diag_items.push_back(r.rhs); }
+      L.n_red = (int32_t)((int64_t)e->pair_reduce.size() - L.red_begin);
+      e->pair_slots = std::max(e->pair_slots, level_slots);
     }
 }
 
@@ -1055,7 +1172,18 @@ static void install_plan(Engine* e) {
     const char* pa = getenv("GTB_POINT_ATOMIC");
     e->point_pairs = !(pa && atoi(pa));
   }
+  {
+    const char* ha = getenv("GTB_HANDOVER_ATOMIC");
+    e->ordered = !(ha && atoi(ha));
+  }
   e->child_work.clear();
+  e->gather_work.clear();
+  e->gather_child.clear();
+  e->gather_smap_off.clear();
+  e->smap.clear();
+  e->smap_of.assign(C, -1);
+  e->flag_off.assign(C, 0);
+  e->tile_flags = 0;
   e->bs_list.clear();
   e->bs_scratch_off.clear();
   e->bs_scratch_doubles = 0;
@@ -1148,10 +1276,19 @@ static void install_plan(Engine* e) {
   e->top_doubles = tail - e->top_off;
   e->arena_doubles = tail;
   e->top_work_begin = (int64_t)e->child_work.size();
-  for (int32_t c : e->top_list)
-    for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k)
-      if (e->owner[p.children[k]] == e->rank) push_child_work(e, p.children[k]);
+  e->top_gather_begin = (int64_t)e->gather_work.size();
+  for (int32_t c : e->top_list) {
+    std::vector<int32_t> kids;
+    for (int64_t k = p.child_off[c]; k < p.child_off[c + 1]; ++k) {
+      const int32_t ch = p.children[k];
+      if (e->owner[ch] != e->rank) continue;
+      if (!e->ordered) push_child_work(e, ch);
+      else if (!e->is_point[ch]) kids.push_back(ch);
+    }
+    push_gather(e, c, kids);
+  }
   e->n_top_work = (int32_t)(e->child_work.size() - e->top_work_begin);
+  e->n_top_gather = (int32_t)(e->gather_work.size() - e->top_gather_begin);
   // scalars whose solution this rank produces (frontals of its cliques; the top belongs to rank 0)
   std::vector<uint8_t> own(e->n_scalars, 0);
   for (int32_t c = 0; c < C; ++c)
@@ -1172,7 +1309,7 @@ static void install_plan(Engine* e) {
     d.pmap_off = (int32_t)p.pmap_off[c]; d.gidx_off = (int32_t)p.gidx_off[c];
     d.first_key_var = p.vars[p.vars_off[c]];
     d.dfac_off = 0;
-    d.pad = 0;
+    d.flag_off = e->flag_off[c];
     d.flags = (is_star_clique(e, c, 15) ? kCliqueStar : 0) | (e->fuse_up[c] ? kCliqueFuseUp : 0);
     if (!e->is_point[c] && !is_small_front(p.F[c], p.F[c] + p.S[c] + 1)) {
       d.dfac_off = (int32_t)dfac_total;
@@ -1195,6 +1332,15 @@ static void install_plan(Engine* e) {
   e->d_large_list.upload(e->large_list, st);
   e->d_own_mask.upload(own, st);
   e->d_child_work.upload(e->child_work, st);
+  e->d_gather_work.upload(e->gather_work, st);
+  e->d_gather_child.upload(e->gather_child, st);
+  e->d_gather_smap_off.upload(e->gather_smap_off, st);
+  e->d_smap.upload(e->smap, st);
+  e->d_pair_reduce.upload(e->pair_reduce, st);
+  e->d_pair_scratch.alloc((size_t)e->pair_slots * kPairSlot + 1);
+  e->d_tile_flags.alloc((size_t)e->tile_flags + 1);
+  CK(cudaMemsetAsync(e->d_tile_flags.p, 0, ((size_t)e->tile_flags + 1) * sizeof(int32_t), st));
+  e->epoch = 0;
   e->d_bs_list.upload(e->bs_list, st);
   e->d_bs_scratch_off.upload(e->bs_scratch_off, st);
   e->d_bs_scratch.alloc((size_t)e->bs_scratch_doubles + 1);
@@ -1237,10 +1383,9 @@ template <int B> static void launch_linearize(Engine* e) {
   constexpr int MW = T::M * T::W;
   constexpr int LDS = (MW % 2 == 0) ? MW + 1 : MW;
   const int smem = kFactorThreads * LDS * sizeof(double);
-  static bool attr = false;
-  if (!attr) {
+  if (!e->lin_attr[B]) {   // function attributes are per device: one flag per engine, not per process
     CK(cudaFuncSetAttribute(linearize_kernel<B>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr = true;
+    e->lin_attr[B] = true;
   }
   const int grid = (bk.n + kFactorThreads - 1) / kFactorThreads;
   const double* s0 = e->d_state[e->cur][T::T0].p;
@@ -1255,7 +1400,7 @@ static void linearize(Engine* e) {
   launch_linearize<4>(e); launch_linearize<5>(e); launch_linearize<6>(e);
   tm.stop();
   e->linearized = true;
-  e->factorized = e->solved = e->have_hdiag = false;
+  e->factorized = e->solved = e->have_hdiag = e->retracted = false;
 }
 
 template <int B> static void launch_error(Engine* e, int which) {
@@ -1324,6 +1469,10 @@ static ElimDev elim_dev(Engine* e, bool damp) {
   for (int b = 0; b < 7; ++b) E.Ab[b] = e->d_Ab[b].p;
   E.damp = damp ? e->d_damp.p : nullptr;
   E.fail = e->d_fail.p;
+  E.ordered = e->ordered ? 1 : 0;
+  E.epoch32 = (e->epoch & 0x3ffffff) * 32;
+  E.tile_flags = e->d_tile_flags.p;
+  E.pair_scratch = e->d_pair_scratch.p;
   static const int dbg = getenv("GTB_DEBUG") ? atoi(getenv("GTB_DEBUG")) : 0;
   E.debug = dbg;
   E.dbg = (dbg & 8) ? e->d_dbg.p : nullptr;
@@ -1376,15 +1525,20 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
     if (L.n_diag_seg)
       LAUNCH(e, K_PAIR, point_diag_kernel<<<(4 * L.n_diag_seg + 127) / 128, 128, 0, st>>>(E, e->d_pair_segs.p + L.diag_seg_begin, L.n_diag_seg,
                                                                                           e->d_diag_items.p));
+    if (L.n_red)
+      LAUNCH(e, K_PAIR, pair_reduce_kernel<<<(L.n_red + 1) / 2, 2 * kPairSlot, 0, st>>>(E, e->d_pair_reduce.p + L.red_begin, L.n_red));
     if (!L.n_large) continue;
     if (L.n_work) {
       LAUNCH(e, K_LCHILD, launch_pdl(large_children_kernel, L.n_work, 256, 0, st, E, e->d_child_work.p + L.work_begin));
     }
+    if (L.n_gather)
+      LAUNCH(e, K_LCHILD, launch_pdl(extend_add_kernel, L.n_gather, 256, 0, st, E, e->d_gather_work.p + L.gather_begin,
+                                     (const int32_t*)e->d_gather_child.p, (const int64_t*)e->d_gather_smap_off.p, (const int32_t*)e->d_smap.p));
     for (size_t s = 0; s < L.step_count.size(); ++s) {
       if (L.step_count[s] > 0)
         LAUNCH(e, K_STEP, launch_pdl(front_step_kernel, L.step_count[s], 256, kStepSmem, st, E, e->d_step_tasks.p + L.step_begin[s], (int)s));
-      if (L.schur_count[s] > 0)
-        LAUNCH(e, K_SCHUR, launch_pdl(schur_step_kernel, L.schur_count[s], 256, kStepSmemTile, st, E, e->d_step_tasks.p + L.schur_begin[s]));
+      for (const LevelSched::Run& run : L.schur_runs[s])
+        LAUNCH(e, K_SCHUR, launch_pdl(schur_step_kernel, run.count, 256, kStepSmemTile, st, E, e->d_step_tasks.p + run.begin));
     }
   }
 }
@@ -1410,9 +1564,9 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
   }
   const int32_t init = INT_MAX;
   CK(cudaMemcpyAsync(e->d_fail.p, &init, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  e->epoch++;
   const ElimDev E = elim_dev(e, damp);
-  static bool attr = false;
-  if (!attr) {
+  if (!e->elim_attr) {   // per device, hence per engine
     CK(cudaFuncSetAttribute(small_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(thin_front_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(point_front_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -1422,14 +1576,14 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     CK(cudaFuncSetAttribute(front_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem));
     CK(cudaFuncSetAttribute(schur_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmemTile));
     CK(cudaFuncSetAttribute(backsolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr = true;
+    e->elim_attr = true;
   }
   // every large front this rank touches is cleared and given its own factors first: thin children add their Schur
   // complements into their parents as soon as they are eliminated.  The top of the tree is cleared on every rank but
   // gets its factors (and damping) on rank 0 only: the fan-in sums the copies.
   if (!e->large_list.empty()) {
     const int nz = (int)e->large_list.size(), nf = e->rank == 0 ? nz : e->n_large_own;
-    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3(64, nz), 256, 0, st>>>(E, e->d_large_list.p));
+    LAUNCH(e, K_ZERO, large_zero_kernel<<<dim3(nz, 64), 256, 0, st>>>(E, e->d_large_list.p));
     if (nf) LAUNCH(e, K_LFACT, large_factors_kernel<<<nf, 256, 0, st>>>(E, e->d_large_list.p));
   }
   factorize_levels(e, E, 0);
@@ -1437,6 +1591,9 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     // fan-in: every rank adds what it owns into its copy of the top fronts, the copies are summed onto rank 0
     if (e->n_top_work)
       LAUNCH(e, K_LCHILD, large_children_kernel<<<e->n_top_work, 256, 0, st>>>(E, e->d_child_work.p + e->top_work_begin));
+    if (e->n_top_gather)
+      LAUNCH(e, K_LCHILD, extend_add_kernel<<<e->n_top_gather, 256, 0, st>>>(E, e->d_gather_work.p + e->top_gather_begin, e->d_gather_child.p,
+                                                                             e->d_gather_smap_off.p, e->d_smap.p));
     comm(e, GTB_COMM_REDUCE_SUM_TO_0, e->d_arena.p + e->top_off, e->top_doubles);
     if (e->rank == 0) factorize_levels(e, E, 1);
   }
@@ -1613,6 +1770,7 @@ static void retract(Engine* e) {
   StageTimer tm(e, 4);
   launch_retract<0>(e); launch_retract<1>(e); launch_retract<2>(e); launch_retract<3>(e);
   tm.stop();
+  e->retracted = true;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -1665,7 +1823,7 @@ static bool try_lambda(Engine* e, const gtb_lm_params& P, LMState& S) {
     }
     newLambda = std::max(P.lambda_lower_bound, newLambda);
     e->cur ^= 1;
-    e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+    e->linearized = e->factorized = e->solved = e->have_hdiag = e->retracted = false;
     S.error = newError; S.lambda = newLambda; S.factor = newFactor;
     S.iterations += 1; S.inner += 1;
     return true;
@@ -1698,7 +1856,20 @@ static bool check_convergence(double rel, double abs_, double errThr, double cur
 // ------------------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------------------
-#define GTB_TRY(e) try {
+// The CUDA current device is per host thread: every entry point makes the engine's device current for its own duration
+// and restores the caller's (an engine may be driven from another thread than the one that created it, or after the
+// caller switched devices).
+struct EngineDeviceGuard {
+  int prev = -1;
+  bool switched = false;
+  explicit EngineDeviceGuard(const gtb_engine* e) {
+    if (!e || !e->has_device) return;
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != e->device) switched = cudaSetDevice(e->device) == cudaSuccess;
+  }
+  ~EngineDeviceGuard() { if (switched && prev >= 0) cudaSetDevice(prev); }
+};
+#define GTB_TRY(e) EngineDeviceGuard _guard(e); try {
 #define GTB_CATCH(e)                                                                         \
   }                                                                                          \
   catch (const StatusError& ex) { (e)->err = ex.what(); return ex.st; }                      \
@@ -1723,18 +1894,26 @@ gtb_status gtb_create(int device, gtb_engine** out) {
       delete e;
       return GTB_ERR_NO_DEVICE;
     }
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&e->ev[0]) != cudaSuccess || cudaEventCreate(&e->ev[1]) != cudaSuccess) {
+    int prev = -1;
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    const bool ok = cudaSetDevice(device) == cudaSuccess && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
+                    cudaEventCreate(&e->ev[0]) == cudaSuccess && cudaEventCreate(&e->ev[1]) == cudaSuccess;
+    if (!ok) {
       delete e;
+      if (prev >= 0) cudaSetDevice(prev);
       return GTB_ERR_CUDA;
     }
     e->has_device = true;
+    if (prev >= 0 && prev != device) cudaSetDevice(prev);
   }
   *out = e;
   return GTB_OK;
 }
 
-void gtb_destroy(gtb_engine* e) { delete e; }
+void gtb_destroy(gtb_engine* e) {
+  EngineDeviceGuard guard(e);
+  delete e;
+}
 const char* gtb_last_error(const gtb_engine* e) { return e ? e->err.c_str() : "null engine"; }
 
 gtb_status gtb_set_variables(gtb_engine* e, int vtype, int64_t n, const uint64_t* keys, const double* state) {
@@ -1928,7 +2107,17 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
           if (want != L.step_count[sidx]) return fail("panel-step task count at level " + std::to_string(l));
           if (L.schur_count[sidx] < want_schur_min || (want_schur_min == 0) != (L.schur_count[sidx] == 0)) return fail("Schur-step task count");
           cnt[1] += L.step_count[sidx] > 0;
-          cnt[2] += L.schur_count[sidx] > 0;
+          {   // the per-rank runs tile the step's Schur tasks
+            int64_t at = L.schur_begin[sidx];
+            if ((int)L.schur_runs.size() != max_np + 1) return fail("Schur run table size");
+            for (const LevelSched::Run& run : L.schur_runs[sidx]) {
+              if (run.begin != at || run.count <= 0) return fail("Schur runs do not tile the step");
+              at += run.count;
+            }
+            if (at != L.schur_begin[sidx] + L.schur_count[sidx]) return fail("Schur runs do not cover the step");
+            if (!e->ordered && L.schur_runs[sidx].size() > 1) return fail("unordered mode with several Schur runs");
+          }
+          cnt[2] += (int64_t)L.schur_runs[sidx].size();
           cnt[7] += L.step_count[sidx] + L.schur_count[sidx];
           for (int64_t t = L.schur_begin[sidx]; t < L.schur_begin[sidx] + L.schur_count[sidx]; ++t) {
             const StepTask& st = e->step_tasks_list[t];
@@ -1967,10 +2156,33 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
         if (sn && sb + sn > (int64_t)e->pair_segs.size()) return fail("segment range");
         for (int64_t k = sb; k < sb + sn; ++k) {
           const PairSeg& sg = e->pair_segs[k];
-          if (sg.count < 1 || sg.begin < 0 || (int64_t)sg.begin + sg.count > nitems || sg.ld < 4 || sg.dst < 0) return fail("segment contents");
+          if (sg.count < 1 || sg.begin < 0 || (int64_t)sg.begin + sg.count > nitems || sg.dst < 0) return fail("segment contents");
+          // ld == 0: a partial block in a scratch slot (ordered hand-over), summed by one of the level's reduce items
+          if (sg.ld == 0 ? (!e->ordered || sg.dst % kPairSlot || sg.dst / kPairSlot >= e->pair_slots) : sg.ld < 4) return fail("segment target");
           (pass ? diag_items_seen : pair_items_seen) += sg.count;
         }
         cnt[pass ? 6 : 5] += sn;
+      }
+      {   // the reduce items of the level cover its scratch slots exactly once
+        std::vector<uint8_t> slot_used;
+        for (int64_t k = L.red_begin; k < L.red_begin + L.n_red; ++k) {
+          const PairReduce& r = e->pair_reduce[k];
+          if (r.count < 2 || r.slot0 < 0 || (int64_t)r.slot0 + r.count > e->pair_slots || r.ld < 4) return fail("pair reduce item");
+          if ((int64_t)slot_used.size() < r.slot0 + r.count) slot_used.resize(r.slot0 + r.count, 0);
+          for (int q = 0; q < r.count; ++q)
+            if (slot_used[r.slot0 + q]++) return fail("scratch slot summed twice");
+        }
+        int64_t partial_segs = 0;
+        for (int pass = 0; pass < 2; ++pass) {
+          const int64_t sb = pass ? L.diag_seg_begin : L.pair_seg_begin, sn = pass ? L.n_diag_seg : L.n_pair_seg;
+          for (int64_t k = sb; k < sb + sn; ++k)
+            if (e->pair_segs[k].ld == 0) {
+              const int64_t slot = e->pair_segs[k].dst / kPairSlot;
+              if (slot >= (int64_t)slot_used.size() || slot_used[slot] != 1) return fail("partial segment without a reduce item");
+              ++partial_segs;
+            }
+        }
+        if (partial_segs != (int64_t)slot_used.size()) return fail("scratch slots without a segment");
       }
     }
   }
@@ -1980,6 +2192,42 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
   }
   for (size_t k = 0; k < rinv_used.size(); ++k)
     if (!rinv_used[k]) return fail("unused inverse block");
+  if (e->ordered) {
+    // ordered extend-add: the work items of a parent tile its columns, every listed child hands over to that parent
+    // through a sorted map that is a permutation of its separator, and no child is gathered twice
+    std::vector<int32_t> gathered(p.n_cliques, 0);
+    for (size_t k = 0; k < e->gather_work.size();) {
+      const GatherWork& w0 = e->gather_work[k];
+      int32_t at = 0;
+      size_t k2 = k;
+      for (; k2 < e->gather_work.size() && e->gather_work[k2].parent == w0.parent && e->gather_work[k2].list_begin == w0.list_begin; ++k2) {
+        const GatherWork& w = e->gather_work[k2];
+        if (w.col_begin != at || w.col_end <= w.col_begin || w.list_end != w0.list_end) return fail("gather work items do not tile the parent");
+        at = w.col_end;
+      }
+      if (at != dim_of(w0.parent)) return fail("gather work items do not cover the parent");
+      for (int32_t q = w0.list_begin; q < w0.list_end; ++q) {
+        const int32_t ch = e->gather_child[q];
+        if (p.parent[ch] != w0.parent || e->is_point[ch]) return fail("gathered child of another parent");
+        gathered[ch]++;
+        const int32_t S1 = p.S[ch] + 1;
+        const int32_t* sm = e->smap.data() + e->gather_smap_off[q];
+        const int32_t* pm = p.pmap.data() + p.pmap_off[ch];
+        for (int32_t v = 0; v < S1; ++v)
+          if ((v && sm[v] <= sm[v - 1]) || sm[S1 + v] < 0 || sm[S1 + v] >= S1 || pm[sm[S1 + v]] != sm[v]) return fail("sorted separator map");
+      }
+      k = k2;
+    }
+    for (int32_t c = 0; c < p.n_cliques; ++c) {
+      const int32_t par = p.parent[c];
+      if (par < 0 || is_small_front(p.F[par], dim_of(par)) || e->is_point[par]) { if (gathered[c]) return fail("gathered child of a small parent"); continue; }
+      // who adds c into its large parent: the pair lists (point), its own Schur step (fuse_up), or the parent's gather
+      const bool here = (e->owner[c] == e->rank && e->owner[par] == e->rank) ||
+                        (e->owner[par] < 0 && (e->owner[c] == e->rank || e->owner[c] < 0));
+      const int want = (here && !e->is_point[c] && !e->fuse_up[c]) ? 1 : 0;
+      if (gathered[c] != want) return fail("clique " + std::to_string(c) + " gathered " + std::to_string(gathered[c]) + " times, expected " + std::to_string(want));
+    }
+  }
   if (e->point_pairs && (pair_items_seen != (int64_t)e->pair_items.size() || diag_items_seen != (int64_t)e->diag_items.size() / 3)) return fail("segments do not cover the item lists");
   cnt[4] = e->rinv_blocks;
   if (out8) std::memcpy(out8, cnt, sizeof(cnt));
@@ -2121,14 +2369,18 @@ gtb_status gtb_retract(gtb_engine* e) {
 }
 gtb_status gtb_error(gtb_engine* e, int which, double* error) {
   if (!e || !error) return GTB_ERR_INVALID;
-  GTB_TRY(e) *error = nonlinear_error(e, which); GTB_CATCH(e)
+  GTB_TRY(e)
+  need(!which || e->retracted, "gtb_error(which = 1) needs gtb_retract first: the scratch copy holds no trial values");
+  *error = nonlinear_error(e, which);
+  GTB_CATCH(e)
 }
 gtb_status gtb_accept(gtb_engine* e) {
   if (!e) return GTB_ERR_INVALID;
   GTB_TRY(e)
   need_device(e);
+  need(e->retracted, "gtb_accept needs gtb_retract since the last gtb_linearize / gtb_accept / gtb_set_variables");
   e->cur ^= 1;
-  e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+  e->linearized = e->factorized = e->solved = e->have_hdiag = e->retracted = false;
   e->lm_have_error = false;
   GTB_CATCH(e)
 }
@@ -2137,6 +2389,7 @@ gtb_status gtb_get_variables(gtb_engine* e, int vtype, int which, double* state)
   GTB_TRY(e)
   need_device(e);
   need(vtype >= 0 && vtype < 4 && state, "bad arguments");
+  need(!which || e->retracted, "gtb_get_variables(which = 1) needs gtb_retract first: the scratch copy holds no trial values");
   const int w = which ? (e->cur ^ 1) : e->cur;
   const size_t n = (size_t)e->vars[vtype].n * kStateDev[vtype];
   if (n) CK(cudaMemcpyAsync(state, e->d_state[w][vtype].p, n * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
@@ -2229,7 +2482,7 @@ gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double rel, do
       retract(e);
       newError = nonlinear_error(e, 1);
       e->cur ^= 1;
-      e->linearized = e->factorized = e->solved = e->have_hdiag = false;
+      e->linearized = e->factorized = e->solved = e->have_hdiag = e->retracted = false;
       ++it;
     } while (it < max_iterations && !check_convergence(rel, abs_, 0.0, currentError, newError) && std::isfinite(currentError));
     err = newError;
@@ -2278,6 +2531,7 @@ gtb_status gtb_profile_read(gtb_engine* e, double* total_ms, int64_t* launches) 
 }
 int64_t gtb_profile_read_raw(gtb_engine* e, int32_t* klass, float* ms, int64_t cap) {
   if (!e || !e->has_device) return -1;
+  EngineDeviceGuard guard(e);
   cudaStreamSynchronize(e->stream);
   const int64_t n = std::min<int64_t>((int64_t)e->prof_class.size(), cap);
   for (int64_t i = 0; i < n; ++i) {
@@ -2290,6 +2544,7 @@ int64_t gtb_profile_read_raw(gtb_engine* e, int32_t* klass, float* ms, int64_t c
 }
 void gtb_debug_read(gtb_engine* e, long long* out8) {
   if (!e || !e->has_device) return;
+  EngineDeviceGuard guard(e);
   cudaStreamSynchronize(e->stream);
   cudaMemcpy(out8, e->d_dbg.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost);
 }

@@ -12,6 +12,9 @@
 //     mode=linearize | solve | lm | gn | time | symbolic | ordering
 //     ordering=colamd|metis|schur|natural|file   (file: array "ordering" in problem)
 //     lambda=<double> diag=0|1                    (solve: LM damping, 0 => none)
+//     tree=0                                      (solve: skip the clique layout, [R S d] and new values: full-size runs)
+//     ld=2 ldsweeps=<k>                           (solve: delta_star by long-double iterative refinement; any size)
+//     ld=1 ldmax=<n>                              (solve: also delta_star, the same damped system solved in long double)
 //     ceres=0|1 maxiter=<n> lambda0=<d>           (lm)
 //     iters=<n>                                   (time)
 //   ref_tool <city10000 file> <out.gtb> mode=isam2 loops=<n> every=<k>
@@ -27,6 +30,7 @@
 #include <gtsam/inference/Symbol.h>
 #include <gtsam/linear/GaussianBayesTree.h>
 #include <gtsam/linear/GaussianFactorGraph.h>
+#include <gtsam/linear/HessianFactor.h>
 #include <gtsam/linear/JacobianFactor.h>
 #include <gtsam/linear/NoiseModel.h>
 #include <gtsam/linear/VectorValues.h>
@@ -328,6 +332,135 @@ static GaussianFactorGraph damp(const GaussianFactorGraph& gfg, const Values& va
   return st.buildDampedSystem(gfg, sq);
 }
 
+// Extended-precision arbiter for the linear solve (mode=solve ld=1): the SAME damped system the reference eliminates
+// (whitened [A | b] of every factor of `sys`, taken from the reference's own JacobianFactor::augmentedJacobian), solved
+// through dense normal equations H = A^T A, g = A^T b with every sum, the Cholesky factorisation and both triangular
+// solves in 80-bit long double (unit round-off 5.4e-20, 2048 times finer than FP64).  The result delta* is what both the
+// reference's delta and the device's delta are measured against: "the device is no further from the exact solution than
+// the reference" is then a statement about two numbers, not about an input-perturbation yardstick.  Dense and O(n^3):
+// meant for the golden fixtures (n <= ~7k scalars), skipped above `ldmax` scalars.
+static bool solve_long_double(const GaussianFactorGraph& sys, const VectorValues& like, std::vector<double>& out) {
+  std::vector<uint64_t> keys;
+  for (const auto& kv : like) keys.push_back(kv.first);
+  std::sort(keys.begin(), keys.end());
+  std::map<Key, size_t> off;
+  size_t n = 0;
+  for (Key k : keys) { off[k] = n; n += like.at(k).size(); }
+  if ((double)n > optd("ldmax", 8000)) return false;
+  typedef long double LD;
+  std::vector<LD> H(n * n, 0.0L), g(n, 0.0L);   // row-major, lower triangle used
+  for (const auto& f : sys) {
+    if (!f) continue;
+    auto jf = std::dynamic_pointer_cast<JacobianFactor>(f);
+    if (!jf) throw std::runtime_error("solve_long_double: not a JacobianFactor");
+    const Matrix Ab = jf->augmentedJacobian();   // whitened
+    std::vector<size_t> col;
+    for (auto it = jf->begin(); it != jf->end(); ++it)
+      for (size_t d = 0; d < (size_t)jf->getDim(it); ++d) col.push_back(off.at(*it) + d);
+    const size_t w = col.size();
+    for (int r = 0; r < Ab.rows(); ++r)
+      for (size_t a = 0; a < w; ++a) {
+        const LD va = (LD)Ab(r, a);
+        g[col[a]] += va * (LD)Ab(r, w);
+        for (size_t b2 = 0; b2 < w; ++b2)
+          if (col[b2] <= col[a]) H[col[a] * n + col[b2]] += va * (LD)Ab(r, b2);
+      }
+  }
+  // Cholesky-Banachiewicz, H = L L^T, rows contiguous
+  for (size_t i = 0; i < n; ++i) {
+    LD* Li = &H[i * n];
+    for (size_t j = 0; j <= i; ++j) {
+      const LD* Lj = &H[j * n];
+      LD s = Li[j];
+      for (size_t k = 0; k < j; ++k) s -= Li[k] * Lj[k];
+      if (j < i) Li[j] = s / Lj[j];
+      else {
+        if (!(s > 0)) return false;
+        Li[i] = sqrtl(s);
+      }
+    }
+  }
+  for (size_t i = 0; i < n; ++i) {   // L y = g
+    LD s = g[i];
+    for (size_t k = 0; k < i; ++k) s -= H[i * n + k] * g[k];
+    g[i] = s / H[i * n + i];
+  }
+  for (size_t ii = n; ii-- > 0;) {   // L^T x = y
+    LD s = g[ii];
+    for (size_t k = ii + 1; k < n; ++k) s -= H[k * n + ii] * g[k];
+    g[ii] = s / H[ii * n + ii];
+  }
+  out.resize(n);
+  for (size_t i = 0; i < n; ++i) out[i] = (double)g[i];
+  return true;
+}
+
+// The same arbiter at sizes where dense normal equations do not fit (mode=solve ld=2): iterative refinement of the
+// reference's own delta.  Each sweep forms the gradient residual rho = A^T (b - A x) of the damped system factor by factor
+// in long double (the entries of A and b are the reference's own doubles, exact), and solves H d = rho with the
+// reference's own multifrontal Cholesky on the same ordering: the factors keep their A with b = 0, and rho enters as
+// one HessianFactor(key, G = 0, g = rho_key, f = 0) per variable.  x += d in long double.  The double-precision solve
+// contracts the error by cond * 1e-16 per sweep, so three or four sweeps reach the long-double solution; the sweep
+// corrections' norms are returned so that the caller sees the convergence.
+static bool refine_long_double(const GaussianFactorGraph& sys, const Ordering& ord, const VectorValues& delta,
+                               std::vector<double>& out, std::vector<double>& steps) {
+  std::vector<uint64_t> keys;
+  for (const auto& kv : delta) keys.push_back(kv.first);
+  std::sort(keys.begin(), keys.end());
+  std::map<Key, size_t> off;
+  std::vector<size_t> dims;
+  size_t n = 0;
+  for (Key k : keys) { off[k] = n; dims.push_back(delta.at(k).size()); n += delta.at(k).size(); }
+  typedef long double LD;
+  std::vector<LD> x(n);
+  for (size_t i = 0; i < keys.size(); ++i)
+    for (size_t d = 0; d < dims[i]; ++d) x[off[keys[i]] + d] = (LD)delta.at(keys[i])(d);
+  GaussianFactorGraph zero_b;
+  for (const auto& f : sys) {
+    auto jf = std::dynamic_pointer_cast<JacobianFactor>(f);
+    if (!jf) throw std::runtime_error("refine_long_double: not a JacobianFactor");
+    auto copy = std::make_shared<JacobianFactor>(*jf);
+    copy->getb().setZero();
+    zero_b.push_back(copy);
+  }
+  const int sweeps = (int)optd("ldsweeps", 4);
+  for (int it = 0; it < sweeps; ++it) {
+    std::vector<LD> rho(n, 0.0L);
+    for (const auto& f : sys) {
+      auto jf = std::static_pointer_cast<JacobianFactor>(f);
+      const Matrix Ab = jf->augmentedJacobian();
+      std::vector<size_t> col;
+      for (auto kit = jf->begin(); kit != jf->end(); ++kit)
+        for (size_t d = 0; d < (size_t)jf->getDim(kit); ++d) col.push_back(off.at(*kit) + d);
+      const size_t w = col.size();
+      for (int r = 0; r < Ab.rows(); ++r) {
+        LD res = (LD)Ab(r, w);
+        for (size_t a = 0; a < w; ++a) res -= (LD)Ab(r, a) * x[col[a]];
+        for (size_t a = 0; a < w; ++a) rho[col[a]] += (LD)Ab(r, a) * res;
+      }
+    }
+    GaussianFactorGraph g2 = zero_b;
+    for (size_t i = 0; i < keys.size(); ++i) {
+      Vector gv(dims[i]);
+      for (size_t d = 0; d < dims[i]; ++d) gv(d) = (double)rho[off[keys[i]] + d];
+      g2.emplace_shared<HessianFactor>(keys[i], Matrix::Zero(dims[i], dims[i]), gv, 0.0);
+    }
+    const VectorValues d = g2.eliminateMultifrontal(ord)->optimize();
+    LD dn = 0, xn = 0;
+    for (size_t i = 0; i < keys.size(); ++i)
+      for (size_t q = 0; q < dims[i]; ++q) {
+        const LD dv = (LD)d.at(keys[i])(q);
+        x[off[keys[i]] + q] += dv;
+        dn += dv * dv;
+      }
+    for (size_t i = 0; i < n; ++i) xn += x[i] * x[i];
+    steps.push_back((double)(sqrtl(dn) / sqrtl(xn)));
+  }
+  out.resize(n);
+  for (size_t i = 0; i < n; ++i) out[i] = (double)x[i];
+  return true;
+}
+
 // mode=isam2: argv[1] is a City10000-format file: "EDGE2 <from> <n> <to> <n> <hypotheses> {x y theta}...".  Schedule and
 // parameters follow examples/ISAM2_City10000.cpp:62-134 (no ambiguity: the first hypothesis of every line): prior
 // 1e-4 on pose 0 and one update; then one update per line -- an odometry line (to = from + 1) adds the new pose,
@@ -560,7 +693,7 @@ int main(int argc, char** argv) {
       bool failed = false;
       try {
         auto bt = sys.eliminateMultifrontal(ord);
-        dump_bayes_tree(*bt, out, mode == "solve");
+        if (optd("tree", 1) != 0) dump_bayes_tree(*bt, out, mode == "solve");   // tree=0: full-size runs keep delta and errors only
         if (mode == "solve") {
           VectorValues delta = bt->optimize();
           dump_delta(delta, out);
@@ -568,7 +701,18 @@ int main(int argc, char** argv) {
           out.put_f64("linear_error1", {gfg->error(delta)});
           Values nv = B.values.retract(delta);
           out.put_f64("error1", {B.graph.error(nv)});
-          dump_values(nv, out, "new_");
+          if (optd("tree", 1) != 0) dump_values(nv, out, "new_");
+          if (optd("ld", 0) == 1) {
+            std::vector<double> star;
+            if (solve_long_double(sys, delta, star)) out.put_f64("delta_star", star);
+          }
+          if (optd("ld", 0) == 2 || optd("ld2", 0) != 0) {
+            std::vector<double> star, steps;
+            if (refine_long_double(sys, ord, delta, star, steps)) {
+              out.put_f64(optd("ld", 0) == 2 ? "delta_star" : "delta_star_refined", star);
+              out.put_f64("delta_star_sweeps", steps);
+            }
+          }
         }
       } catch (const IndeterminantLinearSystemException& e) {
         failed = true;

@@ -79,6 +79,8 @@ def main():
         pfiles[name] = os.path.join(tmp, name + ".gtb")
         p.save(pfiles[name])
         digests[name] = problem_digest(p)
+        if "--solves-only" in sys.argv:
+            continue
         lin = run_tool(pfiles[name], ["mode=linearize"])
         np.savez_compressed(os.path.join(OUT, f"{name}__linearize.npz"), digest=digests[name], **lin)
         print(name, "linearize", {k: v.shape for k, v in lin.items()})
@@ -95,14 +97,23 @@ def main():
         q.save(ulp_files[name])
     for name, ordering, lam, diag in SOLVES:
         args = ["mode=solve", f"ordering={ordering}", f"lambda={lam!r}", f"diag={diag}"]
-        o = run_tool(pfiles[name], args)
+        # ld=1: also delta_star, the same damped system solved in 80-bit long double (the arbiter both the reference's
+        # and the device's delta are measured against, oracle/ref_tool.cpp solve_long_double)
+        # delta_star: by long-double iterative refinement on the reference's own factorisation (ld2=1: converges to ~1e-16, any
+        # size); delta_star_dense: dense long-double normal equations (ld=1: independent check, resolution cond * 5e-20)
+        o = run_tool(pfiles[name], args + ["ld=1", "ld2=1"])
         if "delta" in o:
+            o["delta_star_dense"] = o.pop("delta_star")
+            o["delta_star"] = o.pop("delta_star_refined")
+            o["delta_ref_vs_star"] = np.array([np.linalg.norm(o["delta"] - o["delta_star"]) / np.linalg.norm(o["delta_star"])])
             o2 = run_tool(ulp_files[name], args)
             o["delta_ulp_sensitivity"] = np.array([np.linalg.norm(o2["delta"] - o["delta"]) / np.linalg.norm(o["delta"])])
         tag = f"{name}__solve_{ordering}_{lam:g}_{diag}"
         np.savez_compressed(os.path.join(OUT, tag + ".npz"), digest=digests[name], lam=lam, diag=diag, **o)
         print(tag, "cliques", len(o.get("clique_nfrontal", [])), "failed", int(o["failed"][0]), "ulp sensitivity",
-              float(o.get("delta_ulp_sensitivity", [0])[0]))
+              float(o.get("delta_ulp_sensitivity", [0])[0]), "|delta_ref - delta*| / |delta*|", float(o.get("delta_ref_vs_star", [0])[0]))
+    if "--solves-only" in sys.argv:
+        return
     for name, mode, ordering, extra in RUNS:
         o = run_tool(pfiles[name], [f"mode={mode}", f"ordering={ordering}"] + extra)
         tag = f"{name}__{mode}_{ordering}" + ("_ceres" if "ceres=1" in extra else "")

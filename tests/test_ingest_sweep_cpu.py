@@ -13,13 +13,14 @@ from test_ingest_cpu import compare_with_reference
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DATA = "/root/reference/examples/Data"
 TOOL = os.path.join(ROOT, "oracle", "_ref", "ref_tool")
-FILES = [("pose2example-rewritten.txt", "g2o2"), ("optimizedNoisyToyGraph.txt", "g2o2"), ("orientationsNoisyToyGraph.txt", "g2o2"),
+# (only files the reference SHIPS: "*-rewritten.txt" by-products of the reference's own testDataset are not inputs)
+FILES = [("optimizedNoisyToyGraph.txt", "g2o2"), ("orientationsNoisyToyGraph.txt", "g2o2"),
          ("w20000.txt", "g2o2"),
          ("Klaus3.g2o", "g2o3"), ("toyExample.g2o", "g2o3"), ("pose3Localizationexample.txt", "g2o3"),
-         ("pose3example-grid.txt", "g2o3"), ("pose3example-rewritten.txt", "g2o3"),
+         ("pose3example-grid.txt", "g2o3"),
          ("pose3example-offdiagonal-rewritten.txt", "g2o3"), ("simpleGraph10gradIter.txt", "g2o3"),
          ("sphere2500.txt", "g2o3"), ("sphere2500_groundtruth.txt", "g2o3"),
-         ("dubrovnik-3-7-18-pre.txt", "bal"), ("dubrovnik-3-7-pre-rewritten.txt", "bal"), ("dubrovnik-1-1-pre.txt", "bal")]
+         ("dubrovnik-3-7-18-pre.txt", "bal"), ("dubrovnik-1-1-pre.txt", "bal")]
 
 pytestmark = pytest.mark.skipif(not (os.path.isdir(DATA) and os.path.exists(TOOL)),
                                 reason="needs the reference's data directory and the oracle build (this container only)")

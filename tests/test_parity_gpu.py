@@ -6,7 +6,7 @@ All calls go through the C ABI (ctypes); there is no CPU path to fall back on.""
 import numpy as np
 import pytest
 
-from conftest import golden_problem, load_golden, run_tags, solve_tags
+from conftest import check_delta, golden_problem, load_golden, run_tags, solve_tags
 from gtsam_petercdev_b200.engine import Engine, IndeterminantLinearSystemException
 from gtsam_petercdev_b200.problem import BUCKETS, VTYPES
 
@@ -70,9 +70,9 @@ def test_solve_matches_reference(name, ordering, lam, diag, tag):
     e.backsolve()
     d = e.delta()
     assert np.array_equal(g["delta_keys"], e.var_keys)
-    # 1e-9 relative (north_star), or three times the reference's own sensitivity to a one-ulp change of its inputs
-    # where the system is too ill-conditioned for 1e-9 to mean anything (recorded with the fixture)
-    assert rel(d, g["delta"]) < max(1e-9, 3 * float(g["delta_ulp_sensitivity"][0]))
+    # north_star: delta within 1e-9 relative of the reference's; where the system is too ill-conditioned for two FP64
+    # factorisations to agree that closely, the extended-precision arbiter decides (conftest.check_delta)
+    check_delta(tag, d, g["delta"], g["delta_star"], f"   [R S d] worst clique = {worst:.3e}")
     e0, e1 = e.linear_errors()
     assert abs(e0 - g["linear_error0"][0]) <= 1e-12 * g["linear_error0"][0]
     assert abs(e1 - g["linear_error1"][0]) <= 1e-8 * g["linear_error0"][0]
@@ -151,3 +151,37 @@ def test_bal_known_answer():
     assert abs(r["final_error"] - 0.0199833) < 1e-5
     assert abs(r["final_error"] - g["final_error"][0]) <= 1e-6 * g["final_error"][0]
     assert r["iterations"] == int(g["iterations"][0])
+
+
+def test_engine_driven_from_another_thread_and_call_order_is_enforced():
+    """the CUDA current device is per host thread, so every entry point binds the engine's device itself; and
+    gtb_accept / reads of the trial values need a gtb_retract since the last linearize / accept."""
+    import threading
+    from gtsam_petercdev_b200.engine import EngineError
+    g = load_golden("pose3_120__lm_metis")
+    e = Engine(golden_problem("pose3_120"), device=0)
+    e.set_ordering(g["ordering"])
+    with pytest.raises(EngineError):
+        e.accept()                       # nothing retracted yet
+    with pytest.raises(EngineError):
+        e.error(1)
+    out = {}
+
+    def work():
+        try:
+            out["r"] = e.lm_optimize()
+        except Exception as ex:          # noqa: BLE001
+            out["ex"] = ex
+    t = threading.Thread(target=work)
+    t.start()
+    t.join()
+    assert "ex" not in out, out.get("ex")
+    assert out["r"]["iterations"] == int(g["iterations"][0])
+    assert abs(out["r"]["final_error"] - g["final_error"][0]) <= 1e-6 * g["final_error"][0]
+    e.linearize()
+    e.factorize(1e-3)
+    e.backsolve()
+    e.retract()
+    e.accept()
+    with pytest.raises(EngineError):
+        e.accept()                       # the trial was consumed
