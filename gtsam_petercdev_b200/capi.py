@@ -57,6 +57,7 @@ _SIGS = {
     "gtb_lm_optimize": (C.c_int, [_P, C.POINTER(LMParams), C.POINTER(LMResult), _P, C.c_int64]),
     "gtb_lm_iterate": (C.c_int, [_P, C.POINTER(LMParams), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                  C.POINTER(C.c_double), C.POINTER(C.c_int32)]),
+    "gtb_lm_last_accepted": (C.c_int, [_P]),
     "gtb_gn_optimize": (C.c_int, [_P, C.c_int32, C.c_double, C.c_double, C.POINTER(LMResult)]),
     "gtb_kernel_launches": (C.c_int64, [_P]),
     "gtb_stage_ms": (C.c_int, [_P, _P]),

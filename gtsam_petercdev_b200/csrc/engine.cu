@@ -240,6 +240,7 @@ struct gtb_engine {
   // LM state across gtb_lm_iterate calls
   bool lm_have_error = false;
   double lm_error = 0;
+  int lm_last_accepted = 0;   // the last gtb_lm_iterate ended with an accepted step
 
   ~gtb_engine() {
     if (h_scalars) cudaFreeHost(h_scalars);
@@ -2453,9 +2454,12 @@ gtb_status gtb_lm_iterate(gtb_engine* e, const gtb_lm_params* p, double* lambda_
   lm_iterate(e, *p, S, nullptr);
   *lambda_io = S.lambda; *factor_io = S.factor; *error_io = S.error;
   if (inner) *inner = S.inner - 1;
+  e->lm_last_accepted = S.iterations > 0 ? 1 : 0;
   e->lm_error = S.error; e->lm_have_error = true;
   GTB_CATCH(e)
 }
+
+int gtb_lm_last_accepted(const gtb_engine* e) { return e ? e->lm_last_accepted : 0; }
 
 gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double rel, double abs_, gtb_lm_result* result) {
   if (!e || !result) return GTB_ERR_INVALID;

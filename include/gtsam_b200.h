@@ -169,6 +169,9 @@ gtb_status gtb_lm_optimize(gtb_engine* e, const gtb_lm_params* p, gtb_lm_result*
  * engine between calls; lambda is in/out.                                                                */
 gtb_status gtb_lm_iterate(gtb_engine* e, const gtb_lm_params* p, double* lambda_io, double* lambda_factor_io,
                           double* error_io, int32_t* inner_iterations);
+/* 1 when the last gtb_lm_iterate ended with an accepted step (LevenbergMarquardtState::decreaseLambda: the reference's
+ * iteration counter moves only then, nonlinear/internal/LevenbergMarquardtState.h:81-94), 0 when the lambda search gave up. */
+int gtb_lm_last_accepted(const gtb_engine* e);
 /* GaussNewtonOptimizer::optimize() (nonlinear/GaussNewtonOptimizer.cpp:44-66).                          */
 gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double relative_error_tol,
                            double absolute_error_tol, gtb_lm_result* result);
