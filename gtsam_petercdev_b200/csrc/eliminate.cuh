@@ -1140,68 +1140,6 @@ __host__ __device__ __forceinline__ int schur_task(int tile, int slice, int nspl
   return tile | (slice << kSchurTileBits) | (nsplit << (kSchurTileBits + kSchurSliceBits));
 }
 
-// One warp: Cholesky (upper) of the 32 x 32 block Dh[i * LDP + l] = D(l, i) held in shared memory, in registers with
-// lane = column; rows / columns beyond the front are identity padding.  Also leaves 1 / R(i, i) in dinv_h and the inverses
-// of the four 8 x 8 diagonal blocks in Ws_h[i * 12 + r].  Returns false on a non-positive pivot (Eigen LLT
-// NumericalIssue, base/cholesky.cpp:126-128).  Not inlined: the unrolled body is ~4.5k instructions and is used twice.
-__device__ __noinline__ bool potrf32_warp(double* Dh, double* dinv_h, double* Ws_h, double* rowbuf, int lane) {
-  bool okw = true;
-  double d[NB];
-#pragma unroll
-  for (int i = 0; i < NB; ++i) d[i] = Dh[lane * LDP + i];
-  double myinv = 1.0;
-  // software-pipelined: the next pivot column is updated first so that its rsqrt overlaps the rest of the rank-1 update.
-  // No predication on the triangle: entries below the diagonal of a column (i > lane) and rows above the pivot hold
-  // garbage that is never read, which removes ~500 compare instructions from a body that is instruction-fetch-bound.
-  // The scaled pivot row is broadcast through shared memory (one LDS per use instead of two shuffles), double-buffered.
-  double pk = __shfl_sync(0xffffffffu, d[0], 0);
-  double rinv = rsqrt(pk);
-#pragma unroll
-  for (int k = 0; k < NB; ++k) {
-    double* rb = rowbuf + (k & 1) * NB;
-    okw = okw && (pk > 0.0);
-    d[k] *= rinv;                       // lane == k: pk * rinv = sqrt(pk); lanes < k: unused
-    if (lane == k) myinv = rinv;
-    const double ukl = d[k];
-    // The next pivot D(k+1, k+1) - R(k, k+1)^2 lives entirely in lane k+1 (its own ukl IS R(k, k+1)): the dependent chain
-    // pivot -> rsqrt -> scale -> update -> shuffle never goes through the shared-memory row broadcast, which only feeds
-    // the rest of the rank-1 update.  (A 4-pass body rotated through registers to fit the instruction cache measured
-    // 15 % slower: the chain, not instruction fetch, sets the time.)
-    double pk_next = 1.0, rinv_next = 1.0;
-    if (k + 1 < NB) {
-      pk_next = __shfl_sync(0xffffffffu, d[k + 1] - ukl * ukl, k + 1);
-      rinv_next = rsqrt(pk_next);
-    }
-    rb[lane] = ukl;
-    __syncwarp();
-    if (k + 1 < NB) d[k + 1] -= rb[k + 1] * ukl;
-#pragma unroll
-    for (int i = k + 2; i < NB; ++i) d[i] -= rb[i] * ukl;
-    pk = pk_next;
-    rinv = rinv_next;
-  }
-#pragma unroll
-  for (int i = 0; i < NB; ++i)
-    if (i <= lane) Dh[lane * LDP + i] = d[i];
-  dinv_h[lane] = myinv;
-  __syncwarp();
-  // inverses of the four 8 x 8 diagonal blocks: lane = column, back-substitution within its block
-  const int b8 = lane & ~7, jj = lane & 7;
-  double w[8];
-#pragma unroll
-  for (int i = 7; i >= 0; --i) {
-    double sacc = 0.0;
-#pragma unroll
-    for (int k = i + 1; k < 8; ++k)
-      if (k <= jj) sacc += Dh[(b8 + k) * LDP + b8 + i] * w[k];
-    w[i] = (i == jj) ? myinv : ((i < jj) ? -sacc * dinv_h[b8 + i] : 0.0);
-  }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) Ws_h[lane * 12 + i] = w[i];
-  __syncwarp();
-  return okw;
-}
-
 // Blocked forward substitution Y = R^-T X on NT*8 columns held as X[c * LDP + i] (i = row), one warp, stages
 // [b_begin, b_end) of 8 rows each.  R is the upper factor in Ds (Ds[i * LDP + l] = R(l, i)); Ws holds the inverses of
 // its 8 x 8 diagonal blocks (Ws[i * 12 + r] = inv(R_bb)(r, i % 8)).  Rows of earlier stages must already be solved.
@@ -1399,47 +1337,105 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
       for (int e = 0; e < 2; ++e) Xs[(2 * t + e) * LDP + mt * 8 + g] = b0[mt][e] - acc[mt][e];
     if (warp == 1) stamp(8);
   }
-  if (warp == 0) {
+  {
+    // Cooperative 64 x 64 Cholesky in 8 x 8 blocks, right-looking (replaces two 32 x 32 in-register Choleskys in warp 0 with a
+    // 32 x 32 triangular solve between them: 22.5 k -> 20.6 k cycles in the in-kernel stamps, panel step 26.5 -> 23.6 us).
+    // The dependent chain of a block -- 8 pivots -- runs in warp 0 with the whole 8 x 8 block held REDUNDANTLY in the
+    // registers of every lane: pivot -> rsqrt -> scale -> update never leaves the register file (no shuffle, no
+    // shared-memory broadcast).  Everything else is spread over the CTA: the row block is solved one thread per column
+    // (column-oriented forward substitution with the 8 x 8 factor read by broadcast), the trailing 8-column tiles are
+    // updated on the FP64 tensor pipe (rank 8: two DMMAs per tile) by all warps.  Warp 0 owns the next diagonal tile, so
+    // the next block's chain starts after a warp-level sync; two CTA barriers per block.
+    // (Tried on the box and dropped: bringing D up to date with panel p-1 row block by row block inside this loop and
+    // slicing the column warps' look-ahead into it -- same 2.89 ms per step, the helpers then set the pace of a block;
+    // four tile pairs at a time per warp with warp 0 keeping only the next diagonal tile -- 3.08 ms.)
+    const int nb8 = (kb + 7) >> 3;
     bool okw = true;
-    const int nh = kb > NB ? 2 : 1;
-#pragma unroll 1
-    for (int h = 0; h < nh; ++h) {
-      okw = potrf32_warp(Ds + h * NB * LDP + h * NB, dinv + h * NB, Ws + h * NB * 12, T0, lane);
-      stamp(3 + 2 * h);
-      if (!okw) break;
-      if (h == 0 && nh == 2) {
-        // off-diagonal block T = D00^-T D01 (columns 32..63, rows 0..31), then D11 -= T^T T on its 10 upper tile pairs
-        trsm_stages<4, 4>(Ds, Ws, Ds + NB * LDP, T0, 4, g, t);
-        double acc[10][2];
+    for (int b = 0; b < nb8; ++b) {
+      const int o = 8 * b;
+      if (warp == 0) {
+        double a[8][8];
 #pragma unroll
-        for (int q = 0; q < 10; ++q) acc[q][0] = acc[q][1] = 0.0;
-#pragma unroll 2
-        for (int ks = 0; ks < NB; ks += 4) {
-          double f[4];
+        for (int cc = 0; cc < 8; ++cc)
 #pragma unroll
-          for (int a = 0; a < 4; ++a) f[a] = Ds[(NB + a * 8 + g) * LDP + ks + t];
-          int q = 0;
+          for (int r = 0; r <= cc; ++r) a[r][cc] = Ds[(o + cc) * LDP + o + r];
+        double rv[8];
 #pragma unroll
-          for (int mt = 0; mt < 4; ++mt)
+        for (int k = 0; k < 8; ++k) {
+          const double piv = a[k][k];
+          okw = okw && (piv > 0.0);   // Eigen LLT: NumericalIssue on a non-positive pivot (base/cholesky.cpp:126-128)
+          const double rinv = rsqrt(piv);
+          rv[k] = rinv;
+          a[k][k] = piv * rinv;
 #pragma unroll
-            for (int nt = mt; nt < 4; ++nt, ++q) dmma884(acc[q][0], acc[q][1], f[mt], f[nt]);
+          for (int cc = k + 1; cc < 8; ++cc) a[k][cc] *= rinv;
+#pragma unroll
+          for (int r = k + 1; r < 8; ++r)
+#pragma unroll
+            for (int cc = r; cc < 8; ++cc) a[r][cc] -= a[k][r] * a[k][cc];
         }
-        int q = 0;
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt)
+        for (int cc = 0; cc < 8; ++cc)
 #pragma unroll
-          for (int nt = mt; nt < 4; ++nt, ++q)
+          for (int r = 0; r <= cc; ++r) Ds[(o + cc) * LDP + o + r] = a[r][cc];   // every lane writes the same values
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int i = mt * 8 + g, jj = nt * 8 + 2 * t + e;
-              if (i <= jj && NB + jj < kb) Ds[(NB + jj) * LDP + NB + i] -= acc[q][e];
-            }
-        __syncwarp();
-        stamp(4);
+        for (int k = 0; k < 8; ++k) dinv[o + k] = rv[k];
+        if (b == 0) stamp(3);
       }
+      __syncthreads();   // R_bb and its reciprocal diagonal are published; the updates of block b - 1 are complete
+      const int ncol = 8 * nb8 - (o + 8);
+      if (tid < ncol) {   // row block b, one column per thread: u = R_bb^-T x
+        double* col = Ds + (o + 8 + tid) * LDP + o;
+        double x[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[r] = col[r];
+#pragma unroll
+        for (int l = 0; l < 8; ++l) {
+          x[l] *= dinv[o + l];
+#pragma unroll
+          for (int r = l + 1; r < 8; ++r) x[r] -= Ds[(o + r) * LDP + o + l] * x[l];
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) col[r] = x[r];
+      }
+      __syncthreads();
+      // trailing tiles (mt, nt), b < mt <= nt < nb8: C -= U(:, mt)^T U(:, nt), pair 0 = the next diagonal tile (warp 0)
+      const int m = nb8 - 1 - b, npair = (m * (m + 1)) >> 1;
+      for (int q = warp; q < npair; q += 8) {
+        int idx = q, mt = 0;
+        while (idx >= m - mt) { idx -= m - mt; ++mt; }
+        const int ct = b + 1 + mt + idx, rt = b + 1 + mt;
+        double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+        for (int ks = 0; ks < 8; ks += 4) dmma884(c0, c1, Ds[(8 * rt + g) * LDP + o + ks + t], Ds[(8 * ct + g) * LDP + o + ks + t]);
+        Ds[(8 * ct + 2 * t) * LDP + 8 * rt + g] -= c0;
+        Ds[(8 * ct + 2 * t + 1) * LDP + 8 * rt + g] -= c1;
+      }
+      if (warp == 0) __syncwarp();
     }
-    if (lane == 0) *s_ok = okw ? 1 : 0;
-    if (task == 0 && !okw && lane == 0) atomicMin(E.fail, c);
+    __syncthreads();
+    if (lane < 8 && warp < nb8) {
+      // inverses of the 8 x 8 diagonal blocks for the blocked solve below: one block per warp, one column per lane,
+      // back-substitution within the block
+      const int b8 = warp * 8, jj = lane, cidx = b8 + jj;
+      const double myinv = dinv[cidx];
+      double w[8];
+#pragma unroll
+      for (int i = 7; i >= 0; --i) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int k = i + 1; k < 8; ++k)
+          if (k <= jj) sacc += Ds[(b8 + k) * LDP + b8 + i] * w[k];
+        w[i] = (i == jj) ? myinv : ((i < jj) ? -sacc * dinv[b8 + i] : 0.0);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) Ws[cidx * 12 + i] = w[i];
+    }
+    if (warp == 0) {
+      stamp(5);
+      if (lane == 0) *s_ok = okw ? 1 : 0;
+      if (task == 0 && !okw && lane == 0) atomicMin(E.fail, c);
+    }
   }
   __syncthreads();
   if (!*s_ok) return;
