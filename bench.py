@@ -208,12 +208,11 @@ def main():
     lam = args.lam
 
     def step():
+        # one LM trial = linearize + what tryLambda does (LevenbergMarquardtOptimizer.cpp:121-270): damped multifrontal
+        # Cholesky, back-substitution, both linear errors, retract, nonlinear error; gtb_trial enqueues them back to back
+        # and synchronises once (the three scalars and the failure flag come back together)
         e.linearize()
-        e.factorize(lam)
-        e.backsolve()
-        e0, e1 = e.linear_errors()
-        e.retract()
-        return e.error(1)
+        return e.trial(lam)[2]
 
     cam, pt = p.a.get("cam"), p.a.get("point")
     host_state = [(t, np.ascontiguousarray(p.a[n])) for t, n in enumerate(["pose2", "pose3", "cam", "point"]) if n in p.a]

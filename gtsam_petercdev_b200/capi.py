@@ -45,6 +45,7 @@ _SIGS = {
     "gtb_hessian_diagonal": (C.c_int, [_P, _P]),
     "gtb_factorize": (C.c_int, [_P, C.c_double, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_uint64)]),
     "gtb_backsolve": (C.c_int, [_P]),
+    "gtb_trial": (C.c_int, [_P, C.c_double, C.c_int, C.c_double, C.c_double, _P, C.POINTER(C.c_uint64)]),
     "gtb_get_delta": (C.c_int, [_P, _P]),
     "gtb_get_conditionals": (C.c_int, [_P, _P]),
     "gtb_linear_errors": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

@@ -1413,14 +1413,16 @@ template <int B> static void launch_error(Engine* e, int which) {
   const double* s1 = T::T1 >= 0 ? e->d_state[which][T::T1 >= 0 ? T::T1 : 0].p : nullptr;
   LAUNCH(e, K_ERROR, error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(bk, s0, s1, e->d_partials.p + e->partial_off[B]));
 }
-static double nonlinear_error(Engine* e, int which) {
+// slot >= 0: the sum goes to d_scalars[slot] and nothing is read back (the caller syncs once for several results)
+static double nonlinear_error(Engine* e, int which, int slot = -1) {
   need_device(e);
   need(e->finalized, "problem not finalized");
   StageTimer tm(e, 5);
   const int w = which ? (e->cur ^ 1) : e->cur;
   launch_error<0>(e, w); launch_error<1>(e, w); launch_error<2>(e, w); launch_error<3>(e, w);
   launch_error<4>(e, w); launch_error<5>(e, w); launch_error<6>(e, w);
-  LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p));
+  LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p + (slot >= 0 ? slot : 0)));
+  if (slot >= 0) { tm.stop(); return 0.0; }
   CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
   tm.stop();
@@ -1434,6 +1436,7 @@ template <int B> static void launch_linear_error(Engine* e) {
   LAUNCH(e, K_LINERR, linear_error_kernel<B><<<grid, kFactorThreads, 0, e->stream>>>(
       bk, e->d_delta.p, e->d_partials.p + e->partial_off[B], e->d_partials.p + e->n_partials + e->partial_off[B]));
 }
+// e0 == nullptr: the two sums stay in d_scalars[0], [1] and nothing is read back
 static void linear_errors(Engine* e, double* e0, double* e1) {
   need_device(e);
   need(e->linearized && e->solved, "gtb_linear_errors needs gtb_linearize and gtb_backsolve first");
@@ -1442,6 +1445,7 @@ static void linear_errors(Engine* e, double* e0, double* e1) {
   launch_linear_error<4>(e); launch_linear_error<5>(e); launch_linear_error<6>(e);
   LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p, (int)e->n_partials, e->d_scalars.p));
   LAUNCH(e, K_REDUCE, sum_partials_kernel<<<1, 256, 0, e->stream>>>(e->d_partials.p + e->n_partials, (int)e->n_partials, e->d_scalars.p + 1));
+  if (!e0) { tm.stop(); return; }
   CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
   tm.stop();
@@ -1544,8 +1548,16 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
   }
 }
 
-// returns failing clique id or -1
-static int32_t factorize(Engine* e, double lambda, int diag, double lo, double hi) {
+// the failure flag of the factorisation just enqueued, as a double in d_scalars[8] (agreed over the ranks: every rank must
+// take the same branch of the LM control flow); nothing is read back here
+static void enqueue_fail_flag(Engine* e) {
+  LAUNCH(e, K_REDUCE, fail_flag_kernel<<<1, 1, 0, e->stream>>>(e->d_fail.p, e->d_scalars.p + 8));
+  if (e->world > 1) comm(e, GTB_COMM_ALLREDUCE_MIN, e->d_scalars.p + 8, 1);
+}
+
+// returns failing clique id or -1; defer = true: returns -1 at once, the flag is left in d_scalars[8] (enqueue_fail_flag)
+// for a caller that syncs once at the end of a whole trial
+static int32_t factorize(Engine* e, double lambda, int diag, double lo, double hi, bool defer = false) {
   need_device(e);
   need(e->has_plan, "gtb_set_ordering must be called first");
   need(e->linearized, "gtb_factorize needs gtb_linearize first");
@@ -1598,19 +1610,17 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     comm(e, GTB_COMM_REDUCE_SUM_TO_0, e->d_arena.p + e->top_off, e->top_doubles);
     if (e->rank == 0) factorize_levels(e, E, 1);
   }
-  CK(cudaMemcpyAsync(e->h_scalars + 4, e->d_fail.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  int32_t fail;
-  std::memcpy(&fail, e->h_scalars + 4, sizeof(int32_t));
-  if (e->world > 1) {
-    // every rank must take the same branch of the LM control flow: agree on the first failing clique
-    const double mine = (double)fail;
-    CK(cudaMemcpyAsync(e->d_scalars.p + 8, &mine, sizeof(double), cudaMemcpyHostToDevice, st));
-    comm(e, GTB_COMM_ALLREDUCE_MIN, e->d_scalars.p + 8, 1);
-    CK(cudaMemcpyAsync(e->h_scalars + 5, e->d_scalars.p + 8, sizeof(double), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    fail = (int32_t)e->h_scalars[5];
+  enqueue_fail_flag(e);
+  if (defer) {
+    tm.stop();
+    e->factorized = true;   // provisional: the caller checks the flag after its single sync
+    e->solved = false;
+    e->marg_valid = false;
+    return -1;
   }
+  CK(cudaMemcpyAsync(e->h_scalars + 5, e->d_scalars.p + 8, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const int32_t fail = (int32_t)e->h_scalars[5];
   tm.stop();
   e->factorized = (fail == INT_MAX);
   e->solved = false;
@@ -1774,6 +1784,27 @@ static void retract(Engine* e) {
   e->retracted = true;
 }
 
+// One tryLambda worth of device work with ONE host synchronisation (LevenbergMarquardtOptimizer.cpp:121-270): damped
+// factorisation, back-substitution, both linear errors, retract into the scratch values and their nonlinear error are
+// enqueued back to back; the failure flag and the three scalars come back together.  When the factorisation fails the
+// later kernels run on an unusable factor (bounded loops, results ignored): a rare wasted 1 ms against two round trips
+// to the host in every trial.
+struct TrialResult { int32_t fail; double lin0, lin1, err; };
+static TrialResult trial(Engine* e, double lambda, int diag, double lo, double hi) {
+  factorize(e, lambda, diag, lo, hi, true);
+  backsolve(e);
+  linear_errors(e, nullptr, nullptr);
+  retract(e);
+  nonlinear_error(e, 1, 2);
+  CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, 9 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  TrialResult r;
+  r.fail = e->h_scalars[8] >= (double)INT_MAX ? -1 : (int32_t)e->h_scalars[8];
+  r.lin0 = e->h_scalars[0]; r.lin1 = e->h_scalars[1]; r.err = e->h_scalars[2];
+  if (r.fail >= 0) e->factorized = e->solved = e->retracted = false;
+  return r;
+}
+
 // ------------------------------------------------------------------------------------------------------
 // LM / GN drivers
 // ------------------------------------------------------------------------------------------------------
@@ -1795,15 +1826,12 @@ static bool try_lambda(Engine* e, const gtb_lm_params& P, LMState& S) {
   double modelFidelity = 0.0;
   bool step_ok = false, stop = false;
   double newError = std::numeric_limits<double>::infinity();
-  const int32_t fail = factorize(e, S.lambda, P.diagonal_damping, P.min_diagonal, P.max_diagonal);
-  if (fail < 0) {
-    backsolve(e);
-    double oldLin, newLin;
-    linear_errors(e, &oldLin, &newLin);
+  const TrialResult tr = trial(e, S.lambda, P.diagonal_damping, P.min_diagonal, P.max_diagonal);
+  if (tr.fail < 0) {
+    const double oldLin = tr.lin0, newLin = tr.lin1;
     const double linearizedCostChange = oldLin - newLin;
     if (linearizedCostChange >= 0) {
-      retract(e);
-      newError = nonlinear_error(e, 1);
+      newError = tr.err;
       const double costChange = S.error - newError;
       if (linearizedCostChange > std::numeric_limits<double>::epsilon() * oldLin) {
         modelFidelity = costChange / linearizedCostChange;
@@ -2322,6 +2350,20 @@ gtb_status gtb_factorize(gtb_engine* e, double lambda, int diag, double lo, doub
 gtb_status gtb_backsolve(gtb_engine* e) {
   if (!e) return GTB_ERR_INVALID;
   GTB_TRY(e) backsolve(e); GTB_CATCH(e)
+}
+gtb_status gtb_trial(gtb_engine* e, double lambda, int diag, double lo, double hi, double* out3, uint64_t* failed_key) {
+  if (!e || !out3) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  const TrialResult r = trial(e, lambda, diag, lo, hi);
+  out3[0] = r.lin0; out3[1] = r.lin1; out3[2] = r.err;
+  if (r.fail >= 0) {
+    const uint64_t key = e->vkeys[e->plan.vars[e->plan.vars_off[r.fail]]];
+    if (failed_key) *failed_key = key;
+    char buf[128];
+    snprintf(buf, sizeof buf, "indeterminant linear system detected while working near variable %llu", (unsigned long long)key);
+    throw StatusError(GTB_ERR_INDETERMINATE, buf);
+  }
+  GTB_CATCH(e)
 }
 gtb_status gtb_get_delta(gtb_engine* e, double* out) {
   if (!e) return GTB_ERR_INVALID;

@@ -644,6 +644,9 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const double* __restr
   if (threadIdx.x == 0) *out = v;
 }
 
+// failure flag of a factorisation (min failing clique id, INT_MAX = none) as a double next to the error scalars
+__global__ void fail_flag_kernel(const int32_t* __restrict__ fail, double* __restrict__ out) { *out = (double)*fail; }
+
 // Hessian diagonal (linear/JacobianFactor.cpp:539-564): one warp per variable gathers the squared column norms
 // of every incident factor block in graph order (deterministic, no atomics).
 struct IncidenceDev {

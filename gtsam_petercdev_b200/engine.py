@@ -170,6 +170,17 @@ class Engine:
             raise IndeterminantLinearSystemException(st, self.lib.gtb_last_error(self.h).decode(), key.value)
         self._ck(st)
 
+    def trial(self, lam=0.0, diagonal_damping=False, min_diagonal=1e-6, max_diagonal=1e32):
+        """One tryLambda worth of device work with one host sync: (linear error at 0, at delta, error of the trial values)."""
+        out = np.zeros(3)
+        key = C.c_uint64(0)
+        st = self.lib.gtb_trial(self.h, float(lam), int(bool(diagonal_damping)), float(min_diagonal), float(max_diagonal),
+                                _ptr(out), C.byref(key))
+        if st == capi.ERR_INDETERMINATE:
+            raise IndeterminantLinearSystemException(st, self.lib.gtb_last_error(self.h).decode(), key.value)
+        self._ck(st)
+        return float(out[0]), float(out[1]), float(out[2])
+
     def backsolve(self):
         self._ck(self.lib.gtb_backsolve(self.h))
 

@@ -120,6 +120,12 @@ gtb_status gtb_factorize(gtb_engine* e, double lambda, int diagonal_damping, dou
                          double max_diagonal, uint64_t* failed_key);
 /* GaussianBayesTree::optimize (linear/linearAlgorithms-inst.h:50-155).                                   */
 gtb_status gtb_backsolve(gtb_engine* e);
+/* One whole tryLambda worth of device work with ONE host synchronisation (LevenbergMarquardtOptimizer.cpp:121-270):
+ * gtb_factorize(lambda ...) + gtb_backsolve + gtb_linear_errors + gtb_retract + gtb_error(1) enqueued back to back.
+ * out3 = linear.error(zero), linear.error(delta), graph.error(retracted values).  GTB_ERR_INDETERMINATE + *failed_key as
+ * gtb_factorize.  The trial values stay in the scratch copy (gtb_accept makes them current).                        */
+gtb_status gtb_trial(gtb_engine* e, double lambda, int diagonal_damping, double min_diagonal, double max_diagonal,
+                     double* out3, uint64_t* failed_key);
 /* delta for all variables concatenated in ascending key order (VectorValues iteration order).            */
 gtb_status gtb_get_delta(gtb_engine* e, double* out);
 /* Conditionals [R S d], row-major F x (N+1) per clique, cliques in post-order, concatenated.             */
