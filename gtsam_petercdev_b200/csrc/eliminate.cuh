@@ -45,7 +45,9 @@ struct ElimDev {
   double* dfac;         // side buffer for the factored diagonal blocks of large fronts
   const double* Ab[7];
   const double* damp;   // per global scalar, or nullptr
-  int32_t* fail;        // min failing clique id, initialised to INT_MAX
+  int32_t* fail;        // min failure code (fail_code), initialised to INT_MAX
+  const int32_t* orig_off;   // per clique: its members (reference cliques merged into it for the numeric factorisation) ...
+  const int32_t* orig_end;   // ... as the frontal scalar where each member's pivots end
   long long* dbg;       // optional cycle probe of role A (GTB_DEBUG & 8)
   int32_t dbg_clique, dbg_child;
   int32_t debug;        // experiment switches (GTB_DEBUG env): 1 skip tile tasks, 2 skip role-A column work, 4 skip role A
@@ -60,6 +62,9 @@ struct ElimDev {
 __constant__ int c_M[7] = {3, 6, 2, 3, 6, 9, 3};
 __constant__ int c_W[7] = {7, 13, 13, 4, 7, 10, 4};
 __constant__ int c_N0[7] = {3, 6, 9, 3, 6, 9, 3};
+
+// Failure code: clique id and the index of the failing member inside it (a clique that was not amalgamated has one member)
+__device__ __forceinline__ int fail_code(int c, int member = 0) { return (c << 8) | member; }
 
 __device__ __forceinline__ int frexp_exp(double x) {
   int e;
@@ -184,7 +189,7 @@ __global__ void small_front_kernel(ElimDev E, const int32_t* __restrict__ list) 
     if (F >= 2) ok = frexp_exp(A[(F - 2) + (F - 2) * lds]) - frexp_exp(A[(F - 1) + (F - 1) * lds]) < 12;
     else if (F == 1) ok = frexp_exp(A[0]) > -12;
   }
-  if (!ok && tid == 0) atomicMin(E.fail, c);
+  if (!ok && tid == 0) atomicMin(E.fail, fail_code(c));
   double* dst = E.arena + ci.front_off;
   for (int idx = tid; idx < dim * dim; idx += T) {
     const int j = idx / dim, i = idx - j * dim;
@@ -366,7 +371,7 @@ thin_front_kernel(ElimDev E, const int32_t* __restrict__ list, int count, int gr
     else if (F == 1) ok = frexp_exp(P[0]) > -12;
   }
   if (!ok) {
-    if (gtid == 0) atomicMin(E.fail, c);
+    if (gtid == 0) atomicMin(E.fail, fail_code(c));
     return;
   }
   // (2) S = R^-T [A_FS | b]: one separator column per thread, forward substitution in place (:136)
@@ -505,7 +510,7 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_front_kernel(ElimDev E,
   const double r22 = v22 * i2;
   if (ok) ok = frexp_exp(r11) - frexp_exp(r22) < 12;
   if (!ok) {
-    if (lane == 0) atomicMin(E.fail, c);
+    if (lane == 0) atomicMin(E.fail, fail_code(c));
     return;
   }
   const double d0 = 1.0 / r00, d1 = 1.0 / r11, d2 = 1.0 / r22;
@@ -654,7 +659,7 @@ __global__ void __launch_bounds__(kThinWarps * 32) point_rows_kernel(ElimDev E, 
   const double r22 = v22 * i2;
   if (ok) ok = frexp_exp(r11) - frexp_exp(r22) < 12;
   if (!ok) {
-    if (sl == 0) atomicMin(E.fail, c);
+    if (sl == 0) atomicMin(E.fail, fail_code(c));
     return;
   }
   const double d0 = 1.0 / r00, d1 = 1.0 / r11, d2 = 1.0 / r22;
@@ -1351,6 +1356,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     // four tile pairs at a time per warp with warp 0 keeping only the next diagonal tile -- 3.08 ms.)
     const int nb8 = (kb + 7) >> 3;
     bool okw = true;
+    int bad_pivot = -1;
     for (int b = 0; b < nb8; ++b) {
       const int o = 8 * b;
       if (warp == 0) {
@@ -1363,6 +1369,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const double piv = a[k][k];
+          if (okw && !(piv > 0.0)) bad_pivot = k0 + o + k;
           okw = okw && (piv > 0.0);   // Eigen LLT: NumericalIssue on a non-positive pivot (base/cholesky.cpp:126-128)
           const double rinv = rsqrt(piv);
           rv[k] = rinv;
@@ -1434,7 +1441,13 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     if (warp == 0) {
       stamp(5);
       if (lane == 0) *s_ok = okw ? 1 : 0;
-      if (task == 0 && !okw && lane == 0) atomicMin(E.fail, c);
+      if (task == 0 && !okw && lane == 0) {
+        // the member (reference clique) whose pivot failed
+        const int m0 = E.orig_off[c], m1 = E.orig_off[c + 1];
+        int m = m0;
+        while (m + 1 < m1 && E.orig_end[m] <= bad_pivot) ++m;
+        atomicMin(E.fail, fail_code(c, m - m0));
+      }
     }
   }
   __syncthreads();
@@ -1446,16 +1459,27 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
       const int j = idx / PW, i = idx - j * PW;   // column-major
       db[idx] = (i <= j) ? Ds[j * LDP + i] : 0.0;
     }
-    if (k0 + kb == F && tid == 0) {   // last panel: exponent test (base/cholesky.cpp:146-158)
-      const double dlast = Ds[(kb - 1) * LDP + kb - 1];
-      bool good;
-      if (F >= 2) {
-        const double r2 = (kb >= 2) ? Ds[(kb - 2) * LDP + kb - 2] : dfac[(p - 1) * PW * PW + (PW - 1) * PW + (PW - 1)];
-        good = frexp_exp(r2) - frexp_exp(dlast) < 12;
-      } else {
-        good = frexp_exp(dlast) > -12;
+    if (tid == 0) {
+      // Exponent test on the last two pivots of a clique (base/cholesky.cpp:146-158), for every member of this front
+      // whose pivots end inside this panel: an amalgamated front must fail exactly where the reference's cliques do.
+      const int m0 = E.orig_off[c], m1 = E.orig_off[c + 1];
+      int begin = 0;
+      for (int m = m0; m < m1; ++m) {
+        const int end = E.orig_end[m];
+        if (end > k0 && end <= k0 + kb) {
+          const int l = end - 1 - k0;   // last pivot of the member, inside this panel
+          const double dlast = Ds[l * LDP + l];
+          bool good;
+          if (end - begin >= 2) {
+            const double r2 = (l >= 1) ? Ds[(l - 1) * LDP + l - 1] : dfac[(p - 1) * PW * PW + (PW - 1) * PW + (PW - 1)];
+            good = frexp_exp(r2) - frexp_exp(dlast) < 12;
+          } else {
+            good = frexp_exp(dlast) > -12;
+          }
+          if (!good) atomicMin(E.fail, fail_code(c, m - m0));
+        }
+        begin = end;
       }
-      if (!good) atomicMin(E.fail, c);
     }
   }
   if (!colwarp) return;

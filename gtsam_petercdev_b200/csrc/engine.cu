@@ -136,7 +136,8 @@ struct gtb_engine {
 
   SymbolicInput sym;
   std::vector<int32_t> g_bucket, g_index;   // graph position -> (bucket, index)
-  Plan plan;
+  Plan plan;    // the NUMERIC plan: what the device factorises (the reference's tree after relaxed amalgamation of chains of large fronts)
+  Plan rplan;   // the REPORTED plan: the reference's clique layout, bit-exact (gtb_plan_get, conditionals, failure keys)
   bool has_plan = false;
   std::vector<LevelSched> sched[2];   // phase 0: this rank's subtrees, phase 1: the shared top of the tree (rank 0)
   std::vector<int32_t> sched_lists;   // clique lists of both phases, level by level
@@ -208,6 +209,7 @@ struct gtb_engine {
   DevBuf<int32_t> d_gather_child, d_smap, d_tile_flags;
   DevBuf<int64_t> d_gather_smap_off;
   DevBuf<PairReduce> d_pair_reduce;
+  DevBuf<int32_t> d_orig_off, d_orig_end;
   DevBuf<double> d_pair_scratch;
   DevBuf<StepTask> d_step_tasks;
   DevBuf<PairSeg> d_pair_segs;
@@ -1338,6 +1340,12 @@ static void install_plan(Engine* e) {
   e->d_gather_smap_off.upload(e->gather_smap_off, st);
   e->d_smap.upload(e->smap, st);
   e->d_pair_reduce.upload(e->pair_reduce, st);
+  {
+    need(p.orig_off.back() < INT32_MAX, "member list overflow");
+    std::vector<int32_t> oo(p.orig_off.begin(), p.orig_off.end());
+    e->d_orig_off.upload(oo, st);
+    e->d_orig_end.upload(p.orig_end, st);
+  }
   e->d_pair_scratch.alloc((size_t)e->pair_slots * kPairSlot + 1);
   e->d_tile_flags.alloc((size_t)e->tile_flags + 1);
   CK(cudaMemsetAsync(e->d_tile_flags.p, 0, ((size_t)e->tile_flags + 1) * sizeof(int32_t), st));
@@ -1366,7 +1374,11 @@ static void set_ordering_ids(Engine* e, const std::vector<int32_t>& order) {
   need(e->finalized, "gtb_finalize_problem must be called first");
   e->sym.order = order;
   try {
-    build_plan(e->sym, kDenseMaxDim, &e->plan);
+    // GTB_AMALGAMATE = padded-area ratio up to which a large child is merged into its large parent for the numeric
+    // factorisation (0 or 1: off), GTB_AMALG_MAXF = most frontal scalars of a merged front
+    static const double ratio = getenv("GTB_AMALGAMATE") ? atof(getenv("GTB_AMALGAMATE")) : 1.35;
+    static const int max_f = getenv("GTB_AMALG_MAXF") ? atoi(getenv("GTB_AMALG_MAXF")) : 512;
+    build_plan(e->sym, kDenseMaxDim, &e->rplan, &e->plan, ratio, max_f);
   } catch (const std::runtime_error& ex) {
     throw StatusError(GTB_ERR_INCONSISTENT, ex.what());
   }
@@ -1474,6 +1486,8 @@ static ElimDev elim_dev(Engine* e, bool damp) {
   for (int b = 0; b < 7; ++b) E.Ab[b] = e->d_Ab[b].p;
   E.damp = damp ? e->d_damp.p : nullptr;
   E.fail = e->d_fail.p;
+  E.orig_off = e->d_orig_off.p;
+  E.orig_end = e->d_orig_end.p;
   E.ordered = e->ordered ? 1 : 0;
   E.epoch32 = (e->epoch & 0x3ffffff) * 32;
   E.tile_flags = e->d_tile_flags.p;
@@ -1490,6 +1504,15 @@ static ElimDev elim_dev(Engine* e, bool damp) {
       if (E.dbg_child < 0 || p.S[p.children[k]] > p.S[E.dbg_child]) E.dbg_child = p.children[k];
   }
   return E;
+}
+
+// Failure codes from the device: numeric clique id * 256 + index of the failing member (reference clique) inside it.
+static uint64_t failed_key_of(const Engine* e, int32_t code) {
+  const int32_t nc = code >> 8, sub = code & 255;
+  const Plan& p = e->plan;
+  const int64_t m = std::min<int64_t>(p.orig_off[nc] + sub, p.orig_off[nc + 1] - 1);
+  const int32_t ce = p.orig_clique[m];
+  return e->vkeys[e->rplan.vars[e->rplan.vars_off[ce]]];
 }
 
 static void comm(Engine* e, int op, double* buf, int64_t count) {
@@ -2002,16 +2025,16 @@ gtb_status gtb_plan_sizes(const gtb_engine* e, int64_t* n_cliques, int64_t* n_cl
                           int64_t* n_scalars) {
   if (!e) return GTB_ERR_INVALID;
   if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
-  if (n_cliques) *n_cliques = e->plan.n_cliques;
-  if (n_clique_keys) *n_clique_keys = (int64_t)e->plan.vars.size();
-  if (n_cond) *n_cond = e->plan.cond_off[e->plan.n_cliques];
+  if (n_cliques) *n_cliques = e->rplan.n_cliques;
+  if (n_clique_keys) *n_clique_keys = (int64_t)e->rplan.vars.size();
+  if (n_cond) *n_cond = e->rplan.cond_off[e->rplan.n_cliques];
   if (n_scalars) *n_scalars = e->n_scalars;
   return GTB_OK;
 }
 gtb_status gtb_plan_get(const gtb_engine* e, int64_t* nfrontal, int64_t* nkeys, uint64_t* keys, int64_t* parent) {
   if (!e) return GTB_ERR_INVALID;
   if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
-  const Plan& p = e->plan;
+  const Plan& p = e->rplan;   // the reference's layout, not the amalgamated numeric plan
   for (int32_t c = 0; c < p.n_cliques; ++c) {
     if (nfrontal) nfrontal[c] = p.n_frontal_vars[c];
     if (nkeys) nkeys[c] = p.n_vars[c];
@@ -2049,7 +2072,8 @@ gtb_status gtb_partition_get(const gtb_engine* e, int32_t* owner, double* out) {
   if (!e) return GTB_ERR_INVALID;
   if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
   const Plan& p = e->plan;
-  if (owner) std::memcpy(owner, e->owner.data(), sizeof(int32_t) * p.n_cliques);
+  if (owner)   // per REFERENCE clique (ids as in gtb_plan_get): the owner of the numeric clique that holds it
+    for (int32_t c = 0; c < e->rplan.n_cliques; ++c) owner[c] = e->owner[p.num_of[c]];
   if (out) {
     for (int k = 0; k < 16; ++k) out[k] = 0;
     double total = 0;
@@ -2265,11 +2289,14 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
 gtb_status gtb_plan_stats(const gtb_engine* e, double* out) {
   if (!e || !out) return GTB_ERR_INVALID;
   if (!e->has_plan) { e->err = "no plan"; return GTB_ERR_INVALID; }
+  // Algorithmic work (flops, bytes) is that of the REFERENCE's cliques: the zeros that relaxed amalgamation pads into the
+  // numeric fronts are overhead, not work.  Levels, front sizes and the arena are those of the numeric plan (what runs).
   const Plan& p = e->plan;
-  out[0] = p.n_levels; out[1] = p.max_front; out[2] = p.flops; out[3] = (double)(e->arena_doubles ? e->arena_doubles : p.arena_doubles);
-  out[4] = (double)p.n_small; out[5] = (double)p.n_large; out[6] = p.flops_large; out[7] = p.assembly_bytes;
+  const Plan& r = e->rplan;
+  out[0] = p.n_levels; out[1] = r.max_front; out[2] = r.flops; out[3] = (double)(e->arena_doubles ? e->arena_doubles : p.arena_doubles);
+  out[4] = (double)r.n_small; out[5] = (double)r.n_large; out[6] = r.flops_large; out[7] = r.assembly_bytes;
   double thin_bytes = 0, point_bytes = 0, dense_bytes = 0;
-  out[8] = p.flops_syrk_frontal; out[9] = p.flops_syrk_schur; out[10] = p.bytes_backsolve;
+  out[8] = r.flops_syrk_frontal; out[9] = r.flops_syrk_schur; out[10] = r.bytes_backsolve;
   {
     // small fronts also read the whitened rows of their own factors
     static const int kMW[7] = {21, 78, 26, 12, 42, 90, 12};
@@ -2339,7 +2366,7 @@ gtb_status gtb_factorize(gtb_engine* e, double lambda, int diag, double lo, doub
   GTB_TRY(e)
   const int32_t fail = factorize(e, lambda, diag, lo, hi);
   if (fail >= 0) {
-    const uint64_t key = e->vkeys[e->plan.vars[e->plan.vars_off[fail]]];
+    const uint64_t key = failed_key_of(e, fail);
     if (failed_key) *failed_key = key;
     char buf[128];
     snprintf(buf, sizeof buf, "indeterminant linear system detected while working near variable %llu", (unsigned long long)key);
@@ -2357,7 +2384,7 @@ gtb_status gtb_trial(gtb_engine* e, double lambda, int diag, double lo, double h
   const TrialResult r = trial(e, lambda, diag, lo, hi);
   out3[0] = r.lin0; out3[1] = r.lin1; out3[2] = r.err;
   if (r.fail >= 0) {
-    const uint64_t key = e->vkeys[e->plan.vars[e->plan.vars_off[r.fail]]];
+    const uint64_t key = failed_key_of(e, r.fail);
     if (failed_key) *failed_key = key;
     char buf[128];
     snprintf(buf, sizeof buf, "indeterminant linear system detected while working near variable %llu", (unsigned long long)key);
@@ -2380,17 +2407,29 @@ gtb_status gtb_get_conditionals(gtb_engine* e, double* out) {
   need_device(e);
   need(e->factorized && out, "gtb_get_conditionals needs a successful gtb_factorize first");
   const Plan& p = e->plan;
+  const Plan& r = e->rplan;
   // parity dump: not a hot path; stage the whole arena through the host
   // (with several ranks only the cliques this rank factored hold conditionals; the others read back as assembled)
   std::vector<double> arena((size_t)e->arena_doubles);
   CK(cudaMemcpyAsync(arena.data(), e->d_arena.p, arena.size() * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
-  for (int32_t c = 0; c < p.n_cliques; ++c) {
-    const int F = p.F[c], dim = F + p.S[c] + 1, ld = e->ld[c];
-    const double* A = arena.data() + e->front_off[c];
-    double* o = out + p.cond_off[c];
-    for (int i = 0; i < F; ++i)
-      for (int j = 0; j < dim; ++j) o[(int64_t)i * dim + j] = (j >= i) ? A[i + (int64_t)j * ld] : 0.0;
+  // A reference clique is a band of rows of the numeric front that holds it: its frontal columns follow its first pivot,
+  // its separator scalars are found through their global scalar index (columns the clique does not see are structural
+  // zeros of the merged front and are not part of its conditional).
+  std::vector<int32_t> col_of((size_t)e->n_scalars, -1);
+  for (int32_t nc = 0; nc < p.n_cliques; ++nc) {
+    const int Fn = p.F[nc], Nn = Fn + p.S[nc], ld = e->ld[nc];
+    const double* A = arena.data() + e->front_off[nc];
+    for (int k = 0; k < Nn; ++k) col_of[p.gidx[p.gidx_off[nc] + k]] = k;
+    for (int64_t m = p.orig_off[nc]; m < p.orig_off[nc + 1]; ++m) {
+      const int32_t c = p.orig_clique[m];
+      const int F = r.F[c], N = F + r.S[c], dim = N + 1, r0 = p.num_foff[c];
+      double* o = out + r.cond_off[c];
+      for (int j = 0; j < dim; ++j) {
+        const int jn = j < N ? col_of[r.gidx[r.gidx_off[c] + j]] : Nn;
+        for (int i = 0; i < F; ++i) o[(int64_t)i * dim + j] = (j >= i) ? A[(r0 + i) + (int64_t)jn * ld] : 0.0;
+      }
+    }
   }
   GTB_CATCH(e)
 }
@@ -2521,7 +2560,7 @@ gtb_status gtb_gn_optimize(gtb_engine* e, int32_t max_iterations, double rel, do
       if (fail >= 0) {
         char buf[128];
         snprintf(buf, sizeof buf, "indeterminant linear system detected while working near variable %llu",
-                 (unsigned long long)e->vkeys[e->plan.vars[e->plan.vars_off[fail]]]);
+                 (unsigned long long)failed_key_of(e, fail));
         throw StatusError(GTB_ERR_INDETERMINATE, buf);
       }
       backsolve(e);

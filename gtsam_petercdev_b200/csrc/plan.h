@@ -62,6 +62,13 @@ struct Plan {
   double bytes_backsolve = 0;      // [R S d] read once + delta written
   int32_t max_front = 0;
   int64_t n_small = 0, n_large = 0;
+  // Numeric plan only (relaxed amalgamation, symbolic.cpp): the reference cliques every numeric clique holds, in elimination
+  // order, and where each one's frontal scalars end inside the merged front; and the inverse map.
+  std::vector<int64_t> orig_off;        // [n_cliques+1] into orig_clique / orig_end
+  std::vector<int32_t> orig_clique;     // reference clique id (numbering of the reported plan)
+  std::vector<int32_t> orig_end;        // frontal scalar index (exclusive) where that clique's pivots end
+  std::vector<int32_t> num_of;          // per reference clique: numeric clique id
+  std::vector<int32_t> num_foff;        // per reference clique: first frontal scalar inside the numeric front
 };
 
 // Front classes.  "Small" fronts are assembled and eliminated entirely in shared memory by one warp or CTA:
@@ -84,6 +91,9 @@ GTB_HD inline bool is_fused_child(int32_t F, int32_t dim, int32_t parent_F, int3
 
 // Throws std::runtime_error with a message on inconsistent input.
 // small_max: fronts with F+S+1 <= small_max are handled by the shared-memory kernel.
-void build_plan(const SymbolicInput& in, int32_t small_max, Plan* out);
+// out: the reference's clique layout, bit-exact.  numeric (may be null): the plan the device factorises, after relaxed
+// amalgamation of chains of large fronts (amalg_ratio <= 1 disables it: numeric = out plus the identity member lists).
+void build_plan(const SymbolicInput& in, int32_t small_max, Plan* out, Plan* numeric = nullptr, double amalg_ratio = 0.0,
+                int32_t amalg_max_F = 0);
 
 }  // namespace gtb

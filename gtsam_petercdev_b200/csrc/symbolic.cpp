@@ -29,128 +29,10 @@ struct Cluster {
 };
 }  // namespace
 
-void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P) {
+// Numbers the cliques of a cluster tree in DFS post-order and flattens it to the index arrays of a Plan.
+static void flatten(const SymbolicInput& in, const std::vector<Cluster>& cl, const std::vector<std::vector<int32_t>>& sep,
+                    const std::vector<int32_t>& eparent, Plan* P, std::vector<int32_t>* clique_of_out) {
   const int32_t n = in.n_vars;
-  const int64_t M = in.n_factors;
-  if ((int64_t)in.order.size() != n)
-    throw std::runtime_error("ordering must contain every variable exactly once (partial elimination is not supported)");
-  std::vector<int32_t> pos_of(n, -1);
-  for (int32_t j = 0; j < n; ++j) {
-    int32_t v = in.order[j];
-    if (v < 0 || v >= n || pos_of[v] != -1) throw std::runtime_error("ordering is not a permutation of the variables");
-    pos_of[v] = j;
-  }
-
-  // ---- VariableIndex (CSR, factor indices ascending per variable) -------------------------------------
-  std::vector<int64_t> vi_off(n + 1, 0);
-  for (int64_t g = 0; g < M; ++g)
-    for (int k = 0; k < in.fac_nkeys[g]; ++k) vi_off[in.fac_var[2 * g + k] + 1]++;
-  for (int32_t v = 0; v < n; ++v) vi_off[v + 1] += vi_off[v];
-  std::vector<int32_t> vi_fac(vi_off[n]);
-  {
-    std::vector<int64_t> fill(vi_off.begin(), vi_off.end() - 1);
-    for (int64_t g = 0; g < M; ++g)
-      for (int k = 0; k < in.fac_nkeys[g]; ++k) vi_fac[fill[in.fac_var[2 * g + k]]++] = (int32_t)g;
-  }
-
-  // ---- elimination tree -----------------------------------------------------------------------------
-  std::vector<int32_t> eparent(n, -1), anc(n, -1);
-  std::vector<int32_t> prev_col(M, -1);
-  std::vector<std::vector<int32_t>> echildren(n), efactors(n);
-  for (int32_t j = 0; j < n; ++j) {
-    const int32_t v = in.order[j];
-    if (vi_off[v] == vi_off[v + 1])
-      throw std::runtime_error("EliminationTree: given ordering contains variables that are not involved in the factor graph");
-    for (int64_t q = vi_off[v]; q < vi_off[v + 1]; ++q) {
-      const int32_t i = vi_fac[q];
-      if (prev_col[i] != -1) {
-        // root of the tree containing the previously eliminated key of this factor (path-compressed walk;
-        // the reference walks parents[] uncompressed, the root found is the same)
-        int32_t r = prev_col[i];
-        while (true) {
-          const int32_t a = anc[r];
-          if (a == -1 || a == j) break;
-          anc[r] = j;
-          r = a;
-        }
-        if (anc[r] == -1) {
-          anc[r] = j;
-          eparent[r] = j;
-          echildren[j].push_back(r);
-        }
-      } else {
-        efactors[j].push_back(i);
-      }
-      prev_col[i] = j;
-    }
-  }
-
-  // ---- symbolic elimination: separator of every elimination-tree node ------------------------------
-  std::vector<std::vector<int32_t>> sep(n);
-  {
-    std::vector<int32_t> mark(n, -1);
-    for (int32_t j = 0; j < n; ++j) {
-      const int32_t v = in.order[j];
-      std::vector<int32_t>& s = sep[j];
-      mark[v] = j;
-      for (int32_t g : efactors[j])
-        for (int k = 0; k < in.fac_nkeys[g]; ++k) {
-          const int32_t u = in.fac_var[2 * (int64_t)g + k];
-          if (mark[u] != j) { mark[u] = j; s.push_back(u); }
-        }
-      for (int32_t c : echildren[j])
-        for (int32_t u : sep[c])
-          if (mark[u] != j) { mark[u] = j; s.push_back(u); }
-      std::sort(s.begin(), s.end());
-    }
-  }
-
-  // ---- junction tree: merge children into parents ----------------------------------------------------
-  std::vector<Cluster> cl(n);
-  std::vector<uint8_t> merged_away(n, 0);
-  {
-    std::vector<uint8_t> merge;
-    for (int32_t j = 0; j < n; ++j) {
-      Cluster& me = cl[j];
-      me.frontals.assign(1, in.order[j]);
-      me.factors = std::move(efactors[j]);
-      me.children = std::move(echildren[j]);
-      const size_t my_parents = sep[j].size();
-      size_t my_frontals = 1;
-      const size_t nc = me.children.size();
-      merge.assign(nc, 0);
-      bool any = false;
-      for (size_t i = 0; i < nc; ++i) {
-        const int32_t c = me.children[i];
-        if (my_parents + my_frontals == sep[c].size()) {
-          my_frontals += cl[c].frontals.size();
-          merge[i] = 1;
-          any = true;
-        }
-      }
-      if (!any) continue;
-      std::vector<int32_t> old = std::move(me.children);
-      me.children.clear();
-      for (size_t i = 0; i < nc; ++i) {
-        const int32_t c = old[i];
-        if (merge[i]) {
-          Cluster& ch = cl[c];
-          me.frontals.insert(me.frontals.end(), ch.frontals.rbegin(), ch.frontals.rend());
-          me.factors.insert(me.factors.end(), ch.factors.begin(), ch.factors.end());
-          me.children.insert(me.children.end(), ch.children.begin(), ch.children.end());
-          merged_away[c] = 1;
-          Cluster().frontals.swap(ch.frontals);
-          Cluster().factors.swap(ch.factors);
-          Cluster().children.swap(ch.children);
-          std::vector<int32_t>().swap(sep[c]);
-        } else {
-          me.children.push_back(c);
-        }
-      }
-      std::reverse(me.frontals.begin(), me.frontals.end());
-    }
-  }
-
   // ---- number the cliques in DFS post-order ----------------------------------------------------------
   std::vector<int32_t> node_of;       // clique id -> elimination-tree node id
   std::vector<int32_t> clique_of(n, -1);
@@ -322,6 +204,218 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P) {
           if (small) p.level_n_small[p.level[c]]++;
         }
       }
+  }
+  if (clique_of_out) *clique_of_out = clique_of;
+}
+
+void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, double amalg_ratio, int32_t amalg_max_F) {
+  const int32_t n = in.n_vars;
+  const int64_t M = in.n_factors;
+  if ((int64_t)in.order.size() != n)
+    throw std::runtime_error("ordering must contain every variable exactly once (partial elimination is not supported)");
+  std::vector<int32_t> pos_of(n, -1);
+  for (int32_t j = 0; j < n; ++j) {
+    int32_t v = in.order[j];
+    if (v < 0 || v >= n || pos_of[v] != -1) throw std::runtime_error("ordering is not a permutation of the variables");
+    pos_of[v] = j;
+  }
+
+  // ---- VariableIndex (CSR, factor indices ascending per variable) -------------------------------------
+  std::vector<int64_t> vi_off(n + 1, 0);
+  for (int64_t g = 0; g < M; ++g)
+    for (int k = 0; k < in.fac_nkeys[g]; ++k) vi_off[in.fac_var[2 * g + k] + 1]++;
+  for (int32_t v = 0; v < n; ++v) vi_off[v + 1] += vi_off[v];
+  std::vector<int32_t> vi_fac(vi_off[n]);
+  {
+    std::vector<int64_t> fill(vi_off.begin(), vi_off.end() - 1);
+    for (int64_t g = 0; g < M; ++g)
+      for (int k = 0; k < in.fac_nkeys[g]; ++k) vi_fac[fill[in.fac_var[2 * g + k]]++] = (int32_t)g;
+  }
+
+  // ---- elimination tree -----------------------------------------------------------------------------
+  std::vector<int32_t> eparent(n, -1), anc(n, -1);
+  std::vector<int32_t> prev_col(M, -1);
+  std::vector<std::vector<int32_t>> echildren(n), efactors(n);
+  for (int32_t j = 0; j < n; ++j) {
+    const int32_t v = in.order[j];
+    if (vi_off[v] == vi_off[v + 1])
+      throw std::runtime_error("EliminationTree: given ordering contains variables that are not involved in the factor graph");
+    for (int64_t q = vi_off[v]; q < vi_off[v + 1]; ++q) {
+      const int32_t i = vi_fac[q];
+      if (prev_col[i] != -1) {
+        // root of the tree containing the previously eliminated key of this factor (path-compressed walk;
+        // the reference walks parents[] uncompressed, the root found is the same)
+        int32_t r = prev_col[i];
+        while (true) {
+          const int32_t a = anc[r];
+          if (a == -1 || a == j) break;
+          anc[r] = j;
+          r = a;
+        }
+        if (anc[r] == -1) {
+          anc[r] = j;
+          eparent[r] = j;
+          echildren[j].push_back(r);
+        }
+      } else {
+        efactors[j].push_back(i);
+      }
+      prev_col[i] = j;
+    }
+  }
+
+  // ---- symbolic elimination: separator of every elimination-tree node ------------------------------
+  std::vector<std::vector<int32_t>> sep(n);
+  {
+    std::vector<int32_t> mark(n, -1);
+    for (int32_t j = 0; j < n; ++j) {
+      const int32_t v = in.order[j];
+      std::vector<int32_t>& s = sep[j];
+      mark[v] = j;
+      for (int32_t g : efactors[j])
+        for (int k = 0; k < in.fac_nkeys[g]; ++k) {
+          const int32_t u = in.fac_var[2 * (int64_t)g + k];
+          if (mark[u] != j) { mark[u] = j; s.push_back(u); }
+        }
+      for (int32_t c : echildren[j])
+        for (int32_t u : sep[c])
+          if (mark[u] != j) { mark[u] = j; s.push_back(u); }
+      std::sort(s.begin(), s.end());
+    }
+  }
+
+  // ---- junction tree: merge children into parents ----------------------------------------------------
+  std::vector<Cluster> cl(n);
+  std::vector<uint8_t> merged_away(n, 0);
+  {
+    std::vector<uint8_t> merge;
+    for (int32_t j = 0; j < n; ++j) {
+      Cluster& me = cl[j];
+      me.frontals.assign(1, in.order[j]);
+      me.factors = std::move(efactors[j]);
+      me.children = std::move(echildren[j]);
+      const size_t my_parents = sep[j].size();
+      size_t my_frontals = 1;
+      const size_t nc = me.children.size();
+      merge.assign(nc, 0);
+      bool any = false;
+      for (size_t i = 0; i < nc; ++i) {
+        const int32_t c = me.children[i];
+        if (my_parents + my_frontals == sep[c].size()) {
+          my_frontals += cl[c].frontals.size();
+          merge[i] = 1;
+          any = true;
+        }
+      }
+      if (!any) continue;
+      std::vector<int32_t> old = std::move(me.children);
+      me.children.clear();
+      for (size_t i = 0; i < nc; ++i) {
+        const int32_t c = old[i];
+        if (merge[i]) {
+          Cluster& ch = cl[c];
+          me.frontals.insert(me.frontals.end(), ch.frontals.rbegin(), ch.frontals.rend());
+          me.factors.insert(me.factors.end(), ch.factors.begin(), ch.factors.end());
+          me.children.insert(me.children.end(), ch.children.begin(), ch.children.end());
+          merged_away[c] = 1;
+          Cluster().frontals.swap(ch.frontals);
+          Cluster().factors.swap(ch.factors);
+          Cluster().children.swap(ch.children);
+          std::vector<int32_t>().swap(sep[c]);
+        } else {
+          me.children.push_back(c);
+        }
+      }
+      std::reverse(me.frontals.begin(), me.frontals.end());
+    }
+  }
+
+  // ---- the reference's clique layout, bit-exact -------------------------------------------------------
+  std::vector<int32_t> clique_exact;
+  flatten(in, cl, sep, eparent, P, &clique_exact);
+  if (!N) return;
+
+  // ---- relaxed amalgamation for the NUMERIC plan ------------------------------------------------------
+  // The reference's supernode rule only merges a child whose separator is exactly the parent's variable set.  Trees of
+  // large fronts are full of near misses: a parent that owns one or two variables its child does not see (every link of a
+  // COLAMD-ordered bundle adjustment: 1,124 levels of ONE front with 9 frontal and ~1040 separator scalars; the lower
+  // levels of a METIS tree).  Each link then costs a panel launch, a Schur launch and the hand-over of a ~1000 x 1000
+  // Schur complement for a handful of pivots.  For the numeric factorisation such a child is merged into its parent
+  // anyway: frontals = child's, then parent's; separator = parent's; the child's rows get structural zeros in the columns
+  // it does not see (they stay exactly zero through the elimination).  A merge is taken while the padded area of the
+  // merged front stays within `ratio` of the true area of its members and F stays below `max_F`.  The REPORTED layout (P)
+  // is untouched; N records which reference cliques each numeric clique holds (orig_*), so that conditionals, the
+  // failure rule of base/cholesky.cpp:146-158 (applied at every member's last pivot) and keys are reported per
+  // reference clique.
+  std::vector<std::vector<int32_t>> group(n);
+  std::vector<double> area(n, 0.0);
+  std::vector<int32_t> Fn(n, 0), Sn(n, 0);
+  for (int32_t j = 0; j < n; ++j) {
+    if (merged_away[j]) continue;
+    group[j].assign(1, j);
+    for (int32_t v : cl[j].frontals) Fn[j] += in.var_dim[v];
+    for (int32_t v : sep[j]) Sn[j] += in.var_dim[v];
+    area[j] = 0.5 * Fn[j] * (Fn[j] + 1.0) + (double)Fn[j] * (Sn[j] + 1.0);
+  }
+  if (amalg_ratio > 1.0) {
+    for (int32_t j = 0; j < n; ++j) {
+      if (merged_away[j] || is_small_front(Fn[j], Fn[j] + Sn[j] + 1)) continue;
+      int32_t best = -1;
+      size_t best_pos = 0;
+      for (size_t i = 0; i < cl[j].children.size(); ++i) {
+        const int32_t c = cl[j].children[i];
+        if (is_small_front(Fn[c], Fn[c] + Sn[c] + 1)) continue;
+        if (best < 0 || Fn[c] + Sn[c] > Fn[best] + Sn[best]) { best = c; best_pos = i; }
+      }
+      if (best < 0) continue;
+      const int32_t c = best;
+      const double Fm = (double)Fn[c] + Fn[j];
+      const double merged_area = 0.5 * Fm * (Fm + 1.0) + Fm * (Sn[j] + 1.0);
+      if (Fm > amalg_max_F || group[c].size() + group[j].size() > 255 || merged_area > amalg_ratio * (area[c] + area[j])) continue;
+      Cluster& me = cl[j];
+      Cluster& ch = cl[c];
+      std::vector<int32_t> fr = std::move(ch.frontals);
+      fr.insert(fr.end(), me.frontals.begin(), me.frontals.end());
+      me.frontals = std::move(fr);
+      me.factors.insert(me.factors.end(), ch.factors.begin(), ch.factors.end());
+      std::vector<int32_t> kids(me.children.begin(), me.children.begin() + best_pos);
+      kids.insert(kids.end(), ch.children.begin(), ch.children.end());
+      kids.insert(kids.end(), me.children.begin() + best_pos + 1, me.children.end());
+      me.children = std::move(kids);
+      std::vector<int32_t> gr = std::move(group[c]);
+      gr.insert(gr.end(), group[j].begin(), group[j].end());
+      group[j] = std::move(gr);
+      area[j] += area[c];
+      Fn[j] += Fn[c];
+      merged_away[c] = 1;
+      Cluster().factors.swap(ch.factors);
+      Cluster().children.swap(ch.children);
+      std::vector<int32_t>().swap(sep[c]);
+    }
+  }
+  std::vector<int32_t> clique_num;
+  flatten(in, cl, sep, eparent, N, &clique_num);
+  // members of every numeric clique: reference clique ids in elimination order, with the frontal scalar where each ends
+  Plan& q = *N;
+  q.orig_off.assign(q.n_cliques + 1, 0);
+  q.num_of.assign(P->n_cliques, -1);
+  q.num_foff.assign(P->n_cliques, 0);
+  std::vector<int32_t> node_of_num(q.n_cliques, -1);
+  for (int32_t j = 0; j < n; ++j)
+    if (!merged_away[j] && clique_num[j] >= 0) node_of_num[clique_num[j]] = j;
+  for (int32_t c = 0; c < q.n_cliques; ++c) {
+    const std::vector<int32_t>& g = group[node_of_num[c]];
+    q.orig_off[c + 1] = q.orig_off[c] + (int64_t)g.size();
+    int32_t end = 0;
+    for (int32_t nd : g) {
+      const int32_t ce = clique_exact[nd];
+      q.num_of[ce] = c;
+      q.num_foff[ce] = end;
+      end += P->F[ce];
+      q.orig_clique.push_back(ce);
+      q.orig_end.push_back(end);
+    }
+    if (end != q.F[c]) throw std::runtime_error("internal: amalgamated clique does not add up");
   }
 }
 

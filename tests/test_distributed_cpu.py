@@ -28,7 +28,8 @@ def test_tree_cut_is_a_partition(world, monkeypatch):
     e, part, plan = _partition("ba_60_2000", "ba_60_2000__solve_metis_0.0001_1", 0, world)
     owner, parent = part["owner"], plan["clique_parent"]
     assert owner.min() >= -1 and owner.max() < world
-    assert part["n_top"] == int((owner == -1).sum()) >= 2
+    # n_top counts the fronts the device factorises at the top (reference cliques merged by relaxed amalgamation count once)
+    assert 2 <= part["n_top"] <= int((owner == -1).sum())
     for c in range(len(owner)):
         if parent[c] >= 0:
             if owner[c] == -1:
