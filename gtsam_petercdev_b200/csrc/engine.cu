@@ -1375,10 +1375,12 @@ static void set_ordering_ids(Engine* e, const std::vector<int32_t>& order) {
   e->sym.order = order;
   try {
     // GTB_AMALGAMATE = padded-area ratio up to which a large child is merged into its large parent for the numeric
-    // factorisation (0 or 1: off), GTB_AMALG_MAXF = most frontal scalars of a merged front
+    // factorisation (0 or 1: off), GTB_AMALG_MAXF = most frontal scalars of a merged front, GTB_AMALG_MINS = fewest
+    // separator scalars of a child worth merging
     static const double ratio = getenv("GTB_AMALGAMATE") ? atof(getenv("GTB_AMALGAMATE")) : 1.35;
     static const int max_f = getenv("GTB_AMALG_MAXF") ? atoi(getenv("GTB_AMALG_MAXF")) : 512;
-    build_plan(e->sym, kDenseMaxDim, &e->rplan, &e->plan, ratio, max_f);
+    static const int min_s = getenv("GTB_AMALG_MINS") ? atoi(getenv("GTB_AMALG_MINS")) : 512;
+    build_plan(e->sym, kDenseMaxDim, &e->rplan, &e->plan, ratio, max_f, min_s);
   } catch (const std::runtime_error& ex) {
     throw StatusError(GTB_ERR_INCONSISTENT, ex.what());
   }

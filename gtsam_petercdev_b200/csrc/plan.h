@@ -94,6 +94,6 @@ GTB_HD inline bool is_fused_child(int32_t F, int32_t dim, int32_t parent_F, int3
 // out: the reference's clique layout, bit-exact.  numeric (may be null): the plan the device factorises, after relaxed
 // amalgamation of chains of large fronts (amalg_ratio <= 1 disables it: numeric = out plus the identity member lists).
 void build_plan(const SymbolicInput& in, int32_t small_max, Plan* out, Plan* numeric = nullptr, double amalg_ratio = 0.0,
-                int32_t amalg_max_F = 0);
+                int32_t amalg_max_F = 0, int32_t amalg_min_S = 0);
 
 }  // namespace gtb

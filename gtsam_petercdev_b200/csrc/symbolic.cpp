@@ -208,7 +208,8 @@ static void flatten(const SymbolicInput& in, const std::vector<Cluster>& cl, con
   if (clique_of_out) *clique_of_out = clique_of;
 }
 
-void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, double amalg_ratio, int32_t amalg_max_F) {
+void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, double amalg_ratio, int32_t amalg_max_F,
+                int32_t amalg_min_S) {
   const int32_t n = in.n_vars;
   const int64_t M = in.n_factors;
   if ((int64_t)in.order.size() != n)
@@ -365,6 +366,9 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
       for (size_t i = 0; i < cl[j].children.size(); ++i) {
         const int32_t c = cl[j].children[i];
         if (is_small_front(Fn[c], Fn[c] + Sn[c] + 1)) continue;
+        // below ~512 separator scalars the hand-over of the child's Schur complement (S^2 / 2 entries) is cheaper than the
+        // zeros a merge pads into the parent's panel steps (measured: sphere2500-shape pose graphs get slower when merged)
+        if (Sn[c] < amalg_min_S) continue;
         if (best < 0 || Fn[c] + Sn[c] > Fn[best] + Sn[best]) { best = c; best_pos = i; }
       }
       if (best < 0) continue;
