@@ -64,7 +64,7 @@ def clocks_start(path):
     q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     try:
-        return subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+        return subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                 stdout=open(path, "w"), stderr=subprocess.DEVNULL)
     except Exception:
         return None
@@ -110,6 +110,42 @@ def emit(obj):
     out.flush()
 
 
+def bench_config(args):
+    """The `config` object, identical in both arms (the driver compares them key by key)."""
+    return {"workload": WORKLOADS[args.workload], "ordering": args.ordering, "lambda": args.lam,
+            "l2": "inputs larger than L2 (no flush needed)" if args.workload in ("c3", "c4") else "inputs fit L2 (pose graph of the named size)"}
+
+
+def source_digest():
+    """SHA-256 over the kernel sources: an ncu traffic file is only quoted for the build it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "gtsam_petercdev_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".cpp", ".h")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def dgemm_probe(torch, n=8192, reps=5):
+    """FP64 matrix-multiply rate of THIS box, measured live (cuBLAS DGEMM n^3 through torch, best of `reps`): the
+    denominator of the tensor-bound roofline lines (MEASURED_PEAKS.json carries no FP64 figure)."""
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    b = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a, b)
+    best = 1e30
+    for _ in range(reps):
+        s, f = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        torch.matmul(a, b)
+        f.record()
+        torch.cuda.synchronize()
+        best = min(best, s.elapsed_time(f))
+    del a, b
+    return 2.0 * n ** 3 / (best / 1e3) / 1e12
+
+
 def run_reference(args, rank, world):
     """The reference's own CPU implementation of the step (oracle/_ref/ref_tool mode=time: unmodified GTSAM 4.3a0
     linked from oracle/_ref/libgtsam_ref.so), rank 0 only."""
@@ -117,9 +153,8 @@ def run_reference(args, rank, world):
         return
     tool = os.path.join(ROOT, "oracle", "_ref", "ref_tool")
     base = {"impl": "reference", "metric": "LM iter/s (linearize+multifrontal Cholesky+backsub)", "unit": "iter/s",
-            "n_gpus": args.gpus, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": {"workload": WORKLOADS[args.workload], "ordering": args.ordering,
-                                            "lambda": args.lam}}
+            "n_gpus": args.gpus, "higher_is_better": True, "scaling": "strong" if args.parallelism == "tree" else "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": bench_config(args)}
     if not os.path.exists(tool):
         emit({"impl": "reference", "unavailable": "oracle/_ref/ref_tool not built (needs /root/reference)"})
         return
@@ -232,6 +267,21 @@ def main():
         err1 = step()
     clk_path = os.path.join(tempfile.gettempdir(), f"gtb_clocks_{rank}.csv")
     clk = clocks_start(clk_path) if rank == 0 else None
+    # nvidia-smi needs a few hundred ms before its first sample: keep the GPU under the same load (untimed steps) until the
+    # sampler is live, so that even a short timed region is covered by samples taken during it.  With several ranks every
+    # rank runs the same fixed number of extra steps (a step contains collectives).
+    if world > 1:
+        for _ in range(150):
+            step()
+    elif clk is not None:
+        t_wait = time.time()
+        while time.time() - t_wait < 3.0:
+            step()
+            try:
+                if os.path.getsize(clk_path) > 0:
+                    break
+            except OSError:
+                pass
 
     def timed(fn, n):
         barrier()
@@ -274,16 +324,41 @@ def main():
     total_k = sum(v[0] for v in per_step.values())
     share = {k: v[0] / total_k for k, v in per_step.items()}
     hbm = 6538.6
+    dgemm = dgemm_probe(torch)
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         hbm = float(peaks["hbm_gbs"])
-        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs; fp64 tensor peak = cuBLAS DGEMM measured by tools/probe_box.py)"
+        peak_src = (f"HBM: MEASURED_PEAKS.json hbm_gbs ({peaks.get('when', '?')}, {peaks.get('gpu_name', '?')}); FP64: cuBLAS DGEMM 8192^3 "
+                    f"measured live in this run on this box = {dgemm:.2f} TFLOP/s (MEASURED_PEAKS.json has no FP64 figure; "
+                    f"tcgen05 has no f64 kind, the FP64 tensor instruction is mma.sync m8n8k4)")
     except Exception:
-        hbm, peak_src = 6650.0, "fallback"
+        hbm, peak_src = 6650.0, f"HBM: fallback of the profiling recipe; FP64: cuBLAS DGEMM 8192^3 measured live = {dgemm:.2f} TFLOP/s"
+    # algorithmic work of THIS rank (rank 0): with several ranks only the cliques rank 0 factors count (its subtrees and
+    # the shared top of the tree), computed from the reference clique layout and the ownership map
+    flops_panel, flops_schur = st["flops_large"] - st["flops_syrk_schur"], st["flops_syrk_schur"]
+    if tree:
+        own = e.partition()["owner"]
+        nf, nk = plan["clique_nfrontal"], plan["clique_nkeys"]
+        dims = dict(zip(e.var_keys.tolist(), e.var_dim.tolist()))
+        off, fp, fs = 0, 0.0, 0.0
+        keys = plan["clique_keys"].tolist()
+        for c in range(len(nf)):
+            kk = keys[off:off + int(nk[c])]
+            off += int(nk[c])
+            if own[c] > 0:
+                continue
+            F = float(sum(dims[k] for k in kk[:int(nf[c])]))
+            S = float(sum(dims[k] for k in kk[int(nf[c]):]))
+            if F + S + 1 <= 128 or (F <= 12 and F + S + 1 <= 208):
+                continue          # small fronts are not panel / Schur work
+            s1 = S + 1
+            fs += F * s1 * (s1 + 1)
+            fp += F ** 3 / 3 + F * F * s1
+        flops_panel, flops_schur = fp, fs
     # algorithmic work per step of each candidate class
     work = {
-        "front_step": ("tensor", (st["flops_large"] - st["flops_syrk_schur"]) / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
-        "schur_step": ("tensor", st["flops_syrk_schur"] / 1e12, DGEMM_FP64_TFLOPS, "TFLOP/s"),
+        "front_step": ("tensor", flops_panel / 1e12, dgemm, "TFLOP/s"),
+        "schur_step": ("tensor", flops_schur / 1e12, dgemm, "TFLOP/s"),
         "small_front": ("hbm", st["bytes_dense_small"] / 1e9, hbm, "GB/s"),
         "thin_front": ("hbm", st["bytes_thin"] / 1e9, hbm, "GB/s"),
         "point_front": ("hbm", st["bytes_point"] / 1e9, hbm, "GB/s"),
@@ -294,12 +369,15 @@ def main():
     bound, amount, peak, unit = work[dom]
     achieved = amount / (per_step[dom][0] / 1e3)
     # DRAM bytes per launch of the dominant class, from the committed ncu pass over every launch of this same command
+    # (quoted only when the file was taken from THIS build of the kernels and on one GPU: it records the digest of the sources)
     traffic, traffic_src = None, None
-    tf = os.path.join(ROOT, "profiles", "r01", "ncu_traffic_c3_metis.json")
-    if args.workload == "c3" and args.ordering == "metis" and os.path.exists(tf):
+    tf = os.path.join(ROOT, "profiles", "r02", "ncu_traffic_c3_metis.json")
+    if args.workload == "c3" and args.ordering == "metis" and world == 1 and os.path.exists(tf):
         tj = json.load(open(tf))
-        if dom in tj:
-            traffic, traffic_src = tj[dom]["traffic_bytes_per_launch"], "profiles/r01/ncu_traffic_c3_metis.json (" + tj["_source"] + ")"
+        if tj.get("_source_digest") != source_digest():
+            traffic_src = "profiles/r02/ncu_traffic_c3_metis.json was taken from another build of the kernels: not quoted"
+        elif dom in tj:
+            traffic, traffic_src = tj[dom]["traffic_bytes_per_launch"], "profiles/r02/ncu_traffic_c3_metis.json (" + tj["_source"] + ")"
     roofline = {"kernel": dom, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
                 "traffic": traffic, "traffic_unit": "bytes per launch (dram read + write)", "traffic_source": traffic_src, "peak_source": peak_src, "share_of_step": share[dom],
                 "launches_per_step": per_step[dom][1], "ms_per_step": per_step[dom][0],
@@ -320,14 +398,18 @@ def main():
     line = {
         "metric": "LM iter/s (linearize+multifrontal Cholesky+backsub)", "value": units * args.steps / (ms_dev / 1e3),
         "unit": "iter/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong" if tree else "weak", "vs_baseline": None,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        # ONE problem whatever N: the tree mode is strong scaling (also on the N = 1 line of a scaling run)
+        "scaling": "strong" if args.parallelism == "tree" else "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload], "ordering": args.ordering + " (the reference's own, precomputed)",
-                   "lambda": lam, "parallelism": par,
-                   "l2": "inputs larger than L2 (fronts %.1f GB, Jacobians %.0f MB)" % (st["arena_doubles"] * 8 / 1e9, st["bytes_linearize"] / 1e6),
-                   "cliques": int(len(plan["clique_parent"])), "levels": int(st["levels"]), "max_front": int(st["max_front"]),
-                   "elimination_gflop": st["flops"] / 1e9, "setup_s": {"upload": t_upload, "symbolic_plan": t_plan}},
-        "e2e": {"value": units * args.steps / (ms_e2e / 1e3), "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8 * 3},
+        "config": bench_config(args),
+        "details": {"parallelism": par, "ordering_source": "the reference's own Ordering::Metis / Colamd, precomputed (tests/golden/*_orderings.npz)",
+                    "working_set": "fronts %.1f GB, Jacobians %.0f MB" % (st["arena_doubles"] * 8 / 1e9, st["bytes_linearize"] / 1e6),
+                    "cliques": int(len(plan["clique_parent"])), "levels_of_the_numeric_plan": int(st["levels"]), "max_front": int(st["max_front"]),
+                    "elimination_gflop": st["flops"] / 1e9, "setup_s": {"upload": t_upload, "symbolic_plan": t_plan}},
+        # the step's result that comes back to the host: the failure flag, both linear errors and the new graph error
+        # (9 doubles); delta and the retracted values stay on the device, as in an LM trial of the reference's loop
+        "e2e": {"value": units * args.steps / (ms_e2e / 1e3), "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8 * 9},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,

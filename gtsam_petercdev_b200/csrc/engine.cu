@@ -375,10 +375,10 @@ struct StageTimer {
 
 // kernel classes for launch counting and optional per-launch event timing
 enum { K_LINEARIZE = 0, K_ERROR, K_LINERR, K_REDUCE, K_HDIAG, K_DAMP, K_SMALL, K_THIN, K_POINT, K_PAIR, K_ZERO, K_LFACT, K_LCHILD, K_STEP, K_SCHUR,
-       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_MARGINAL, K_NUM };
+       K_BACKSOLVE, K_BSGEMV, K_RETRACT, K_OWNDELTA, K_MARGINAL, K_COMM, K_NUM };
 static const char* kKernelNames[K_NUM] = {"linearize", "error", "linear_error", "sum_partials", "hessian_diag", "damping",
                                           "small_front", "thin_front", "point_front", "point_schur", "large_zero", "large_factors", "large_children", "front_step", "schur_step",
-                                          "backsolve", "backsolve_gemv", "retract", "own_delta", "marginals"};
+                                          "backsolve", "backsolve_gemv", "retract", "own_delta", "marginals", "collectives"};
 
 static void prof_begin(Engine* e, int k) {
   if (!e->profiling) return;
@@ -1520,7 +1520,10 @@ static uint64_t failed_key_of(const Engine* e, int32_t code) {
 static void comm(Engine* e, int op, double* buf, int64_t count) {
   if (e->world <= 1) return;
   if (!e->comm) throw StatusError(GTB_ERR_INVALID, "gtb_set_distributed: world > 1 needs a communication callback");
-  if (e->comm(e->comm_user, op, buf, count, e->stream) != 0) throw StatusError(GTB_ERR_CUDA, "communication callback failed");
+  prof_begin(e, K_COMM);   // a profile class of its own (not a kernel of this library: not counted as a launch)
+  const int rc = e->comm(e->comm_user, op, buf, count, e->stream);
+  if (e->profiling) cudaEventRecord(e->prof_events[e->prof_used++], e->stream);
+  if (rc != 0) throw StatusError(GTB_ERR_CUDA, "communication callback failed");
 }
 
 // Elimination of one phase, leaves to roots.  Phase 1 fronts were cleared and partly assembled before the fan-in; only

@@ -1,23 +1,27 @@
 #!/bin/bash
-# Trimmed round-end pass: GPU tests, smoke, default bench (with the CPU baseline), pose-graph lines, launch trace.
-# FULL=1 adds the COLAMD lines and the ncu launch list with DRAM bytes (about 4 more minutes).
+# Round-end pass on ONE GPU: GPU tests, smoke, default bench (with the CPU baseline), the other workloads / orderings,
+# launch trace, per-level times, ncu launch list with DRAM bytes, ncu --set full of the two contraction kernels.
 set -x
-mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > gpurun_out/pytest_gpu.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1
-python bench.py > gpurun_out/bench_c3_full.json 2> gpurun_out/bench_c3_full.err
-for cfg in "c1 metis" "c2 metis" ${FULL:+"c1 colamd" "c2 colamd"}; do
+mkdir -p gpurun_out/r02
+O=gpurun_out/r02
+rm -f gpurun_out/parity_deltas.txt
+(time timeout 900 python -m pytest tests -m gpu -x -q) > $O/pytest_gpu.log 2>&1
+cp gpurun_out/parity_deltas.txt gpurun_out/dropin_test.txt $O/ 2>/dev/null
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1
+python bench.py > $O/bench_c3_full.json 2> $O/bench_c3_full.err
+python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_c3_ref.json 2> $O/bench_c3_ref.err
+for cfg in "c1 metis 30" "c2 metis 30" "c1 colamd 20" "c2 colamd 20" "c3 colamd 10" "c3 schur 10" "c4 metis 5"; do
   set -- $cfg
-  python bench.py --workload $1 --ordering $2 --steps 10 > gpurun_out/bench_$1_$2.json 2> gpurun_out/bench_$1_$2.err
+  python bench.py --workload $1 --ordering $2 --steps $3 > $O/bench_$1_$2.json 2> $O/bench_$1_$2.err
 done
-GTB_DEBUG=8 python tools/launch_trace.py c3 metis > gpurun_out/launch_trace_c3_metis.txt 2>&1
-if [ -n "$FULL" ]; then
-  timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 3000 --csv \
-    --log-file gpurun_out/ncu_launches_c3_metis.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
-  gzip -f gpurun_out/ncu_launches_c3_metis.csv
-fi
-cat gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log
-for f in gpurun_out/bench_c*_*.json; do python - "$f" <<'P'
+GTB_DEBUG=8 python tools/launch_trace.py c3 metis > $O/launch_trace_c3_metis.txt 2>&1
+python tools/level_times.py c3 metis > $O/level_times_c3_metis.txt 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 3000 --csv \
+  --log-file $O/ncu_launches_c3_metis.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_launches.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'front_step_kernel|schur_step_kernel' -s 160 -c 24 -o $O/ncu_full_c3 \
+  python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $O/ncu_full.log 2>&1
+cat $O/pytest_gpu.log | tail -6; tail -2 $O/smoke.log
+for f in $O/bench_c*.json; do python - "$f" <<'P'
 import json,sys
 try:
     d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1]); print(sys.argv[1], d["value"], d["ms_per_step"], d.get("e2e",{}).get("value"), d.get("cpu_baseline",{}).get("value"))

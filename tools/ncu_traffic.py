@@ -33,10 +33,14 @@ def main(path, out):
         agg[k][2] += ms.get("dram__bytes_write.sum", 0.0)
     res = {k: {"launches": n, "dram_read_bytes_per_launch": r / n, "dram_write_bytes_per_launch": w / n,
                "traffic_bytes_per_launch": (r + w) / n} for k, (n, r, w) in agg.items()}
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    res["_source_digest"] = bench.source_digest()   # bench.py quotes the file only for this build of the kernels
     res["_source"] = "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum over every launch of `bench.py --steps 2 --warmup 1` (C3, METIS)"
     json.dump(res, open(out, "w"), indent=1, sort_keys=True)
     for k, v in sorted(res.items()):
-        if k != "_source":
+        if not k.startswith("_"):
             print(f"{k:18s} {v['launches']:5d} launches  {v['traffic_bytes_per_launch'] / 1e6:10.3f} MB / launch")
 
 
