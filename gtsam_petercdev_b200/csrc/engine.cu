@@ -707,7 +707,9 @@ static double front_cost(const Plan& p, int32_t c) {
 // fronts), then the top fronts are reduced and rank 0 walks the top.  Constants are the measured C3 figures
 // (DESIGN.md section 4); only the ranking of candidate cuts matters.
 static double modelled_time(const Plan& p, const std::vector<int32_t>& owner, int world) {
-  const double tau = 30e-6, rate = 6e12, t_small = 25e-9, bw = 3e11;
+  // r02 calibration (profiles/r02): a panel step 23 us, Schur tiles 12 TFLOP/s sustained, 4 ns per point clique (the whole
+  // point path of C3 is 0.63 ms for 156 k points), fan-in reduce ~300 GB/s (119 MB in 0.4 ms at 8 ranks)
+  const double tau = 23e-6, rate = 12e12, t_small = 4e-9, bw = 3e11;
   const int L = p.n_levels, G = world + 1;
   std::vector<double> flops((size_t)G * L, 0.0), steps((size_t)G * L, 0.0), smalls((size_t)G * L, 0.0);
   double reduce_bytes = 0;
@@ -1578,9 +1580,12 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
 
 // the failure flag of the factorisation just enqueued, as a double in d_scalars[8] (agreed over the ranks: every rank must
 // take the same branch of the LM control flow); nothing is read back here
-static void enqueue_fail_flag(Engine* e) {
+// ride = true (a whole trial with several ranks): no collective here; the flag rides on the delta all-reduce of the
+// back-substitution as a count of failing ranks (backsolve), and the ranks only agree on the failing clique when that
+// count is not zero -- one collective less in every trial.
+static void enqueue_fail_flag(Engine* e, bool ride = false) {
   LAUNCH(e, K_REDUCE, fail_flag_kernel<<<1, 1, 0, e->stream>>>(e->d_fail.p, e->d_scalars.p + 8));
-  if (e->world > 1) comm(e, GTB_COMM_ALLREDUCE_MIN, e->d_scalars.p + 8, 1);
+  if (e->world > 1 && !ride) comm(e, GTB_COMM_ALLREDUCE_MIN, e->d_scalars.p + 8, 1);
 }
 
 // returns failing clique id or -1; defer = true: returns -1 at once, the flag is left in d_scalars[8] (enqueue_fail_flag)
@@ -1638,7 +1643,7 @@ static int32_t factorize(Engine* e, double lambda, int diag, double lo, double h
     comm(e, GTB_COMM_REDUCE_SUM_TO_0, e->d_arena.p + e->top_off, e->top_doubles);
     if (e->rank == 0) factorize_levels(e, E, 1);
   }
-  enqueue_fail_flag(e);
+  enqueue_fail_flag(e, defer);
   if (defer) {
     tm.stop();
     e->factorized = true;   // provisional: the caller checks the flag after its single sync
@@ -1695,8 +1700,10 @@ static void backsolve(Engine* e) {
   backsolve_levels(e, E, 0);
   if (e->world > 1) {
     const int n = (int)e->n_scalars;
-    LAUNCH(e, K_OWNDELTA, own_delta_kernel<<<(n + 255) / 256, 256, 0, e->stream>>>(n, e->d_delta.p, e->d_own_mask.p, e->d_delta_own.p));
-    comm(e, GTB_COMM_ALLREDUCE_SUM, e->d_delta_own.p, e->n_scalars);
+    // entry n of the summed vector: how many ranks saw their factorisation fail (d_scalars[8] holds this rank's flag)
+    LAUNCH(e, K_OWNDELTA, own_delta_kernel<<<(n + 1 + 255) / 256, 256, 0, e->stream>>>(n, e->d_delta.p, e->d_own_mask.p, e->d_delta_own.p,
+                                                                                      e->d_scalars.p + 8));
+    comm(e, GTB_COMM_ALLREDUCE_SUM, e->d_delta_own.p, e->n_scalars + 1);
     CK(cudaMemcpyAsync(e->d_delta.p, e->d_delta_own.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
   }
   tm.stop();
@@ -1825,7 +1832,15 @@ static TrialResult trial(Engine* e, double lambda, int diag, double lo, double h
   retract(e);
   nonlinear_error(e, 1, 2);
   CK(cudaMemcpyAsync(e->h_scalars, e->d_scalars.p, 9 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  if (e->world > 1)
+    CK(cudaMemcpyAsync(e->h_scalars + 9, e->d_delta_own.p + e->n_scalars, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
   CK(cudaStreamSynchronize(e->stream));
+  if (e->world > 1 && e->h_scalars[9] > 0.0) {
+    // some rank failed (every rank sees the same count): agree on the first failing clique, as the reference would report
+    comm(e, GTB_COMM_ALLREDUCE_MIN, e->d_scalars.p + 8, 1);
+    CK(cudaMemcpyAsync(e->h_scalars + 8, e->d_scalars.p + 8, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+  }
   TrialResult r;
   r.fail = e->h_scalars[8] >= (double)INT_MAX ? -1 : (int32_t)e->h_scalars[8];
   r.lin0 = e->h_scalars[0]; r.lin1 = e->h_scalars[1]; r.err = e->h_scalars[2];

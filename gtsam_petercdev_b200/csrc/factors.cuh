@@ -706,9 +706,11 @@ __global__ void damping_kernel(int n, double s, int diag_mode, double lo, double
 // Several ranks: keep the entries of delta this rank solved for and clear the rest, so that a sum over ranks rebuilds
 // the whole vector exactly (every entry has one owner).
 __global__ void __launch_bounds__(256)
-own_delta_kernel(int n, const double* __restrict__ delta, const uint8_t* __restrict__ own, double* __restrict__ out) {
+own_delta_kernel(int n, const double* __restrict__ delta, const uint8_t* __restrict__ own, double* __restrict__ out,
+                 const double* __restrict__ fail_flag) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = own[i] ? delta[i] : 0.0;
+  else if (i == n) out[n] = (*fail_flag < 2147483647.0) ? 1.0 : 0.0;   // this rank's factorisation failed (INT_MAX = no failure)
 }
 
 // Values::retract (nonlinear/Values.cpp:53-63): one thread per variable of one type.

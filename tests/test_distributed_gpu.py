@@ -99,3 +99,30 @@ def test_lm_takes_the_same_path_on_every_rank(name, mode, ordering, extra, tag, 
         assert out[r]["inner_iterations"] == int(g["inner_iterations"][0])
         assert abs(out[r]["final_error"] - g["final_error"][0]) <= 1e-6 * g["final_error"][0]
     assert out[0]["final_error"] == out[1]["final_error"]
+
+
+def test_a_failed_factorisation_is_agreed_across_ranks(force_top):
+    """A whole trial (gtb_trial) carries the failure flag on the delta all-reduce; when any rank's factorisation fails, every
+    rank raises IndeterminantLinearSystemException with the same key, and a damped trial afterwards succeeds everywhere."""
+    from gtsam_petercdev_b200.engine import IndeterminantLinearSystemException
+    from gtsam_petercdev_b200.problem import Problem
+    p0 = golden_problem("ba_60_2000")
+    a = {k: v for k, v in p0.a.items() if not k.startswith("prior")}   # gauge freedom: undamped elimination must fail
+    g = load_golden("ba_60_2000__solve_metis_0.0001_1")
+
+    def body(r, cb):
+        e = Engine(Problem(a), device=0)
+        e.set_distributed(r, 2, cb)
+        e.set_ordering(g["ordering"])
+        e.linearize()
+        key = None
+        try:
+            e.trial(0.0)
+        except IndeterminantLinearSystemException as ex:
+            key = ex.key
+        ok = e.trial(1e-3)
+        return key, ok
+
+    out, _ = run_ranks(2, body)
+    assert out[0][0] is not None and out[0][0] == out[1][0]
+    assert out[0][1] == out[1][1] and np.all(np.isfinite(out[0][1]))
