@@ -1661,6 +1661,43 @@ diag_inverse_kernel(ElimDev E, const int32_t* __restrict__ tasks, int count, dou
   for (int k = 0; k < 32; ++k) out[k * 32 + lane] = u[k * 33 + lane];
 }
 
+// Point cliques with at most 8 cameras, four per warp (8 lanes each): x_F = R^-1 (d - S x_S) over the three conditional rows
+// stored as one 32-byte column per separator scalar.  A warp per point leaves three quarters of its lanes idle on the 9 k <=
+// 72 columns of such a point; this is the bulk of the cliques of a bundle-adjustment problem (C4: 993 k of them).
+__global__ void __launch_bounds__(kBsWarps * 32)
+backsolve_points_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta) {
+  constexpr int LPP = 8;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sl = lane % LPP, sw = lane / LPP;
+  const int slot = (blockIdx.x * kBsWarps + warp) * (32 / LPP) + sw;
+  pdl_trigger();
+  const bool active = slot < count;
+  const CliqueDev ci = E.cliques[list[active ? slot : count - 1]];   // idle groups shadow the last point: the warp stays converged
+  pdl_wait();
+  const int S = ci.S;
+  const double* A = E.arena + ci.front_off;
+  const int32_t* g = E.gidx + ci.gidx_off;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+#pragma unroll 3
+  for (int j = sl; j < S; j += LPP) {
+    const double x = delta[g[3 + j]];
+    const Col4 col = ld_col(A + (int64_t)(3 + j) * 4);
+    a0 += col.x * x; a1 += col.y * x; a2 += col.z * x;
+  }
+#pragma unroll
+  for (int o = LPP / 2; o > 0; o >>= 1) {
+    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+    a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+  }
+  if (active && sl == 0) {
+    const double* d = A + (int64_t)(3 + S) * 4;
+    const double x2 = (d[2] - a2) * (1.0 / A[2 + 2 * 4]);
+    const double x1 = (d[1] - a1 - A[1 + 2 * 4] * x2) * (1.0 / A[1 + 1 * 4]);
+    const double x0 = (d[0] - a0 - A[0 + 1 * 4] * x1 - A[0 + 2 * 4] * x2) * (1.0 / A[0]);
+    delta[g[0]] = x0; delta[g[1]] = x1; delta[g[2]] = x2;
+  }
+}
+
 template <bool WARP>
 __global__ void __launch_bounds__(WARP ? kBsWarps * 32 : kBsCtaThreads)
 backsolve_kernel(ElimDev E, const int32_t* __restrict__ list, int count, double* __restrict__ delta,

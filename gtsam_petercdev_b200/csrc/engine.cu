@@ -81,6 +81,7 @@ struct LevelSched {
   int32_t n_all = 0;          // all cliques at the level (back-substitution)
   int64_t bs_begin = 0;       // into the back-substitution list: warp-class cliques first, then CTA-class
   int32_t n_bs_warp = 0, n_bs_cta = 0, bs_cta_smem = 0;
+  int32_t n_bs_pt = 0;        // leading part of the warp class: point cliques with <= 8 cameras (four per warp)
   int32_t bs_max_F = 0, bs_max_S = 0;   // CTA class: grid of the partial-GEMV kernel
   int64_t zero_blocks = 0;
   std::vector<int64_t> step_begin;  // per panel step 0..max_np: range of the compact task list (panel-step tasks)
@@ -943,12 +944,14 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
     L.n_gather = (int32_t)(e->gather_work.size() - L.gather_begin);
     L.bs_begin = (int64_t)e->bs_list.size();
     int32_t maxN = 0;
-    for (int pass = 0; pass < 2; ++pass)
+    for (int pass = 0; pass < 3; ++pass)
       for (int64_t q = b; q < en; ++q) {
         const int32_t c = lc[q];
         const bool warp_class = (p.F[c] <= 32 && p.F[c] + p.S[c] + 1 <= kDenseMaxDim) || e->is_point[c];
-        if (warp_class != (pass == 0)) continue;
+        const bool pt8 = e->is_point[c] && p.S[c] <= 72;   // (is_point: handled by the point path, conditional rows with ld = 4)
+        if ((pass == 0) != pt8 || (pass < 2) != warp_class) continue;
         e->bs_list.push_back(c);
+        if (pt8) L.n_bs_pt++;
         if (warp_class) L.n_bs_warp++;
         else {
           L.n_bs_cta++;
@@ -1671,10 +1674,13 @@ static void backsolve_levels(Engine* e, const ElimDev& E, int phase) {
     const int32_t* bl = e->d_bs_list.p + L.bs_begin;
     const int32_t* so = e->d_bs_scratch_off.p + L.bs_begin;
     const int32_t* ro = e->d_bs_rinv_off.p + L.bs_begin;
-    if (L.n_bs_warp)
-      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<true>, (L.n_bs_warp + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
-                                        kBsWarps * kBsWarpDoubles * sizeof(double), e->stream, E, bl, L.n_bs_warp, e->d_delta.p,
-                                        so, (const double*)e->d_bs_scratch.p, ro, (const double*)e->d_bs_rinv.p));
+    if (L.n_bs_pt)
+      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_points_kernel, (L.n_bs_pt + 4 * kBsWarps - 1) / (4 * kBsWarps), kBsWarps * 32, 0, e->stream, E,
+                                        bl, L.n_bs_pt, e->d_delta.p));
+    if (L.n_bs_warp > L.n_bs_pt)
+      LAUNCH(e, K_BACKSOLVE, launch_pdl(backsolve_kernel<true>, (L.n_bs_warp - L.n_bs_pt + kBsWarps - 1) / kBsWarps, kBsWarps * 32,
+                                        kBsWarps * kBsWarpDoubles * sizeof(double), e->stream, E, bl + L.n_bs_pt, L.n_bs_warp - L.n_bs_pt, e->d_delta.p,
+                                        so + L.n_bs_pt, (const double*)e->d_bs_scratch.p, ro + L.n_bs_pt, (const double*)e->d_bs_rinv.p));
     if (L.n_bs_cta) {
       if (L.bs_max_S > 0)
         LAUNCH(e, K_BSGEMV, launch_pdl(backsolve_gemv_kernel,
@@ -2207,6 +2213,7 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
         if (p.level[c] != l || !mine(c)) return fail("foreign clique in a back-substitution list");
         const bool warp_class = (p.F[c] <= 32 && dim_of(c) <= kDenseMaxDim) || e->is_point[c];
         if (warp_class != (k < L.bs_begin + L.n_bs_warp)) return fail("back-substitution class of clique " + std::to_string(c));
+        if ((e->is_point[c] && p.S[c] <= 72) != (k < L.bs_begin + L.n_bs_pt)) return fail("point class of the back-substitution list");
         if (warp_class && !e->is_point[c] && p.S[c] > 160) return fail("warp-class conditional wider than its shared memory");
         if (!warp_class) {
           if ((int64_t)(p.F[c] + p.S[c] + kBsCtaThreads + 64 + 2 * 32 * 33) * 8 > L.bs_cta_smem || L.bs_cta_smem > 200 * 1024) return fail("back-substitution shared memory");
@@ -2221,7 +2228,7 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
         seen_bs[c]++;
       }
       if (L.n_bs_warp + L.n_bs_cta != L.n_all) return fail("back-substitution count at level " + std::to_string(l));
-      cnt[3] += (L.n_bs_warp > 0) + (L.n_bs_cta > 0) * (1 + (L.bs_max_S > 0));
+      cnt[3] += (L.n_bs_pt > 0) + (L.n_bs_warp > L.n_bs_pt) + (L.n_bs_cta > 0) * (1 + (L.bs_max_S > 0));
       // camera-pair segments of the level's point cliques
       for (int pass = 0; pass < 2; ++pass) {
         const int64_t sb = pass ? L.diag_seg_begin : L.pair_seg_begin, sn = pass ? L.n_diag_seg : L.n_pair_seg;
