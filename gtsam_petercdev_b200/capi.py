@@ -25,6 +25,11 @@ class LMResult(C.Structure):
                 ("iterations", C.c_int32), ("inner_iterations", C.c_int32), ("log_rows", C.c_int32)]
 
 
+class ISAM2Result(C.Structure):
+    _fields_ = [("update_count", C.c_int64), ("variables_relinearized", C.c_int64), ("n_variables", C.c_int64),
+                ("n_factors", C.c_int64), ("n_cliques", C.c_int64), ("plan_ms", C.c_double), ("solve_ms", C.c_double)]
+
+
 _P = C.c_void_p
 _SIGS = {
     "gtb_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
@@ -89,6 +94,17 @@ _SIGS = {
     "gtb_dataset_factor_noise": (_P, [_P, C.c_int]),
     "gtb_dataset_robust": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "gtb_dataset_apply": (C.c_int, [_P, _P]),
+    "gtb_relinearize_marked": (C.c_int, [_P, C.c_double, _P, C.POINTER(C.c_int64)]),
+    "gtb_isam2_create": (C.c_int, [C.c_int, C.c_double, C.c_int32, C.POINTER(_P)]),
+    "gtb_isam2_destroy": (None, [_P]),
+    "gtb_isam2_last_error": (C.c_char_p, [_P]),
+    "gtb_isam2_add_variables": (C.c_int, [_P, C.c_int, C.c_int64, _P, _P]),
+    "gtb_isam2_add_factors": (C.c_int, [_P, C.c_int, C.c_int64, _P, _P, _P, _P]),
+    "gtb_isam2_set_ordering": (C.c_int, [_P, C.c_int64, _P]),
+    "gtb_isam2_update": (C.c_int, [_P, C.POINTER(ISAM2Result), C.POINTER(C.c_uint64)]),
+    "gtb_isam2_estimate": (C.c_int, [_P, C.c_int, _P]),
+    "gtb_isam2_count": (C.c_int64, [_P, C.c_int]),
+    "gtb_isam2_engine": (_P, [_P]),
     "gtb_noalloc_setup": (C.c_int, [C.c_int]),
     "gtb_bucket_error_noalloc": (C.c_int, [C.c_int, C.c_int, C.c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gtb_noalloc_last_error": (C.c_char_p, []),

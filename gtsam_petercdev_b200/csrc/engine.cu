@@ -23,18 +23,9 @@
 #include "marginals.cuh"
 #include "factors.cuh"
 #include "plan.h"
+#include "layout.h"
 
 namespace gtb {
-
-static const int kZIn[7] = {3, 12, 2, 3, 12, 17, 3};       // measurement doubles per factor as given by the caller
-static const int kZDev[7] = {4, 12, 2, 4, 12, 17, 3};      // ... as kept on the device (Pose2 -> cos, sin, x, y)
-static const int kM[7] = {3, 6, 2, 3, 6, 9, 3};
-static const int kW[7] = {7, 13, 13, 4, 7, 10, 4};
-static const int kNKeys[7] = {2, 2, 2, 1, 1, 1, 1};
-static const int kVT[7][2] = {{0, 0}, {1, 1}, {2, 3}, {0, -1}, {1, -1}, {2, -1}, {3, -1}};
-static const int kStateIn[4] = {3, 12, 17, 3};
-static const int kStateDev[4] = {4, 12, 17, 3};
-static const int kDim[4] = {3, 6, 9, 3};
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
 #define CK(call)                                                                                   \
@@ -870,6 +861,18 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
             for (int t = lo; t < hi; ++t) e->step_tasks_list.push_back(StepTask{c, t});
           }
         L.step_count.push_back((int32_t)(e->step_tasks_list.size() - L.step_begin.back()));
+        if (getenv("GTB_DUMP_STEPS")) {   // composition of this panel-step launch (planning aid, tools/step_mix.py)
+          int nf = 0, na = 0, maxdim = 0, maxF = 0;
+          for (int64_t q = L.large_begin; q < en; ++q) {
+            const int32_t c = lc[q];
+            const int F = p.F[c], dim = F + p.S[c] + 1;
+            if (sidx >= (F + PW - 1) / PW) continue;
+            const int k0 = sidx * PW, kb = std::min(PW, F - k0);
+            ++nf; na += (dim - k0 - kb + SLICE - 1) / SLICE; maxdim = std::max(maxdim, dim); maxF = std::max(maxF, F);
+          }
+          fprintf(stderr, "step level=%d p=%d fronts=%d roleA=%d tiles=%d maxF=%d maxdim=%d\n", (int)l, sidx, nf, na,
+                  (int)L.step_count.back() - na, maxF, maxdim);
+        }
         L.schur_begin.push_back((int64_t)e->step_tasks_list.size());
         // a launch with fewer tiles than the machine holds (2 CTAs per SM) splits K = F over several CTAs per tile
         int64_t launch_tiles = 0;
@@ -1816,6 +1819,14 @@ template <int VT> static void launch_retract(Engine* e) {
   LAUNCH(e, K_RETRACT, retract_kernel<VT><<<(n + 127) / 128, 128, 0, e->stream>>>(n, e->d_state[e->cur][VT].p, e->d_type_goff[VT].p,
                                                              e->d_delta.p, e->d_state[e->cur ^ 1][VT].p));
 }
+template <int VT> static void launch_relinearize(Engine* e, double threshold, uint8_t* d_marks, int* d_count) {
+  const int n = (int)e->vars[VT].n;
+  if (!n) return;
+  relinearize_marked_kernel<VT><<<(n + 127) / 128, 128, 0, e->stream>>>(n, e->d_type_goff[VT].p, e->d_delta.p, threshold,
+                                                                        e->d_state[e->cur ^ 1][VT].p, e->d_state[e->cur][VT].p, d_marks,
+                                                                        d_count);
+  CK(cudaGetLastError());
+}
 static void retract(Engine* e) {
   need_device(e);
   need(e->solved, "gtb_retract needs gtb_backsolve first");
@@ -2490,6 +2501,33 @@ gtb_status gtb_accept(gtb_engine* e) {
   need(e->retracted, "gtb_accept needs gtb_retract since the last gtb_linearize / gtb_accept / gtb_set_variables");
   e->cur ^= 1;
   e->linearized = e->factorized = e->solved = e->have_hdiag = e->retracted = false;
+  e->lm_have_error = false;
+  GTB_CATCH(e)
+}
+gtb_status gtb_relinearize_marked(gtb_engine* e, double threshold, uint8_t* marks, int64_t* n_marked) {
+  if (!e) return GTB_ERR_INVALID;
+  GTB_TRY(e)
+  need_device(e);
+  need(e->retracted, "gtb_relinearize_marked needs gtb_retract first: the marked variables take their retracted values");
+  need(e->world == 1, "gtb_relinearize_marked: single rank only");
+  int64_t off[5] = {0, 0, 0, 0, 0};
+  for (int t = 0; t < 4; ++t) off[t + 1] = off[t] + e->vars[t].n;
+  DevBuf<uint8_t> d_marks;
+  DevBuf<int> d_count;
+  d_marks.alloc((size_t)off[4] + 1);
+  d_count.alloc(1);
+  CK(cudaMemsetAsync(d_count.p, 0, sizeof(int), e->stream));
+  launch_relinearize<0>(e, threshold, d_marks.p + off[0], d_count.p);
+  launch_relinearize<1>(e, threshold, d_marks.p + off[1], d_count.p);
+  launch_relinearize<2>(e, threshold, d_marks.p + off[2], d_count.p);
+  launch_relinearize<3>(e, threshold, d_marks.p + off[3], d_count.p);
+  int count = 0;
+  CK(cudaMemcpyAsync(&count, d_count.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  if (marks && off[4]) CK(cudaMemcpyAsync(marks, d_marks.p, (size_t)off[4], cudaMemcpyDeviceToHost, e->stream));
+  CK(cudaStreamSynchronize(e->stream));
+  if (n_marked) *n_marked = count;
+  // the current values moved: everything computed from them is stale
+  if (count) e->linearized = e->factorized = e->solved = e->have_hdiag = e->retracted = false;
   e->lm_have_error = false;
   GTB_CATCH(e)
 }

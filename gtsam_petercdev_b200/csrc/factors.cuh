@@ -748,4 +748,28 @@ retract_kernel(int n, const double* __restrict__ cur, const int32_t* __restrict_
   }
 }
 
+// ISAM2's fluid relinearisation (nonlinear/ISAM2.cpp:456-468, ISAM2-impl.h:341-351 CheckRelinearizationFull): a variable
+// whose |delta|_inf reaches the threshold moves its linearisation point, theta_j := theta_j (+) delta_j
+// (Values::retractMasked).  `retracted` already holds theta (+) delta of every variable (retract_kernel), so the marked rows
+// are copied.  One thread per variable of one type.
+template <int VT>
+__global__ void __launch_bounds__(128)
+relinearize_marked_kernel(int n, const int32_t* __restrict__ goff, const double* __restrict__ delta, double threshold,
+                          const double* __restrict__ retracted, double* __restrict__ cur, uint8_t* __restrict__ marks,
+                          int* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  constexpr int dim = VT == 0 ? 3 : VT == 1 ? 6 : VT == 2 ? 9 : 3;
+  const double* d = delta + goff[i];
+  double m = 0.0;
+#pragma unroll
+  for (int k = 0; k < dim; ++k) m = fmax(m, fabs(d[k]));
+  const bool mark = m >= threshold;
+  if (marks) marks[i] = mark ? 1 : 0;
+  if (!mark) return;
+#pragma unroll
+  for (int k = 0; k < state_size(VT); ++k) cur[(int64_t)i * state_size(VT) + k] = retracted[(int64_t)i * state_size(VT) + k];
+  atomicAdd(count, 1);
+}
+
 }  // namespace gtb

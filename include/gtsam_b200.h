@@ -245,6 +245,56 @@ gtb_status gtb_write_g2o(const char* path, int64_t n_pose2, const uint64_t* pose
 gtb_status gtb_marginals_compute(gtb_engine* e);
 gtb_status gtb_marginal_covariance(gtb_engine* e, int64_t n, const uint64_t* keys, double* out);
 
+/* ---- ISAM2 update ---------------------------------------------------------------
+ * gtsam::ISAM2::update(newFactors, newTheta) + calculateEstimate() (nonlinear/ISAM2.cpp:401-480, 725-784) for the
+ * Gauss-Newton configuration of examples/ISAM2_City10000.cpp:62-68 (ISAM2GaussNewtonParams(0.0): wildfire threshold 0, so
+ * every update ends in a complete back-substitution and delta is the exact solution of the current linear system).
+ * What is kept of the reference: the split of the estimate into a linearisation point theta and a delta, fluid
+ * relinearisation (a variable moves its linearisation point only when |delta_j|_inf >= relinearize_threshold, checked every
+ * relinearize_skip updates, ISAM2-impl.h:341-351; the check and the masked retract run on the device:
+ * gtb_relinearize_marked), factors linearised at theta (what the reference's cached linear factors amount to,
+ * ISAM2.cpp:176-230), new variables entering with delta = 0.  With that the estimate after every update equals the
+ * reference's (tests/test_isam2_gpu.py: 1e-9 on tests/golden/isam2__city10000_200loops.npz).
+ * What is NOT kept: the reference re-eliminates only the top of the Bayes tree that the new factors and the relinearised
+ * variables touch and re-uses the orphaned subtrees (ISAM2.cpp:117-175, 250-363); this layer re-plans and re-eliminates the
+ * WHOLE system on the device at every update (batch engine underneath), so an update costs one symbolic analysis on the
+ * host plus one multifrontal factorisation, not work proportional to the affected part.  DESIGN.md 8 says what an
+ * incremental plan would take.
+ * Usage: stage the new variables and factors (same row layouts as gtb_set_variables / gtb_set_factors; a key may be staged
+ * once), then gtb_isam2_update.  Ordering: gtb_isam2_set_ordering gives an elimination order for the variables known so
+ * far (the reference computes a constrained COLAMD per update, ISAM2.cpp:301-340; any order gives the same estimate);
+ * variables that are not listed are eliminated last in the order they were added.  Without it: ascending keys.      */
+typedef struct gtb_isam2 gtb_isam2;
+typedef struct {
+  int64_t update_count;            /* ISAM2::update_count_                                            */
+  int64_t variables_relinearized;  /* variables that moved their linearisation point in this update   */
+  int64_t n_variables, n_factors;  /* totals after the update                                         */
+  int64_t n_cliques;               /* cliques of the Bayes tree of this update                        */
+  double plan_ms;                  /* host: engine set-up + symbolic analysis                         */
+  double solve_ms;                 /* device: linearise + factorise + back-substitute + retract, with the sync */
+} gtb_isam2_result;
+gtb_status gtb_isam2_create(int device, double relinearize_threshold, int32_t relinearize_skip, gtb_isam2** out);
+void gtb_isam2_destroy(gtb_isam2* s);
+const char* gtb_isam2_last_error(const gtb_isam2* s);
+gtb_status gtb_isam2_add_variables(gtb_isam2* s, int vtype, int64_t n, const uint64_t* keys, const double* state);
+gtb_status gtb_isam2_add_factors(gtb_isam2* s, int bucket, int64_t n, const uint64_t* keys, const double* z,
+                                 const int32_t* noise_kind, const double* noise);
+gtb_status gtb_isam2_set_ordering(gtb_isam2* s, int64_t n, const uint64_t* keys);
+/* Commits what was staged and runs the update.  GTB_ERR_INDETERMINATE + *failed_key as gtb_factorize (the staged
+ * additions stay committed, as in the reference, whose update throws after pushing the factors).              */
+gtb_status gtb_isam2_update(gtb_isam2* s, gtb_isam2_result* result, uint64_t* failed_key);
+/* calculateEstimate(): theta (+) delta for every variable of one type, in the order the variables were added, device
+ * row layout (gtb_get_variables).  n = number of variables of that type (gtb_isam2_count).                    */
+gtb_status gtb_isam2_estimate(gtb_isam2* s, int vtype, double* state);
+int64_t gtb_isam2_count(const gtb_isam2* s, int vtype);
+/* The batch engine of the last update (linearised at theta, factorised, solved): gtb_get_delta, gtb_get_conditionals,
+ * gtb_marginals_compute ... work on it.  Owned by the ISAM2 object, replaced by the next update.             */
+gtb_engine* gtb_isam2_engine(gtb_isam2* s);
+/* ISAM2 steps 4 and 6 on the device (ISAM2.cpp:456-468): every variable of `e` with |delta_j|_inf >= threshold takes its
+ * retracted value as the new current value (Values::retractMasked).  Needs gtb_retract.  marks (may be NULL): one byte
+ * per variable, types concatenated POSE2, POSE3, CAMERA, POINT3 in upload order.                              */
+gtb_status gtb_relinearize_marked(gtb_engine* e, double threshold, uint8_t* marks, int64_t* n_marked);
+
 /* ---- several GPUs: one engine per process / GPU ---------------------------------------------
  * The reference parallelises elimination over the children of a clique with TBB tasks
  * (inference/ClusterTree-inst.h:286-318).  Across GPUs the same tree is cut instead: every rank holds the whole

@@ -74,3 +74,33 @@ def test_unconnected_variable_is_inconsistent():
     with pytest.raises(EngineError) as ei:
         e.set_ordering("natural")
     assert ei.value.status == capi.ERR_INCONSISTENT
+
+
+def test_isam2_layer_host_side():
+    """gtb_isam2_*: argument checks and staging work without a device; the update itself needs one and says so."""
+    import numpy as np
+    from gtsam_petercdev_b200.engine import EngineError
+    from gtsam_petercdev_b200.isam2 import ISAM2
+    with pytest.raises(EngineError):
+        ISAM2(relinearize_threshold=-1.0)
+    with pytest.raises(EngineError):
+        ISAM2(relinearize_skip=0)
+    s = ISAM2(0.01, 1, device=-1)
+    x = lambda i: (ord("x") << 56) | i
+    s.add_variables("pose2", [x(0)], [[0.0, 0.0, 0.0]])
+    with pytest.raises(EngineError, match="already exists"):
+        s.add_variables("pose2", [x(0)], [[1.0, 0.0, 0.0]])
+    s.add_factors("prior2", [x(0)], [[0.0, 0.0, 0.0]], 2, [[1e-4, 1e-4, 1e-4]])
+    assert s.count("pose2") == 0                      # staged, not committed
+    with pytest.raises(EngineError) as ei:
+        s.update()
+    assert ei.value.status == capi.ERR_NO_DEVICE
+    assert s.count("pose2") == 1                      # the additions stay committed, as in the reference
+    with pytest.raises(EngineError):
+        s.calculate_estimate("pose2")
+    # a factor on an unknown key is refused by the engine at the update
+    s.add_factors("between2", [[x(0), x(7)]], [[1.0, 0.0, 0.0]])
+    with pytest.raises(EngineError) as ei:
+        s.update()
+    assert ei.value.status == capi.ERR_KEY_MISSING
+    s.close()

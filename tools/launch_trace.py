@@ -35,10 +35,11 @@ if os.environ.get("GTB_DEBUG") and int(os.environ["GTB_DEBUG"]) & 8:
     e.lib.gtb_debug_read.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     e.lib.gtb_debug_read(e.h, buf)
     b = list(buf)
-    names = {1: "loads + sync", 2: "D -= PtP + sync", 3: "potrf 0 + inverses", 4: "T solve + D11 update", 5: "potrf 1 + inverses"}
-    print("role A cycle stamps (root, p=2, slice 0), warp 0:")
-    for k in range(1, 6):
-        print("  %-24s %7d" % (names[k], b[k] - b[k - 1]))
+    print("role A cycle stamps (root, p=2, slice 0), warp 0, cycles from kernel entry:")
+    print("  loads + sync               %7d" % (b[1] - b[0]))
+    print("  D -= PtP + sync            %7d" % (b[2] - b[1]))
+    print("  first 8 x 8 block factored %7d" % (b[3] - b[2]))
+    print("  64 x 64 Cholesky + inverses%7d" % (b[5] - b[2]))
     print("column warp 1: X update done at %d, released at %d, solve %d, store %d (cycles from kernel start)" % (
         b[8] - b[0], b[9] - b[0], b[10] - b[9], b[11] - b[10]))
     print("schur step of the root's last child: tile 0 %d cycles (%d ns), tile 77 %d cycles (%d ns)" % (b[12], b[13], b[14], b[15]))
