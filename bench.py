@@ -33,7 +33,9 @@ WORKLOADS = {
     "c2": "C2 sphere2500-shape Pose3 graph (2,500 Pose3, 4,949 BetweenFactor<Pose3> + prior)",
     "c1": "C1 M3500-shape Pose2 graph (3,500 Pose2, 5,450 BetweenFactor<Pose2> + prior)",
     "c4": "C4 Venice-scale synthetic BA (1,778 cams, ~993,000 points, ~5M GeneralSFMFactor<Cal3Bundler> + 2 priors)",
+    "c5": "C5 ISAM2 on City10000 (examples/ISAM2_City10000.cpp schedule: one update per measurement line, relinearizeThreshold 0.01, relinearizeSkip 1)",
 }
+CITY_FULL = os.path.join(ROOT, "tests", "golden", "data", "T1_city10000_04.txt")
 DGEMM_FP64_TFLOPS = 35.46   # cuBLAS fp64 8192^3 measured on this pool's B200 (tools/probe_box.py, profiles/probe_r01.json)
 
 
@@ -53,7 +55,7 @@ def make_problem(workload):
 def ordering_for(problem, workload, name):
     """Ordering keys, or a builtin name.  COLAMD / METIS orderings are the reference's own (computed once by
     oracle/_ref/ref_tool, committed as permutations under tests/golden/): ordering is an input of the path."""
-    if name in ("schur", "natural"):
+    if name in ("schur", "natural", "nested_dissection"):
         return name
     f = os.path.join(ROOT, "tests", "golden", {"c3": "ladybug_shape", "c2": "sphere_shape", "c1": "m3500_shape", "c4": "venice_shape"}[workload] + "_orderings.npz")
     perm = np.load(f)[name]
@@ -188,6 +190,91 @@ def run_reference(args, rank, world):
     emit(base)
 
 
+def isam2_reference(lines, loops_hint=None):
+    """The reference's own gtsam::ISAM2 on the first `lines` lines (oracle/_ref/ref_tool mode=isam2), seconds per update."""
+    from gtsam_petercdev_b200 import gtbio
+    tool = os.path.join(ROOT, "oracle", "_ref", "ref_tool")
+    if not os.path.exists(tool):
+        return None
+    tmp = tempfile.mkdtemp()
+    head = os.path.join(tmp, "head.txt")
+    with open(CITY_FULL) as f, open(head, "w") as g:
+        for i, line in enumerate(f):
+            if i >= lines:
+                break
+            g.write(line)
+    out = os.path.join(tmp, "o.gtb")
+    subprocess.run([tool, head, out, "mode=isam2", "every=1000000"], check=True)
+    return np.asarray(gtbio.load(out)["update_seconds"], dtype=np.float64)
+
+
+def latency_stats(ms):
+    ms = np.asarray(ms, dtype=np.float64)
+    return {"mean": float(ms.mean()), "median": float(np.median(ms)), "p99": float(np.percentile(ms, 99)), "max": float(ms.max()),
+            "last_100_mean": float(ms[-100:].mean())}
+
+
+def run_isam2(args, reference_arm):
+    """--workload c5: per-update latency of the ISAM2 layer (gtb_isam2_update + read-back of the estimate, host buffers, through
+    the C ABI) over the first --updates lines of City10000, beside the reference's gtsam::ISAM2 on the same lines on this
+    host.  A step = one update; value = updates per second over the whole run (wall clock: the update is host-driven)."""
+    lines = args.updates
+    cfg = {"workload": WORKLOADS["c5"], "updates": lines, "ordering": "built-in nested dissection, recomputed per update (device arm); "
+           "constrained COLAMD per update (reference arm)"}
+    base = {"metric": "ISAM2 updates/s (City10000 schedule)", "unit": "updates/s", "n_gpus": 1, "higher_is_better": True, "scaling": "n/a",
+            "vs_baseline": None, "dtype": "f64", "data": "the reference's examples/Data/T1_city10000_04.txt (first %d lines)" % lines,
+            "config": cfg, "steps": lines, "warmup": 0}
+    if reference_arm:
+        sec = isam2_reference(lines)
+        if sec is None:
+            emit({"impl": "reference", "unavailable": "oracle/_ref/ref_tool not built (needs /root/reference)"})
+            return
+        ms = 1e3 * sec
+        base.update({"impl": "reference", "value": float(len(ms) / sec.sum()), "ms_per_step": float(ms.mean()), "latency_ms": latency_stats(ms),
+                     "cpu_baseline": {"value": float(len(ms) / sec.sum()), "unit": "updates/s", "cores": 1, "kind": "reference",
+                                      "sample": "all %d updates, gtsam::ISAM2 (ref_tool mode=isam2)" % len(ms)},
+                     "e2e": {"value": float(len(ms) / sec.sum()), "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                     "gpu_launches": 0})
+        emit(base)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    from gtsam_petercdev_b200.isam2 import ISAM2, drive_city10000, read_city10000
+    rows = read_city10000(CITY_FULL)[:lines]
+    warm = ISAM2(0.01, 1)                      # CUDA context, module load, allocator warm-up: untimed
+    drive_city10000(warm, rows[:50])
+    warm.close()
+    sampler = clocks_start("/tmp/gtb_clocks_isam2.csv")
+    isam = ISAM2(0.01, 1)
+    stamps = [time.perf_counter()]
+    est, row_of, results = drive_city10000(isam, rows, lambda u, e, r: stamps.append(time.perf_counter()))
+    clocks = clocks_stop(sampler, "/tmp/gtb_clocks_isam2.csv", 0)
+    wall_ms = 1e3 * np.diff(np.array(stamps))
+    total_s = stamps[-1] - stamps[0]
+    lib = isam.lib
+    launches = int(lib.gtb_kernel_launches(lib.gtb_isam2_engine(isam.h)))
+    n = len(rows)
+    h2d = int(np.mean([r["n_variables"] * 3 * 8 + r["n_factors"] * (2 * 8 + 3 * 8 + 4 + 9 * 8) for r in results]))
+    d2h = int(np.mean([r["n_variables"] * 4 * 8 for r in results]))
+    base.update({"value": n / total_s, "ms_per_step": float(wall_ms.mean()), "latency_ms": latency_stats(wall_ms),
+                 "host_plan_ms": latency_stats([r["plan_ms"] for r in results]), "device_solve_ms": latency_stats([r["solve_ms"] for r in results]),
+                 "e2e": {"value": n / total_s, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                 "gpu_launches": launches, "gpu_launches_note": "kernels of the LAST update (every update builds a fresh engine)",
+                 "clocks": clocks, "final": {"poses": results[-1]["n_variables"], "factors": results[-1]["n_factors"], "cliques": results[-1]["n_cliques"],
+                                             "relinearized_variables_total": int(sum(r["variables_relinearized"] for r in results))},
+                 "roofline": {"bound": "launch latency + host planning", "note": "an update of a <= 10k-pose graph is a few hundred kernels of microseconds "
+                              "each plus a symbolic analysis on the host: neither HBM nor the FP64 pipe is the bound (see host_plan_ms / device_solve_ms)",
+                              "achieved": None, "peak": None, "frac": None, "traffic": None}})
+    if not args.no_cpu_baseline:
+        sec = isam2_reference(lines)
+        if sec is not None:
+            base["cpu_baseline"] = {"value": float(len(sec) / sec.sum()), "unit": "updates/s", "cores": 1, "kind": "reference",
+                                    "sample": "the same %d updates, gtsam::ISAM2 (ref_tool mode=isam2) on this host" % len(sec),
+                                    "latency_ms": latency_stats(1e3 * sec)}
+    emit(base)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -198,6 +285,7 @@ def main():
     ap.add_argument("--ordering", default="metis")
     ap.add_argument("--lam", type=float, default=1e-5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--updates", type=int, default=1264, help="--workload c5: number of City10000 lines (1264 = the first 200 loop closures)")
     ap.add_argument("--parallelism", default="tree", choices=["tree", "replicas"],
                     help="N > 1: 'tree' = ONE problem, elimination tree cut across the GPUs (fan-in over NCCL, strong "
                          "scaling); 'replicas' = one independent problem per GPU (weak scaling, no collective)")
@@ -211,6 +299,10 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "c5":
+        if rank == 0:
+            run_isam2(args, args.impl == "reference")
+        return
     if args.impl == "reference":
         run_reference(args, rank, world)
         return

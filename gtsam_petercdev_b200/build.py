@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 ROOT = os.path.dirname(HERE)
 LIB = os.path.join(HERE, "libgtsam_b200.so")
-SOURCES = ["engine.cu", "symbolic.cpp", "ingest.cpp", "isam2.cpp"]
+SOURCES = ["engine.cu", "symbolic.cpp", "ingest.cpp", "isam2.cpp", "ordering.cpp"]
 # every source and header under csrc/ plus the public header: editing any of them triggers a rebuild
 DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".cpp", ".h"))) + [os.path.join(ROOT, "include", "gtsam_b200.h")]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

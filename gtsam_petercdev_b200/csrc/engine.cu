@@ -13,6 +13,8 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <map>
+#include <mutex>
 #include <queue>
 #include <stdexcept>
 #include <string>
@@ -40,22 +42,106 @@ struct StatusError : std::runtime_error {
   StatusError(gtb_status s, const std::string& m) : std::runtime_error(m), st(s) {}
 };
 
+// Device and pinned-host blocks of destroyed engines are kept for the next engine instead of going back to the driver: the
+// ISAM2 layer (isam2.cpp) builds a fresh engine at every update, and cudaMalloc / cudaFree / cudaMallocHost / cudaFreeHost of
+// an engine's ~40 buffers cost several milliseconds, ten times the numeric update of a small problem.  Process-wide, per
+// device; a block is reused for a request of at least half its size.  GTB_BLOCK_CACHE_MB bounds what is held (default 256,
+// 0 = off: every release goes to cudaFree as before); a single block above a quarter of the bound is never kept.
+struct BlockCache {
+  static constexpr int kSlots = 65;   // devices 0..63, slot 64 = pinned host memory
+  std::mutex mu;
+  std::multimap<size_t, void*> blocks[kSlots];
+  size_t held = 0;
+  static size_t bound() {
+    static const size_t b = (size_t)(getenv("GTB_BLOCK_CACHE_MB") ? strtoull(getenv("GTB_BLOCK_CACHE_MB"), nullptr, 10) : 256) << 20;
+    return b;
+  }
+  void* take(int slot, size_t bytes, size_t* cap) {
+    if (!bound() || slot < 0 || slot >= kSlots) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = blocks[slot].lower_bound(bytes);
+    if (it == blocks[slot].end() || it->first > 2 * bytes + 4096) return nullptr;
+    void* p = it->second;
+    *cap = it->first;
+    held -= it->first;
+    blocks[slot].erase(it);
+    return p;
+  }
+  bool give(int slot, void* p, size_t cap) {
+    if (slot < 0 || slot >= kSlots || cap > bound() / 4) return false;
+    std::lock_guard<std::mutex> lock(mu);
+    if (held + cap > bound()) return false;
+    blocks[slot].emplace(cap, p);
+    held += cap;
+    return true;
+  }
+};
+static BlockCache g_blocks;
+
+static void* pinned_alloc(size_t bytes, size_t* cap) {
+  bytes = (bytes + 255) & ~(size_t)255;
+  if (bytes <= BlockCache::bound() / 4) {
+    size_t c = 512;
+    while (c < bytes) c <<= 1;
+    bytes = c;
+  }
+  void* p = g_blocks.take(BlockCache::kSlots - 1, bytes, cap);
+  if (p) return p;
+  CK(cudaMallocHost(&p, bytes));
+  *cap = bytes;
+  return p;
+}
+static void pinned_free(void* p, size_t cap) {
+  if (p && !g_blocks.give(BlockCache::kSlots - 1, p, cap)) cudaFreeHost(p);
+}
+
 template <class T> struct DevBuf {
   T* p = nullptr;
   size_t n = 0;
-  void alloc(size_t count) {
+  size_t cap = 0;   // bytes of the block behind p
+  int dev = 0;      // device the block lives on
+  // zero = true: the buffer starts at zero whether it is fresh from the driver or reused (reused blocks are dirty)
+  void alloc(size_t count, bool zero = true) {
     release();
     n = count;
-    if (count) CK(cudaMalloc(&p, count * sizeof(T)));
+    if (!count) return;
+    size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+    if (bytes <= BlockCache::bound() / 4) {   // cacheable: power-of-two size classes, so that a problem that grows by one
+      size_t c = 512;                         // variable per update (ISAM2) finds its blocks again
+      while (c < bytes) c <<= 1;
+      bytes = c;
+    }
+    CK(cudaGetDevice(&dev));
+    p = static_cast<T*>(g_blocks.take(dev, bytes, &cap));
+    if (p) {
+      if (zero) {
+        CK(cudaMemsetAsync(p, 0, bytes, 0));
+        CK(cudaStreamSynchronize(0));   // the engine's stream does not wait for the legacy stream
+      }
+      return;
+    }
+    CK(cudaMalloc(&p, bytes));
+    cap = bytes;
   }
   void upload(const std::vector<T>& h, cudaStream_t s) {
-    if (h.size() != n || (!p && n)) alloc(h.size());
+    if (h.size() != n || (!p && n)) alloc(h.size(), false);
     if (n) CK(cudaMemcpyAsync(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice, s));
   }
   void release() {
-    if (p) cudaFree(p);
+    if (p) {
+      bool kept = false;
+      if (BlockCache::bound() && cap <= BlockCache::bound() / 4) {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        if (cur != dev) cudaSetDevice(dev);
+        // what cudaFree guarantees implicitly: nothing in flight still touches the block
+        kept = cudaDeviceSynchronize() == cudaSuccess && g_blocks.give(dev, p, cap);
+        if (cur != dev) cudaSetDevice(cur);
+      }
+      if (!kept) cudaFree(p);
+    }
     p = nullptr;
-    n = 0;
+    n = cap = 0;
   }
   ~DevBuf() { release(); }
 };
@@ -186,6 +272,7 @@ struct gtb_engine {
   int64_t partial_off[7] = {0};
   int64_t n_partials = 0;
   double* h_scalars = nullptr;   // pinned
+  size_t h_scalars_cap = 0, h_stage_cap[4] = {0, 0, 0, 0};   // block sizes (BlockCache)
   double* h_stage[4] = {nullptr, nullptr, nullptr, nullptr};   // pinned staging of the per-step state refresh
   cudaEvent_t stage_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   DevBuf<int64_t> d_inc_off;
@@ -237,9 +324,9 @@ struct gtb_engine {
   int lm_last_accepted = 0;   // the last gtb_lm_iterate ended with an accepted step
 
   ~gtb_engine() {
-    if (h_scalars) cudaFreeHost(h_scalars);
+    pinned_free(h_scalars, h_scalars_cap);
     for (int t = 0; t < 4; ++t) {
-      if (h_stage[t]) cudaFreeHost(h_stage[t]);
+      pinned_free(h_stage[t], h_stage_cap[t]);
       if (stage_ev[t]) cudaEventDestroy(stage_ev[t]);
     }
     for (auto ev_ : prof_events) cudaEventDestroy(ev_);
@@ -426,7 +513,7 @@ static void set_variables(Engine* e, int vt, int64_t n, const uint64_t* keys, co
     if (e->has_device && n) {
       // convert straight into a pinned staging buffer so that the copy is a real asynchronous DMA
       if (!e->h_stage[vt]) {
-        CK(cudaMallocHost(&e->h_stage[vt], v.state.size() * sizeof(double)));
+        e->h_stage[vt] = static_cast<double*>(pinned_alloc(v.state.size() * sizeof(double), &e->h_stage_cap[vt]));
         CK(cudaEventCreateWithFlags(&e->stage_ev[vt], cudaEventDisableTiming));
       } else {
         CK(cudaEventSynchronize(e->stage_ev[vt]));   // the previous refresh has left the buffer
@@ -603,7 +690,7 @@ static void finalize_problem(Engine* e) {
   }
   e->d_partials.alloc(2 * std::max<int64_t>(e->n_partials, 1));
   e->d_scalars.alloc(16);
-  CK(cudaMallocHost(&e->h_scalars, 16 * sizeof(double)));
+  e->h_scalars = static_cast<double*>(pinned_alloc(16 * sizeof(double), &e->h_scalars_cap));
   e->d_delta.alloc(e->n_scalars);
   e->d_hdiag.alloc(e->n_scalars);
   e->d_damp.alloc(e->n_scalars);
@@ -2001,6 +2088,7 @@ gtb_status gtb_create(int device, gtb_engine** out) {
 
 void gtb_destroy(gtb_engine* e) {
   EngineDeviceGuard guard(e);
+  if (e && e->has_device && e->stream) cudaStreamSynchronize(e->stream);   // its blocks go back to the cache: nothing may be in flight
   delete e;
 }
 const char* gtb_last_error(const gtb_engine* e) { return e ? e->err.c_str() : "null engine"; }
@@ -2052,6 +2140,9 @@ gtb_status gtb_set_ordering_builtin(gtb_engine* e, int which) {
     for (int64_t i = 0; i < e->vars[GTB_POINT3].n; ++i) order.push_back(e->type_var[GTB_POINT3][i]);
     for (int64_t i = 0; i < e->vars[GTB_CAMERA].n; ++i) order.push_back(e->type_var[GTB_CAMERA][i]);
     need((int32_t)order.size() == V, "Schur ordering needs a problem with only cameras and points");
+  } else if (which == 2) {
+    order = nested_dissection_order(e->sym);
+    need((int32_t)order.size() == V, "nested dissection lost a variable");
   } else {
     need(false, "unknown builtin ordering");
   }

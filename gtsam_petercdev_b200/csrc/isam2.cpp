@@ -146,7 +146,7 @@ gtb_status rebuild(gtb_isam2* s) {
   }
   st = pass(s, gtb_finalize_problem(s->eng), "gtb_finalize_problem");
   if (st != GTB_OK) return st;
-  if (!s->have_ordering) return pass(s, gtb_set_ordering_builtin(s->eng, 0), "gtb_set_ordering_builtin");
+  if (!s->have_ordering) return pass(s, gtb_set_ordering_builtin(s->eng, 2), "gtb_set_ordering_builtin");
   // the caller's order for the keys it names, then the rest in the order they were added (the newest variables last:
   // they are the ones the next update touches, cf. the constrained ordering of ISAM2.cpp:301-340)
   std::vector<uint64_t> order;

@@ -93,6 +93,10 @@ GTB_HD inline bool is_fused_child(int32_t F, int32_t dim, int32_t parent_F, int3
 // small_max: fronts with F+S+1 <= small_max are handled by the shared-memory kernel.
 // out: the reference's clique layout, bit-exact.  numeric (may be null): the plan the device factorises, after relaxed
 // amalgamation of chains of large fronts (amalg_ratio <= 1 disables it: numeric = out plus the identity member lists).
+// Elimination position -> variable id by automatic nested dissection (ordering.cpp); subsets of at most leaf_size variables are
+// ordered by degree.
+std::vector<int32_t> nested_dissection_order(const SymbolicInput& in, int leaf_size = 2);
+
 void build_plan(const SymbolicInput& in, int32_t small_max, Plan* out, Plan* numeric = nullptr, double amalg_ratio = 0.0,
                 int32_t amalg_max_F = 0, int32_t amalg_min_S = 0);
 

@@ -102,7 +102,7 @@ class Engine:
 
     def set_ordering(self, keys):
         if isinstance(keys, str):
-            which = {"natural": 0, "schur": 1}[keys]
+            which = {"natural": 0, "schur": 1, "nested_dissection": 2}[keys]
             self._ck(self.lib.gtb_set_ordering_builtin(self.h, which))
             return
         keys = np.ascontiguousarray(keys, dtype=np.uint64)

@@ -84,3 +84,54 @@ class ISAM2:
         out = np.zeros((self.count(t), _STATE_DEV[t]))
         self._ck(self.lib.gtb_isam2_estimate(self.h, t, _ptr(out)))
         return out
+
+
+# ---- the City10000 schedule (examples/ISAM2_City10000.cpp:62-134), shared by tests/test_isam2_gpu.py and bench.py --------
+DIAG_SIGMAS = 2   # GTB_NOISE_DIAG_SIGMAS
+
+
+def X(i):
+    return (ord("x") << 56) | int(i)   # gtsam::Symbol('x', i)
+
+
+def read_city10000(path):
+    """Lines "EDGE2 <from> <n> <to> <n> <hypotheses> {x y theta}...": (from, to, x, y, theta) of the first hypothesis."""
+    rows = []
+    for line in open(path):
+        f = line.split()
+        if len(f) >= 9 and f[0] == "EDGE2":
+            rows.append((int(f[1]), int(f[3]), float(f[6]), float(f[7]), float(f[8])))
+    return rows
+
+
+def pose2_compose(p, z):
+    """Pose2 * Pose2 (geometry/Pose2.h:147-151) for an estimate row (cos, sin, x, y) and a measurement (x, y, theta)."""
+    c, s, x, y = p
+    cz, sz = np.cos(z[2]), np.sin(z[2])
+    return [x + c * z[0] - s * z[1], y + s * z[0] + c * z[1], np.arctan2(s * cz + c * sz, c * cz - s * sz)]
+
+
+def drive_city10000(isam, rows, on_update=None):
+    """Prior 1e-4 on pose 0 and one update; then one update per line: an odometry line (to = from + 1) adds the new pose,
+    initialised by composing the current estimate of `from` with the measurement, and a BetweenFactor with sigmas
+    (1/30, 1/30, 1/100); any other line is a loop closure with sigmas 10.  The estimate is read back after every update, as
+    the example does.  Returns (estimate rows, pose -> row, the result dict of every update)."""
+    isam.add_variables("pose2", [X(0)], [[0.0, 0.0, 0.0]])
+    isam.add_factors("prior2", [X(0)], [[0.0, 0.0, 0.0]], DIAG_SIGMAS, [[1e-4, 1e-4, 1e-4]])
+    isam.update()
+    est = isam.calculate_estimate("pose2")
+    row_of = {0: 0}
+    results = []
+    for u, (a, b, zx, zy, zt) in enumerate(rows, start=1):
+        z = [zx, zy, zt]
+        if b == a + 1:
+            row_of[b] = len(row_of)
+            isam.add_variables("pose2", [X(b)], [pose2_compose(est[row_of[a]], z)])
+            isam.add_factors("between2", [[X(a), X(b)]], [z], DIAG_SIGMAS, [[1.0 / 30.0, 1.0 / 30.0, 1.0 / 100.0]])
+        else:
+            isam.add_factors("between2", [[X(a), X(b)]], [z], DIAG_SIGMAS, [[10.0, 10.0, 10.0]])
+        results.append(isam.update())
+        est = isam.calculate_estimate("pose2")
+        if on_update:
+            on_update(u, est, row_of)
+    return est, row_of, results

@@ -85,8 +85,11 @@ gtb_status gtb_finalize_problem(gtb_engine* e);
  * merge rule (JunctionTree-inst.h:65-121, ClusterTree-inst.h:46-96) -> clique layout in Scatter order
  * (linear/Scatter.cpp:39-73).  The result is bit-identical to the reference's Bayes-tree structure.      */
 gtb_status gtb_set_ordering(gtb_engine* e, int64_t n, const uint64_t* keys);
-/* Convenience orderings that need no graph algorithm: 0 = natural (sorted keys, Ordering::Natural),
- * 1 = Schur (all POINT3 then all CAMERA, timing/timeSFMBAL.h:74-83).                                    */
+/* Orderings computed inside the library: 0 = natural (sorted keys, Ordering::Natural), 1 = Schur (all POINT3 then all
+ * CAMERA, timing/timeSFMBAL.h:74-83), 2 = nested dissection on the variable adjacency graph (csrc/ordering.cpp: level-
+ * structure separators, written for pose graphs; NOT the permutation CCOLAMD or METIS would give -- a caller that wants
+ * the reference's own ordering computes it with Ordering::Colamd / Ordering::Metis and passes it to gtb_set_ordering,
+ * as integration/DeviceOptimizers.cpp does).                                                             */
 gtb_status gtb_set_ordering_builtin(gtb_engine* e, int which);
 gtb_status gtb_plan_sizes(const gtb_engine* e, int64_t* n_cliques, int64_t* n_clique_keys,
                           int64_t* n_conditional_doubles, int64_t* n_scalars);
@@ -263,7 +266,7 @@ gtb_status gtb_marginal_covariance(gtb_engine* e, int64_t n, const uint64_t* key
  * Usage: stage the new variables and factors (same row layouts as gtb_set_variables / gtb_set_factors; a key may be staged
  * once), then gtb_isam2_update.  Ordering: gtb_isam2_set_ordering gives an elimination order for the variables known so
  * far (the reference computes a constrained COLAMD per update, ISAM2.cpp:301-340; any order gives the same estimate);
- * variables that are not listed are eliminated last in the order they were added.  Without it: ascending keys.      */
+ * variables that are not listed are eliminated last in the order they were added.  Without it: the built-in nested dissection (gtb_set_ordering_builtin(2)), recomputed at every update. */
 typedef struct gtb_isam2 gtb_isam2;
 typedef struct {
   int64_t update_count;            /* ISAM2::update_count_                                            */

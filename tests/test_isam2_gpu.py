@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from gtsam_petercdev_b200.isam2 import ISAM2
+from gtsam_petercdev_b200.isam2 import ISAM2, X, drive_city10000 as drive, read_city10000 as read_city
 
 pytestmark = pytest.mark.gpu
 
@@ -16,20 +16,6 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = os.path.join(HERE, "golden", "isam2__city10000_200loops.npz")
 HEAD = os.path.join(HERE, "golden", "data", "T1_city10000_04_head1264.txt")
 TOL = 1e-9
-DIAG_SIGMAS = 2   # GTB_NOISE_DIAG_SIGMAS
-
-
-def X(i):
-    return (ord("x") << 56) | int(i)   # gtsam::Symbol('x', i)
-
-
-def read_city(path):
-    rows = []
-    for line in open(path):
-        f = line.split()
-        if len(f) >= 9 and f[0] == "EDGE2":
-            rows.append((int(f[1]), int(f[3]), float(f[6]), float(f[7]), float(f[8])))
-    return rows
 
 
 def xyt(rows):
@@ -37,37 +23,8 @@ def xyt(rows):
     return np.stack([rows[:, 2], rows[:, 3], np.arctan2(rows[:, 1], rows[:, 0])], axis=1)
 
 
-def compose(p, z):
-    """Pose2 * Pose2 (geometry/Pose2.h:147-151) for an estimate row (cos, sin, x, y) and a measurement (x, y, theta)."""
-    c, s, x, y = p
-    cz, sz = np.cos(z[2]), np.sin(z[2])
-    return [x + c * z[0] - s * z[1], y + s * z[0] + c * z[1], np.arctan2(s * cz + c * sz, c * cz - s * sz)]
-
-
 def angle_diff(a, b):
     return np.angle(np.exp(1j * (a - b)))
-
-
-def drive(isam, rows, on_update=None):
-    isam.add_variables("pose2", [X(0)], [[0.0, 0.0, 0.0]])
-    isam.add_factors("prior2", [X(0)], [[0.0, 0.0, 0.0]], DIAG_SIGMAS, [[1e-4, 1e-4, 1e-4]])
-    isam.update()
-    est = isam.calculate_estimate("pose2")
-    row_of = {0: 0}
-    results = []
-    for u, (a, b, zx, zy, zt) in enumerate(rows, start=1):
-        z = [zx, zy, zt]
-        if b == a + 1:
-            row_of[b] = len(row_of)
-            isam.add_variables("pose2", [X(b)], [compose(est[row_of[a]], z)])
-            isam.add_factors("between2", [[X(a), X(b)]], [z], DIAG_SIGMAS, [[1.0 / 30.0, 1.0 / 30.0, 1.0 / 100.0]])
-        else:
-            isam.add_factors("between2", [[X(a), X(b)]], [z], DIAG_SIGMAS, [[10.0, 10.0, 10.0]])
-        results.append(isam.update())
-        est = isam.calculate_estimate("pose2")
-        if on_update:
-            on_update(u, est, row_of)
-    return est, row_of, results
 
 
 def test_estimates_after_every_update_match_the_reference():
