@@ -82,6 +82,21 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 // because the compiler turns an unused-result atomicAdd into the waiting form (ATOM) as soon as a fence follows it in
 // the same function -- seen in the SASS of schur_step_kernel, where it cost 1.1 ms per step.  A later __threadfence()
 // still orders these adds before whatever the thread writes after it.
+// 1 / sqrt(x) without the special-case branch of the library routine: the branch ends the basic block, and with it the
+// overlap of the Newton steps with the independent updates around them (the 8 x 8 register Cholesky of the panel step is one
+// dependent chain of eight of these).  Hardware seed (2^-22) and two Newton steps; x <= 0, NaN and denormals give NaN or
+// infinity, which the pivot test that precedes every use reports as a failed factorisation.
+__device__ __forceinline__ double rsqrt_chain(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double t = x * y, h = 0.5 * y;
+  double e = fma(-t, y, 1.0);
+  y = fma(h, e, y);
+  t = x * y;
+  h = 0.5 * y;
+  e = fma(-t, y, 1.0);
+  return fma(h, e, y);
+}
 __device__ __forceinline__ void red_add(double* p, double v) {
   asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
 }
@@ -1233,10 +1248,9 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     return;
   }
   // ---- role A: slice `task` of row panel p (64 pivots) ----
-  // Every role-A CTA factors the 64 x 64 diagonal block redundantly (warp 0: two 32 x 32 in-register Choleskys with a
-  // 32 x 32 triangular solve and a rank-32 update between them), so no CTA waits on another inside a launch.  Warps 1..7
-  // own 8 columns each: look-ahead update by panel p-1 while warp 0 factors, then the blocked triangular solve.
-  // All GEMM-shaped work runs on the FP64 tensor pipe.
+  // Every role-A CTA factors the 64 x 64 diagonal block redundantly (cooperative 8 x 8-block Cholesky below), so no CTA
+  // waits on another inside a launch.  Warps 1..7 own 8 columns each: look-ahead update by panel p-1 in the slack of the
+  // factorisation, then the blocked triangular solve.  All GEMM-shaped work runs on the FP64 tensor pipe.
   if (E.debug & 4) return;
   const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   double* Ps = sm;                    // Ps[i * LDP + k] = R[k0-64+k, k0+i]           (panel p-1, columns of D)
@@ -1251,23 +1265,12 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
   auto stamp = [&](int k) { if (probe) E.dbg[k] = clock64(); };
   if (warp == 0) stamp(0);
   if (task == 0 && p >= 1 && F - rest0 <= 0) copy_diag_block(A, ld, F, dfac, p - 1, tid);   // no tile task to do it
-  // column warps: issue every global load of the slice up front (fragment layout), they overlap the diagonal-block loads
+  // Every global load of the CTA is issued before the first use.  The diagonal block and the matching columns of panel p-1
+  // go first (one column = 64 contiguous doubles per two warp instructions): the Cholesky chain starts from them, while the
+  // column warps' own slice (fragment layout) is not needed before the look-ahead update.
   const int jbase = rest0 + task * SLICE + (warp - 1) * CWID;
   const bool colwarp = warp > 0 && jbase < dim;
   double qf[16], b0[8][2];
-  if (colwarp) {
-    const int j = jbase + g;
-#pragma unroll
-    for (int ks = 0; ks < 16; ++ks) qf[ks] = (p >= 1 && j < dim) ? A[(k0 - PW + ks * 4 + t) + (int64_t)j * ld] : 0.0;
-#pragma unroll
-    for (int mt = 0; mt < 8; ++mt)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int i = mt * 8 + g, jj = jbase + 2 * t + e;
-        b0[mt][e] = (jj < dim && i < kb) ? A[(k0 + i) + (int64_t)jj * ld] : 0.0;
-      }
-  }
-  // diagonal block and the matching columns of panel p-1: one column (64 contiguous doubles) per two warp instructions
   {
     double vp[8][2], vd[8][2];
 #pragma unroll
@@ -1279,6 +1282,18 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
         vp[q][h] = (p >= 1 && col < kb) ? A[(k0 - PW + l) + (int64_t)(k0 + col) * ld] : 0.0;
         vd[q][h] = (l <= col && col < kb) ? A[(k0 + l) + (int64_t)(k0 + col) * ld] : ((l == col) ? 1.0 : 0.0);
       }
+    }
+    if (colwarp) {
+      const int j = jbase + g;
+#pragma unroll
+      for (int ks = 0; ks < 16; ++ks) qf[ks] = (p >= 1 && j < dim) ? A[(k0 - PW + ks * 4 + t) + (int64_t)j * ld] : 0.0;
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int i = mt * 8 + g, jj = jbase + 2 * t + e;
+          b0[mt][e] = (jj < dim && i < kb) ? A[(k0 + i) + (int64_t)jj * ld] : 0.0;
+        }
     }
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
@@ -1324,54 +1339,37 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
     __syncthreads();
   }
   if (warp == 0) stamp(2);
-  // column warps: X = B - P^T Q (needs only panel p-1), while warp 0 factors
-  if (colwarp) {
-    double acc[8][2];
-#pragma unroll
-    for (int mt = 0; mt < 8; ++mt) acc[mt][0] = acc[mt][1] = 0.0;
-    if (p >= 1) {
-#pragma unroll
-      for (int ks = 0; ks < 16; ++ks) {
-#pragma unroll
-        for (int mt = 0; mt < 8; ++mt) dmma884(acc[mt][0], acc[mt][1], Ps[(mt * 8 + g) * LDP + ks * 4 + t], qf[ks]);
-      }
-    }
-#pragma unroll
-    for (int mt = 0; mt < 8; ++mt)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) Xs[(2 * t + e) * LDP + mt * 8 + g] = b0[mt][e] - acc[mt][e];
-    if (warp == 1) stamp(8);
-  }
+  // Cooperative 64 x 64 Cholesky in 8 x 8 blocks, right-looking, WITH LOOK-AHEAD: warp 0 alone walks the dependent chain
+  //   factor block b (8 pivots, the whole 8 x 8 block held redundantly in the registers of every lane: pivot -> rsqrt ->
+  //   scale -> update never leaves the register file) -> solve the 8 columns of the NEXT diagonal tile against it (one lane
+  //   per column) -> bring that tile up to date (two DMMAs) -> factor block b + 1 ...
+  // while warps 1..7 (the helpers) trail one block behind with everything that is not on the chain: the row solve of the
+  // other columns (one thread per column) and the rank-8 DMMA updates of the other trailing tiles.  Hand-shakes are named
+  // barriers: 1 = "row block b of the next tile's columns is solved" (warp 0 arrives, helpers wait), 2 = "bulk update of block
+  // b is done" (helpers arrive, warp 0 waits one block later), 3 = the helpers among themselves.  The column warps' look-ahead
+  // X = B - P^T Q (needs only panel p-1) is cut into one slice per block and runs in the helpers' slack.
+  // (Before: every block went factor -> CTA barrier -> row solve -> CTA barrier -> update with warp 0 waiting at both barriers,
+  // 2,450 cycles per block; the in-kernel stamps of the root front are in profiles/r02/launch_trace_c3_metis.txt.)
   {
-    // Cooperative 64 x 64 Cholesky in 8 x 8 blocks, right-looking (replaces two 32 x 32 in-register Choleskys in warp 0 with a
-    // 32 x 32 triangular solve between them: 22.5 k -> 20.6 k cycles in the in-kernel stamps, panel step 26.5 -> 23.6 us).
-    // The dependent chain of a block -- 8 pivots -- runs in warp 0 with the whole 8 x 8 block held REDUNDANTLY in the
-    // registers of every lane: pivot -> rsqrt -> scale -> update never leaves the register file (no shuffle, no
-    // shared-memory broadcast).  Everything else is spread over the CTA: the row block is solved one thread per column
-    // (column-oriented forward substitution with the 8 x 8 factor read by broadcast), the trailing 8-column tiles are
-    // updated on the FP64 tensor pipe (rank 8: two DMMAs per tile) by all warps.  Warp 0 owns the next diagonal tile, so
-    // the next block's chain starts after a warp-level sync; two CTA barriers per block.
-    // (Tried on the box and dropped: bringing D up to date with panel p-1 row block by row block inside this loop and
-    // slicing the column warps' look-ahead into it -- same 2.89 ms per step, the helpers then set the pace of a block;
-    // four tile pairs at a time per warp with warp 0 keeping only the next diagonal tile -- 3.08 ms.)
+    auto bar_sync = [](int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); };
+    auto bar_arrive = [](int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); };
     const int nb8 = (kb + 7) >> 3;
     bool okw = true;
     int bad_pivot = -1;
-    for (int b = 0; b < nb8; ++b) {
-      const int o = 8 * b;
-      if (warp == 0) {
-        double a[8][8];
+    if (warp == 0) {
+      double a[8][8], rv[8];
 #pragma unroll
-        for (int cc = 0; cc < 8; ++cc)
+      for (int cc = 0; cc < 8; ++cc)
 #pragma unroll
-          for (int r = 0; r <= cc; ++r) a[r][cc] = Ds[(o + cc) * LDP + o + r];
-        double rv[8];
+        for (int r = 0; r <= cc; ++r) a[r][cc] = Ds[cc * LDP + r];
+      for (int b = 0; b < nb8; ++b) {
+        const int o = 8 * b;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const double piv = a[k][k];
           if (okw && !(piv > 0.0)) bad_pivot = k0 + o + k;
           okw = okw && (piv > 0.0);   // Eigen LLT: NumericalIssue on a non-positive pivot (base/cholesky.cpp:126-128)
-          const double rinv = rsqrt(piv);
+          const double rinv = rsqrt_chain(piv);
           rv[k] = rinv;
           a[k][k] = piv * rinv;
 #pragma unroll
@@ -1388,37 +1386,100 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
 #pragma unroll
         for (int k = 0; k < 8; ++k) dinv[o + k] = rv[k];
         if (b == 0) stamp(3);
-      }
-      __syncthreads();   // R_bb and its reciprocal diagonal are published; the updates of block b - 1 are complete
-      const int ncol = 8 * nb8 - (o + 8);
-      if (tid < ncol) {   // row block b, one column per thread: u = R_bb^-T x
-        double* col = Ds + (o + 8 + tid) * LDP + o;
-        double x[8];
+        if (b + 1 < nb8) {
+          if (b >= 1) bar_sync(2, 256);   // bulk(b-1) is done: row block b and tile (b+1, b+1) carry every earlier update
+          if (lane < 8) {                 // u = R_bb^-T x for the 8 columns of the next diagonal tile, factor from registers
+            double* col = Ds + (o + 8 + lane) * LDP + o;
+            double x[8];
 #pragma unroll
-        for (int r = 0; r < 8; ++r) x[r] = col[r];
+            for (int r = 0; r < 8; ++r) x[r] = col[r];
 #pragma unroll
-        for (int l = 0; l < 8; ++l) {
-          x[l] *= dinv[o + l];
+            for (int l = 0; l < 8; ++l) {
+              x[l] *= rv[l];
 #pragma unroll
-          for (int r = l + 1; r < 8; ++r) x[r] -= Ds[(o + r) * LDP + o + l] * x[l];
+              for (int r = l + 1; r < 8; ++r) x[r] -= a[l][r] * x[l];
+            }
+#pragma unroll
+            for (int r = 0; r < 8; ++r) col[r] = x[r];
+          }
+          __syncwarp();
+          bar_arrive(1, 256);
+          // tile (b+1, b+1) -= U^T U, straight into the register copy of the next block
+          double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+          for (int ks = 0; ks < 8; ks += 4) {
+            const double f = Ds[(o + 8 + g) * LDP + o + ks + t];
+            dmma884(c0, c1, f, f);
+          }
+          // this lane holds C[g][2t], C[g][2t+1] of the product; the tile lives at Ds[col * LDP + row]
+          if (g <= 2 * t) Ds[(o + 8 + 2 * t) * LDP + o + 8 + g] -= c0;
+          if (g <= 2 * t + 1) Ds[(o + 8 + 2 * t + 1) * LDP + o + 8 + g] -= c1;
+          __syncwarp();
+#pragma unroll
+          for (int cc = 0; cc < 8; ++cc)
+#pragma unroll
+            for (int r = 0; r <= cc; ++r) a[r][cc] = Ds[(o + 8 + cc) * LDP + o + 8 + r];
         }
-#pragma unroll
-        for (int r = 0; r < 8; ++r) col[r] = x[r];
       }
-      __syncthreads();
-      // trailing tiles (mt, nt), b < mt <= nt < nb8: C -= U(:, mt)^T U(:, nt), pair 0 = the next diagonal tile (warp 0)
-      const int m = nb8 - 1 - b, npair = (m * (m + 1)) >> 1;
-      for (int q = warp; q < npair; q += 8) {
-        int idx = q, mt = 0;
-        while (idx >= m - mt) { idx -= m - mt; ++mt; }
-        const int ct = b + 1 + mt + idx, rt = b + 1 + mt;
-        double c0 = 0.0, c1 = 0.0;
+      if (nb8 >= 2) bar_sync(2, 256);   // the last bulk update (balances the helpers' arrival)
+    } else {
+      // helpers; the column warps among them carry the look-ahead accumulators through the loop
+      double acc[8][2];
 #pragma unroll
-        for (int ks = 0; ks < 8; ks += 4) dmma884(c0, c1, Ds[(8 * rt + g) * LDP + o + ks + t], Ds[(8 * ct + g) * LDP + o + ks + t]);
-        Ds[(8 * ct + 2 * t) * LDP + 8 * rt + g] -= c0;
-        Ds[(8 * ct + 2 * t + 1) * LDP + 8 * rt + g] -= c1;
+      for (int mt = 0; mt < 8; ++mt) acc[mt][0] = acc[mt][1] = 0.0;
+      auto lookahead = [&](int ks0, int ks1) {
+        if (!colwarp || p < 1) return;
+#pragma unroll
+        for (int ks = 0; ks < 16; ++ks) {
+          if (ks < ks0 || ks >= ks1) continue;
+#pragma unroll
+          for (int mt = 0; mt < 8; ++mt) dmma884(acc[mt][0], acc[mt][1], Ps[(mt * 8 + g) * LDP + ks * 4 + t], qf[ks]);
+        }
+      };
+      const int ht = tid - 32;   // 0 .. 223
+      for (int b = 0; b + 1 < nb8; ++b) {
+        const int o = 8 * b;
+        bar_sync(1, 256);   // R_bb, its reciprocal diagonal and the solved block (b, b+1) are published
+        const int ncol = 8 * nb8 - (o + 16);
+        if (ht < ncol) {    // row block b of the columns beyond the next tile, one column per thread
+          double* col = Ds + (o + 16 + ht) * LDP + o;
+          double x[8];
+#pragma unroll
+          for (int r = 0; r < 8; ++r) x[r] = col[r];
+#pragma unroll
+          for (int l = 0; l < 8; ++l) {
+            x[l] *= dinv[o + l];
+#pragma unroll
+            for (int r = l + 1; r < 8; ++r) x[r] -= Ds[(o + r) * LDP + o + l] * x[l];
+          }
+#pragma unroll
+          for (int r = 0; r < 8; ++r) col[r] = x[r];
+        }
+        bar_sync(3, 224);
+        // trailing tiles (mt, nt), b < mt <= nt < nb8, without (b+1, b+1) which warp 0 keeps: C -= U(:, mt)^T U(:, nt)
+        const int m = nb8 - 1 - b, npair = (m * (m + 1)) >> 1;
+        for (int q = warp; q < npair; q += 7) {
+          int idx = q, mt = 0;
+          while (idx >= m - mt) { idx -= m - mt; ++mt; }
+          const int ct = b + 1 + mt + idx, rt = b + 1 + mt;
+          double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+          for (int ks = 0; ks < 8; ks += 4) dmma884(c0, c1, Ds[(8 * rt + g) * LDP + o + ks + t], Ds[(8 * ct + g) * LDP + o + ks + t]);
+          Ds[(8 * ct + 2 * t) * LDP + 8 * rt + g] -= c0;
+          Ds[(8 * ct + 2 * t + 1) * LDP + 8 * rt + g] -= c1;
+        }
+        __syncwarp();
+        bar_arrive(2, 256);
+        lookahead(2 * b, 2 * b + 2);
       }
-      if (warp == 0) __syncwarp();
+      lookahead(nb8 >= 2 ? 2 * (nb8 - 1) : 0, 16);   // what the loop did not reach (ragged last panel)
+      if (colwarp) {
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) Xs[(2 * t + e) * LDP + mt * 8 + g] = b0[mt][e] - acc[mt][e];
+        if (warp == 1) stamp(8);
+      }
     }
     __syncthreads();
     if (lane < 8 && warp < nb8) {
