@@ -1131,17 +1131,32 @@ __host__ __device__ __forceinline__ int trapezoid_tiles(int nrt, int nct) {
   if (nrt > nct) nrt = nct;
   return nrt * nct - nrt * (nrt - 1) / 2;
 }
+// Tile t of a trapezoid -> (row ty, column tx), rows ty = 0, 1, ... hold nct - ty tiles (tx >= ty).  Row ty starts at
+// off(ty) = ty * nct - ty (ty - 1) / 2: solved in floating point and corrected by at most one step (a loop over the rows
+// costs ~20 cycles per row on a dependent integer chain: 600 cycles in front of a 64 x 64 tile of a 25-row trapezoid).
 __device__ __forceinline__ void trapezoid_decode(int t, int nct, int& ty, int& tx) {
-  ty = 0;
-  while (t >= nct - ty) { t -= nct - ty; ++ty; }
-  tx = ty + t;
+  const float w = 2.0f * nct + 1.0f;
+  float root;   // the approximate instruction: no special-case branch, and the correction below absorbs its last bits
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(root) : "f"(fmaxf(w * w - 8.0f * t, 0.0f)));
+  ty = (int)((w - root) * 0.5f);
+  ty = max(0, min(ty, nct - 1));
+  int off = ty * nct - ((ty * (ty - 1)) >> 1);
+  if (off > t) { --ty; off -= nct - ty; }
+  else if (t - off >= nct - ty) { off += nct - ty; ++ty; }
+  tx = ty + (t - off);
 }
 // tasks of clique (F, dim) at panel step p (host mirrors this to size the grid)
-__host__ __device__ __forceinline__ int step_tasks(int F, int dim, int p) {
+// spc = column slices per role-A CTA of this launch (the host raises it when a launch would hold more role-A CTAs than the
+// machine has SMs: every role-A CTA factors the diagonal block on its own, so a second wave of them repeats that work)
+__host__ __device__ __forceinline__ int role_a_ctas(int dim, int rest0, int spc) {
+  const int nA = (dim - rest0 + SLICE - 1) / SLICE;
+  return (nA + spc - 1) / spc;
+}
+__host__ __device__ __forceinline__ int step_tasks(int F, int dim, int p, int spc = 1) {
   const int np = (F + PW - 1) / PW;
   if (p < np) {
     const int k0 = p * PW, kb = (F - k0 < PW) ? F - k0 : PW, rest0 = k0 + kb;
-    int n = (dim - rest0 + SLICE - 1) / SLICE;
+    int n = role_a_ctas(dim, rest0, spc);
     if (p >= 1) n += trapezoid_tiles((F - rest0 + TW - 1) / TW, (dim - rest0 + TW - 1) / TW);
     return n;
   }
@@ -1220,7 +1235,7 @@ __device__ __forceinline__ void copy_diag_block(double* __restrict__ A, int ld, 
   }
 }
 
-__global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTask* __restrict__ tasks, int p) {
+__global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTask* __restrict__ tasks, int p, int spc) {
   extern __shared__ __align__(16) double sm[];
   pdl_trigger();
   const StepTask me = tasks[blockIdx.x];   // compact list: role-A slices (the critical path) first, no empty CTAs
@@ -1235,10 +1250,11 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
   const int tid = threadIdx.x;
   if (p >= np) return;   // the Schur complement step of this clique runs in schur_step_kernel
   const int k0 = p * PW, kb = min(PW, F - k0), rest0 = k0 + kb;
-  const int nA = (dim - rest0 + SLICE - 1) / SLICE;
-  if (task >= nA) {
+  const int nA = (dim - rest0 + SLICE - 1) / SLICE;   // column slices of this row panel
+  const int nAc = (nA + spc - 1) / spc;               // role-A CTAs: CTA `task` takes slices task, task + nAc, ...
+  if (task >= nAc) {
     if (p == 0) return;
-    task -= nA;
+    task -= nAc;
     const int nrt = (F - rest0 + TW - 1) / TW, nct = (dim - rest0 + TW - 1) / TW;
     if (task >= trapezoid_tiles(nrt, nct)) return;
     int ty, tx;
@@ -1314,12 +1330,10 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
 #pragma unroll
     for (int q = 0; q < 5; ++q) {
       acc[q][0] = acc[q][1] = 0.0;
-      // pair index -> (mt, nt), mt <= nt < 8, row-major over the upper triangle
-      int idx = warp + 8 * q, mt = 0;
-      while (mt < 7 && idx >= 8 - mt) { idx -= 8 - mt; ++mt; }   // (indices >= 36 are masked below)
-      pm[q] = mt;
-      pn[q] = mt + idx;
+      // pair index -> (mt, nt), mt <= nt < 8, row-major over the upper triangle (indices >= 36 are masked below)
+      trapezoid_decode(min(warp + 8 * q, 35), 8, pm[q], pn[q]);
     }
+    if (warp == 0) stamp(4);
 #pragma unroll 4
     for (int ks = 0; ks < PW; ks += 4) {
 #pragma unroll
@@ -1327,6 +1341,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
         if (warp + 8 * q < 36)
           dmma884(acc[q][0], acc[q][1], Ps[(pm[q] * 8 + g) * LDP + ks + t], Ps[(pn[q] * 8 + g) * LDP + ks + t]);
     }
+    if (warp == 0) stamp(6);
 #pragma unroll
     for (int q = 0; q < 5; ++q)
       if (warp + 8 * q < 36) {
@@ -1336,6 +1351,7 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
           if (i <= jj && jj < kb) Ds[jj * LDP + i] -= acc[q][e];
         }
       }
+    if (warp == 0) stamp(7);
     __syncthreads();
   }
   if (warp == 0) stamp(2);
@@ -1459,9 +1475,9 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
         // trailing tiles (mt, nt), b < mt <= nt < nb8, without (b+1, b+1) which warp 0 keeps: C -= U(:, mt)^T U(:, nt)
         const int m = nb8 - 1 - b, npair = (m * (m + 1)) >> 1;
         for (int q = warp; q < npair; q += 7) {
-          int idx = q, mt = 0;
-          while (idx >= m - mt) { idx -= m - mt; ++mt; }
-          const int ct = b + 1 + mt + idx, rt = b + 1 + mt;
+          int mt, nt;
+          trapezoid_decode(q, m, mt, nt);
+          const int ct = b + 1 + nt, rt = b + 1 + mt;
           double c0 = 0.0, c1 = 0.0;
 #pragma unroll
           for (int ks = 0; ks < 8; ks += 4) dmma884(c0, c1, Ds[(8 * rt + g) * LDP + o + ks + t], Ds[(8 * ct + g) * LDP + o + ks + t]);
@@ -1545,17 +1561,53 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
   }
   if (!colwarp) return;
   if (warp == 1) stamp(9);
-  // blocked forward substitution Y = R^-T X in 8-row stages
-  trsm_stages<1, 8>(Ds, Ws, Xs, Ts, (kb + 7) / 8, g, t);
-  if (warp == 1) stamp(10);
-  for (int cc = 0; cc < CWID; ++cc) {
-    const int j = jbase + cc;
-    if (j < dim) {
-      if (lane < kb) A[(k0 + lane) + (int64_t)j * ld] = Xs[cc * LDP + lane];
-      if (lane + NB < kb) A[(k0 + lane + NB) + (int64_t)j * ld] = Xs[cc * LDP + lane + NB];
+  int jb = jbase;
+  for (int sl = task;;) {
+    // blocked forward substitution Y = R^-T X in 8-row stages
+    trsm_stages<1, 8>(Ds, Ws, Xs, Ts, (kb + 7) / 8, g, t);
+    if (warp == 1 && sl == task) stamp(10);
+    for (int cc = 0; cc < CWID; ++cc) {
+      const int j = jb + cc;
+      if (j < dim) {
+        if (lane < kb) A[(k0 + lane) + (int64_t)j * ld] = Xs[cc * LDP + lane];
+        if (lane + NB < kb) A[(k0 + lane + NB) + (int64_t)j * ld] = Xs[cc * LDP + lane + NB];
+      }
     }
+    if (warp == 1 && sl == task) stamp(11);
+    // further slices of this CTA (wide launches only): the factored block is reused, each column warp repeats its
+    // look-ahead update and solve on the next 8 columns it owns; everything is warp-local
+    sl += nAc;
+    if (sl >= nA) break;
+    jb = rest0 + sl * SLICE + (warp - 1) * CWID;
+    if (jb >= dim) break;
+    __syncwarp();
+    {
+      const int j = jb + g;
+#pragma unroll
+      for (int ks = 0; ks < 16; ++ks) qf[ks] = (p >= 1 && j < dim) ? A[(k0 - PW + ks * 4 + t) + (int64_t)j * ld] : 0.0;
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int i = mt * 8 + g, jj = jb + 2 * t + e;
+          b0[mt][e] = (jj < dim && i < kb) ? A[(k0 + i) + (int64_t)jj * ld] : 0.0;
+        }
+      double acc[8][2];
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt) acc[mt][0] = acc[mt][1] = 0.0;
+      if (p >= 1) {
+#pragma unroll
+        for (int ks = 0; ks < 16; ++ks)
+#pragma unroll
+          for (int mt = 0; mt < 8; ++mt) dmma884(acc[mt][0], acc[mt][1], Ps[(mt * 8 + g) * LDP + ks * 4 + t], qf[ks]);
+      }
+#pragma unroll
+      for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) Xs[(2 * t + e) * LDP + mt * 8 + g] = b0[mt][e] - acc[mt][e];
+    }
+    __syncwarp();
   }
-  if (warp == 1) stamp(11);
 }
 
 // Step np of a clique (after its last panel): Schur complement C -= S^T S with K = F on 64 x 64 DMMA tiles, and the last

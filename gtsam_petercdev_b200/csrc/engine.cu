@@ -163,6 +163,7 @@ struct LevelSched {
   int64_t zero_blocks = 0;
   std::vector<int64_t> step_begin;  // per panel step 0..max_np: range of the compact task list (panel-step tasks)
   std::vector<int32_t> step_count;
+  std::vector<int32_t> step_spc;    // per step: column slices per role-A CTA of that launch
   std::vector<int64_t> schur_begin; // per step: tile tasks of the cliques whose Schur-complement step this is
   std::vector<int32_t> schur_count;
   // ordered hand-over: the Schur-step tasks of a step are cut into one launch per rank among same-level siblings that hand
@@ -935,15 +936,31 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
       const int max_np = (L.max_F + PW - 1) / PW;
       for (int sidx = 0; sidx <= max_np; ++sidx) {
         L.step_begin.push_back((int64_t)e->step_tasks_list.size());
-        // role-A slices of every clique first (critical path), then the tile tasks
+        // Column slices per role-A CTA: one, unless the launch would then hold more role-A CTAs than the machine has SMs
+        // (one such CTA per SM): every role-A CTA factors its front's diagonal block by itself, so a second wave repeats
+        // that work, while a CTA that walks several slices pays for it once.
+        static const int sm_target = getenv("GTB_ROLE_A_CTAS") ? atoi(getenv("GTB_ROLE_A_CTAS")) : 148;
+        int spc = 1;
+        for (; spc < 16; ++spc) {
+          int64_t ctas = 0;
+          for (int64_t q = L.large_begin; q < en; ++q) {
+            const int32_t c = lc[q];
+            const int F = p.F[c], dim = F + p.S[c] + 1;
+            if (sidx >= (F + PW - 1) / PW) continue;
+            ctas += role_a_ctas(dim, sidx * PW + std::min(PW, F - sidx * PW), spc);
+          }
+          if (ctas <= sm_target) break;
+        }
+        L.step_spc.push_back(spc);
+        // role-A CTAs of every clique first (critical path), then the tile tasks
         for (int pass = 0; pass < 2; ++pass)
           for (int64_t q = L.large_begin; q < en; ++q) {
             const int32_t c = lc[q];
             const int F = p.F[c], dim = F + p.S[c] + 1, np_c = (F + PW - 1) / PW;
             if (sidx >= np_c) continue;
-            const int n = step_tasks(F, dim, sidx);
+            const int n = step_tasks(F, dim, sidx, spc);
             const int k0 = sidx * PW, kb = std::min(PW, F - k0);
-            const int nA = (dim - k0 - kb + SLICE - 1) / SLICE;
+            const int nA = role_a_ctas(dim, k0 + kb, spc);
             const int lo = pass == 0 ? 0 : nA, hi = pass == 0 ? nA : n;
             for (int t = lo; t < hi; ++t) e->step_tasks_list.push_back(StepTask{c, t});
           }
@@ -955,9 +972,9 @@ static void build_phase(Engine* e, int ph, std::vector<int32_t>& lc) {
             const int F = p.F[c], dim = F + p.S[c] + 1;
             if (sidx >= (F + PW - 1) / PW) continue;
             const int k0 = sidx * PW, kb = std::min(PW, F - k0);
-            ++nf; na += (dim - k0 - kb + SLICE - 1) / SLICE; maxdim = std::max(maxdim, dim); maxF = std::max(maxF, F);
+            ++nf; na += role_a_ctas(dim, k0 + kb, spc); maxdim = std::max(maxdim, dim); maxF = std::max(maxF, F);
           }
-          fprintf(stderr, "step level=%d p=%d fronts=%d roleA=%d tiles=%d maxF=%d maxdim=%d\n", (int)l, sidx, nf, na,
+          fprintf(stderr, "step level=%d p=%d fronts=%d roleA=%d (x%d slices) tiles=%d maxF=%d maxdim=%d\n", (int)l, sidx, nf, na, spc,
                   (int)L.step_count.back() - na, maxF, maxdim);
         }
         L.schur_begin.push_back((int64_t)e->step_tasks_list.size());
@@ -1664,7 +1681,8 @@ static void factorize_levels(Engine* e, const ElimDev& E, int phase) {
                                      (const int32_t*)e->d_gather_child.p, (const int64_t*)e->d_gather_smap_off.p, (const int32_t*)e->d_smap.p));
     for (size_t s = 0; s < L.step_count.size(); ++s) {
       if (L.step_count[s] > 0)
-        LAUNCH(e, K_STEP, launch_pdl(front_step_kernel, L.step_count[s], 256, kStepSmem, st, E, e->d_step_tasks.p + L.step_begin[s], (int)s));
+        LAUNCH(e, K_STEP, launch_pdl(front_step_kernel, L.step_count[s], 256, kStepSmem, st, E, e->d_step_tasks.p + L.step_begin[s], (int)s,
+                                     (int)L.step_spc[s]));
       for (const LevelSched::Run& run : L.schur_runs[s])
         LAUNCH(e, K_SCHUR, launch_pdl(schur_step_kernel, run.count, 256, kStepSmemTile, st, E, e->d_step_tasks.p + run.begin));
     }
@@ -2282,7 +2300,7 @@ gtb_status gtb_schedule_check(const gtb_engine* e, int64_t* out8) {
           for (int64_t k = L.large_begin; k < L.large_begin + L.n_large; ++k) {
             const int32_t c = e->sched_lists[k];
             const int np_c = (p.F[c] + PW - 1) / PW;
-            if (sidx < np_c) want += step_tasks(p.F[c], dim_of(c), sidx);
+            if (sidx < np_c) want += step_tasks(p.F[c], dim_of(c), sidx, L.step_spc[sidx]);
             if (sidx == np_c) want_schur_min += step_tasks(p.F[c], dim_of(c), sidx);
           }
           if (want != L.step_count[sidx]) return fail("panel-step task count at level " + std::to_string(l));

@@ -37,9 +37,17 @@ if os.environ.get("GTB_DEBUG") and int(os.environ["GTB_DEBUG"]) & 8:
     b = list(buf)
     print("role A cycle stamps (root, p=2, slice 0), warp 0, cycles from kernel entry:")
     print("  loads + sync               %7d" % (b[1] - b[0]))
-    print("  D -= PtP + sync            %7d" % (b[2] - b[1]))
+    print("  D -= PtP + sync            %7d   (tile-pair indices %d, DMMA loop %d, write-back %d, barrier %d)" % (
+        b[2] - b[1], b[4] - b[1], b[6] - b[4], b[7] - b[6], b[2] - b[7]))
     print("  first 8 x 8 block factored %7d" % (b[3] - b[2]))
     print("  64 x 64 Cholesky + inverses%7d" % (b[5] - b[2]))
     print("column warp 1: X update done at %d, released at %d, solve %d, store %d (cycles from kernel start)" % (
         b[8] - b[0], b[9] - b[0], b[10] - b[9], b[11] - b[10]))
     print("schur step of the root's last child: tile 0 %d cycles (%d ns), tile 77 %d cycles (%d ns)" % (b[12], b[13], b[14], b[15]))
+
+if os.environ.get("GTB_TRACE_STEPS"):
+    print("front_step launches in order (ms):")
+    print(" ".join("%.3f" % x for x in fs))
+    ss = ms[[k for k, n in enumerate(names) if n == "schur_step"]]
+    print("schur_step launches in order (ms):")
+    print(" ".join("%.3f" % x for x in ss))
