@@ -1003,7 +1003,7 @@ template <int MODE = 0>
 __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int dim, int r0, int c0, int re, int ka,
                                             int kend, double* sm, const int32_t* __restrict__ pm = nullptr,
                                             double* __restrict__ PA = nullptr, int pld = 0, int F = 0, bool add_c = false,
-                                            int* flag = nullptr, int turn = 0) {
+                                            int* flag = nullptr, int turn = 0, int dbg = 0) {
   double* Xs = sm;                        // [kStages][TW * LDT]
   double* Ys = sm + kStages * TW * LDT;   // [kStages][TW * LDT]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -1066,7 +1066,7 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
         }
       }
   }
-  for (int ch = 0; ch < nchunk; ++ch) {
+  for (int ch = 0; ch < ((dbg & 64) ? 1 : nchunk); ++ch) {   // GTB_DEBUG=64 (timing experiment): one K chunk only
     cp_async_wait<kStages - 2>();   // chunk ch has landed (for this thread's copies)
     __syncthreads();                // ... and for everybody's; also: everybody is done with the buffer refilled below
     if (ch + kStages - 1 < nchunk) fetch(ka + (ch + kStages - 1) * NB, (ch + kStages - 1) % kStages);
@@ -1087,6 +1087,7 @@ __device__ __forceinline__ void tile_update(double* __restrict__ A, int ld, int 
     }
   }
   cp_async_wait<0>();
+  if (dbg & 32) return;   // GTB_DEBUG=32 (timing experiment, wrong results): no epilogue
   // Ordered K split: the slices of a tile hand their partial products over one after the other (slice 0 first): a slice
   // waits until the tile's flag says that its predecessor's adds are visible.  The CTAs of earlier slices come earlier in
   // the task list, so they are resident (or done) whenever a later slice spins.
@@ -1640,11 +1641,11 @@ __global__ void __launch_bounds__(256, 2) schur_step_kernel(ElimDev E, const Ste
     if (ci.flags & kCliqueFuseUp) {
       const CliqueDev cp = E.cliques[ci.parent];
       tile_update<2>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm, E.pmap + ci.pmap_off, E.arena + cp.front_off, cp.ld, F,
-                     slice == 0, flag, E.epoch32 + slice);
+                     slice == 0, flag, E.epoch32 + slice, E.debug);
     } else if (nsplit <= 1) {
-      tile_update<0>(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm);
+      tile_update<0>(A, ld, dim, F + ty * TW, F + tx * TW, dim, 0, F, sm, nullptr, nullptr, 0, 0, false, nullptr, 0, E.debug);
     } else {
-      tile_update<1>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm, nullptr, nullptr, 0, 0, false, flag, E.epoch32 + slice);
+      tile_update<1>(A, ld, dim, F + ty * TW, F + tx * TW, dim, ka, kend, sm, nullptr, nullptr, 0, 0, false, flag, E.epoch32 + slice, E.debug);
     }
   }
   if (probe) {
