@@ -33,6 +33,7 @@ WORKLOADS = {
     "c2": "C2 sphere2500-shape Pose3 graph (2,500 Pose3, 4,949 BetweenFactor<Pose3> + prior)",
     "c1": "C1 M3500-shape Pose2 graph (3,500 Pose2, 5,450 BetweenFactor<Pose2> + prior)",
     "c4": "C4 Venice-scale synthetic BA (1,778 cams, ~993,000 points, ~5M GeneralSFMFactor<Cal3Bundler> + 2 priors)",
+    "c2_real": "C2 on the shipped examples/Data/sphere2500.txt (2,500 Pose3, 4,949 BetweenFactor<Pose3> + prior; dead-reckoning initial values)",
     "c5": "C5 ISAM2 on City10000 (examples/ISAM2_City10000.cpp schedule: one update per measurement line, relinearizeThreshold 0.01, relinearizeSkip 1)",
 }
 CITY_FULL = os.path.join(ROOT, "tests", "golden", "data", "T1_city10000_04.txt")
@@ -49,6 +50,8 @@ def make_problem(workload):
         return datasets.m3500_shape()
     if workload == "c4":
         return datasets.venice_shape()
+    if workload == "c2_real":
+        return datasets.sphere2500_file()
     raise SystemExit(f"unknown workload {workload}")
 
 
@@ -57,6 +60,8 @@ def ordering_for(problem, workload, name):
     oracle/_ref/ref_tool, committed as permutations under tests/golden/): ordering is an input of the path."""
     if name in ("schur", "natural", "nested_dissection"):
         return name
+    if workload == "c2_real":
+        return problem.variables()[0][np.load(os.path.join(ROOT, "tests", "golden", "fullsize__c2_real_metis.npz"))["ordering_" + name]]
     f = os.path.join(ROOT, "tests", "golden", {"c3": "ladybug_shape", "c2": "sphere_shape", "c1": "m3500_shape", "c4": "venice_shape"}[workload] + "_orderings.npz")
     perm = np.load(f)[name]
     return problem.variables()[0][perm]
@@ -168,7 +173,7 @@ def run_reference(args, rank, world):
     pf, of = os.path.join(tmp, "p.gtb"), os.path.join(tmp, "o.gtb")
     p.save(pf)
     # bounded sample: at ~10 s per C3 step the run is capped to what fits in a few minutes
-    est = {"c3": 11.0, "c2": 0.2, "c1": 0.1, "c4": 120.0}[args.workload]
+    est = {"c3": 11.0, "c2": 0.2, "c2_real": 0.2, "c1": 0.1, "c4": 120.0}[args.workload]
     steps = max(1, min(args.steps, int(240 / est)))
     warm = 1 if (args.warmup + steps) * est > 240 else args.warmup
     sample = f"{steps} full LM inner iterations of the whole workload after {warm} warm-up (asked {args.steps}/{args.warmup})"

@@ -362,6 +362,32 @@ def read_g2o(path, is3d=False, kernel="none"):
     return _read_native("gtb_dataset_read_g2o", os.fsencode(path), int(bool(is3d)), LOSSES.index(kernel))
 
 
+def sphere2500_file(path=None):
+    """C2 on the dataset the reference ships (examples/Data/sphere2500.txt, a copy travels under tests/golden/data/).  The file
+    holds TORO EDGE3 records only (no vertices): the factors come from the native reader (bit-exact against the reference's
+    load3D, tests/test_ingest_sweep_cpu.py); the initial values are dead reckoning along the odometry edges (i, i + 1) from the
+    identity, which is what the reference's own example for this file does (matlab/gtsam_examples/Pose3SLAMExample_graph.m:
+    load3D(..., smart = true) chains the odometry); pose 0 is held by the prior of examples/Pose3SLAMExample_g2o.cpp:50-53,
+    noiseModel::Diagonal::Variances(1e-6 x3, 1e-4 x3)."""
+    if path is None:
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "data", "sphere2500.txt")
+    p = read_g2o(path, is3d=True)
+    fk, z = p.a["between3_keys"], p.a["between3_z"]
+    keys = np.unique(fk)
+    pose = {int(keys[0]): (np.eye(3), np.zeros(3))}
+    for (a, b), zz in zip(fk, z):
+        a, b = int(a), int(b)
+        if b == a + 1 and a in pose and b not in pose:
+            Ra, ta = pose[a]
+            pose[b] = (Ra @ zz[:9].reshape(3, 3), ta + Ra @ zz[9:])
+    if len(pose) != len(keys):
+        raise DatasetError("sphere2500: the odometry chain does not reach every pose")
+    rows = np.stack([np.concatenate([pose[int(k)][0].reshape(9), pose[int(k)][1]]) for k in keys])
+    p.set_variables("pose3", keys, rows)
+    p.set_factors("prior3", keys[:1], rows[:1], 5, np.array([[1e-6, 1e-6, 1e-6, 1e-4, 1e-4, 1e-4]]))   # 5 = GTB_NOISE_DIAG_VARIANCES
+    return p
+
+
 def read_bal_native(path):
     """SfmData::FromBalFile + the projection factors of SFMExample_bal (gtb_dataset_read_bal) -> Problem."""
     return _read_native("gtb_dataset_read_bal", os.fsencode(path))

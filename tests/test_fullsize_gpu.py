@@ -80,3 +80,34 @@ def test_solution_does_not_depend_on_the_ordering(workload, other):
     assert abs(lin1_a - lin1_b) <= 1e-9 * abs(lin1_a)
     assert abs(err_a - err_b) <= 1e-9 * err_a
     assert abs(err_b - REF[workload]) <= 1e-9 * REF[workload]
+
+
+def test_c2_on_the_shipped_sphere2500():
+    """C2 on the dataset the reference ships: examples/Data/sphere2500.txt through the native reader, the
+    reference's own METIS ordering for that graph, one damped trial against the unmodified reference
+    (tests/golden/fullsize__c2_real_metis.npz by tests/golden/make_c2_real_golden.py).  Same bars as the synthetic twin."""
+    import make_golden
+    from gtsam_petercdev_b200 import datasets
+    g = dict(np.load(os.path.join(GOLDEN, "fullsize__c2_real_metis.npz")))
+    p = datasets.sphere2500_file()
+    assert make_golden.problem_digest(p) == str(g["digest"]), "the native reader / dead reckoning drifted from the fixture"
+    keys = p.variables()[0]
+
+    def trial(order):
+        e = Engine(p, device=0)
+        e.set_ordering(keys[g["ordering_" + order]])
+        err0 = e.error()
+        e.linearize(); e.factorize(LAM); e.backsolve()
+        lin0, lin1 = e.linear_errors()
+        e.retract()
+        return err0, lin0, lin1, e.error(1), e.delta()
+    err0, lin0, lin1, err1, delta = trial("metis")
+    check_delta("fullsize c2_real (sphere2500.txt) metis", delta, g["delta"], g["delta_star"],
+                f"   trial error rel = {abs(err1 - g['error1'][0]) / g['error1'][0]:.2e}")
+    assert abs(err0 - g["error0"][0]) <= 1e-12 * g["error0"][0]
+    assert abs(lin0 - g["linear_error0"][0]) <= 1e-12 * g["linear_error0"][0]
+    assert abs(lin1 - g["linear_error1"][0]) <= 1e-8 * g["linear_error0"][0]
+    assert abs(err1 - g["error1"][0]) <= 1e-9 * g["error1"][0]
+    # the other ordering of the reference gives the same step
+    _, _, _, err1c, deltac = trial("colamd")
+    assert _rel(deltac, delta) < 1e-8 and abs(err1c - err1) <= 1e-9 * err1
