@@ -20,6 +20,10 @@
 
 namespace gtsam {
 
+using device_detail::Bucket;
+using device_detail::PackedGraph;
+using device_detail::PackedValues;
+
 namespace {
 
 typedef PinholeCamera<Cal3Bundler> Camera;
@@ -52,15 +56,6 @@ Pose3 pose3From(const double* p) {
   R << p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8];
   return Pose3(Rot3(R), Point3(p[9], p[10], p[11]));
 }
-
-struct Bucket {
-  std::vector<uint64_t> keys;
-  std::vector<double> z, noise;
-  std::vector<int32_t> kind;
-  int loss = -1;       // -1: no factor seen yet; GTB_LOSS_*
-  double lossK = 0;
-  size_t n = 0;
-};
 
 // m-estimator of a Robust model -> (GTB_LOSS_*, parameter)  (linear/LossFunctions.h)
 std::pair<int, double> lossOf(const noiseModel::mEstimator::Base::shared_ptr& est) {
@@ -172,28 +167,36 @@ DeviceProblem::~DeviceProblem() {
 
 // Values -> one contiguous array per type (replaces the map lookups + dynamic_cast + copy of every Values::at,
 // nonlinear/Values-inl.h:261-272)
-void DeviceProblem::uploadValues(const Values& v) {
-  std::vector<double> st[GTB_NUM_VTYPES];
-  std::vector<std::pair<Key, size_t>> all;
+PackedValues device_detail::packValues(const Values& v) {
+  PackedValues out;
   for (const auto& kv : v) {
     int t;
     if (auto p = dynamic_cast<const GenericValue<Pose2>*>(&kv.value)) {
       t = GTB_POSE2;
-      st[t].insert(st[t].end(), {p->value().x(), p->value().y(), p->value().theta()});
+      out.state[t].insert(out.state[t].end(), {p->value().x(), p->value().y(), p->value().theta()});
     } else if (auto p3 = dynamic_cast<const GenericValue<Pose3>*>(&kv.value)) {
       t = GTB_POSE3;
-      appendPose3(st[t], p3->value());
+      appendPose3(out.state[t], p3->value());
     } else if (auto pc = dynamic_cast<const GenericValue<Camera>*>(&kv.value)) {
       t = GTB_CAMERA;
-      appendCamera(st[t], pc->value());
+      appendCamera(out.state[t], pc->value());
     } else if (auto pp = dynamic_cast<const GenericValue<Point3>*>(&kv.value)) {
       t = GTB_POINT3;
-      st[t].insert(st[t].end(), {pp->value().x(), pp->value().y(), pp->value().z()});
+      out.state[t].insert(out.state[t].end(), {pp->value().x(), pp->value().y(), pp->value().z()});
     } else {
       throw std::invalid_argument("gtsam_b200: unsupported Value type for key " + DefaultKeyFormatter(kv.key));
     }
-    keys_[t].push_back(kv.key);
-    all.emplace_back(kv.key, (size_t)kTangent[t]);
+    out.keys[t].push_back(kv.key);
+  }
+  return out;
+}
+
+void DeviceProblem::uploadValues(const Values& v) {
+  const PackedValues pv = device_detail::packValues(v);
+  std::vector<std::pair<Key, size_t>> all;
+  for (int t = 0; t < GTB_NUM_VTYPES; ++t) {
+    keys_[t] = pv.keys[t];
+    for (Key k : pv.keys[t]) all.emplace_back(k, (size_t)kTangent[t]);
   }
   std::sort(all.begin(), all.end());
   for (const auto& a : all) {
@@ -203,19 +206,18 @@ void DeviceProblem::uploadValues(const Values& v) {
   for (int t = 0; t < GTB_NUM_VTYPES; ++t)
     if (!keys_[t].empty()) {
       std::vector<uint64_t> k(keys_[t].begin(), keys_[t].end());
-      check(gtb_set_variables(eng_, t, (int64_t)k.size(), k.data(), st[t].data()));
+      check(gtb_set_variables(eng_, t, (int64_t)k.size(), k.data(), pv.state[t].data()));
     }
 }
 
 // NonlinearFactorGraph -> one table per factor type, discovered once by dynamic_cast (seam S5)
-void DeviceProblem::uploadGraph(const NonlinearFactorGraph& g) {
-  Bucket b[GTB_NUM_BUCKETS];
-  std::vector<int64_t> order;
-  graphSlots_.clear();
+PackedGraph device_detail::packGraph(const NonlinearFactorGraph& g) {
+  PackedGraph out;
+  Bucket* b = out.bucket;
   for (const auto& f : g) {
     int bi = -1;
     if (!f) {
-      graphSlots_.push_back(Slot{-1, 0});
+      out.slots.emplace_back(-1, 0);
       continue;
     }
     if (auto q = std::dynamic_pointer_cast<BetweenFactor<Pose2>>(f)) {
@@ -256,10 +258,23 @@ void DeviceProblem::uploadGraph(const NonlinearFactorGraph& g) {
     } else {
       throw std::invalid_argument("gtsam_b200: factor type without a device kernel (there is no CPU fallback)");
     }
-    graphSlots_.push_back(Slot{bi, b[bi].n});
-    order.push_back(bi);
-    order.push_back((int64_t)b[bi].n);
+    out.slots.emplace_back(bi, b[bi].n);
     b[bi].n++;
+  }
+  return out;
+}
+
+void DeviceProblem::uploadGraph(const NonlinearFactorGraph& g) {
+  const PackedGraph pg = device_detail::packGraph(g);
+  const Bucket* b = pg.bucket;
+  std::vector<int64_t> order;
+  graphSlots_.clear();
+  for (const auto& s : pg.slots) {
+    graphSlots_.push_back(Slot{s.first, s.second});
+    if (s.first >= 0) {
+      order.push_back(s.first);
+      order.push_back((int64_t)s.second);
+    }
   }
   bucketKeys_.assign(GTB_NUM_BUCKETS, {});
   for (int bi = 0; bi < GTB_NUM_BUCKETS; ++bi) {
@@ -273,6 +288,20 @@ void DeviceProblem::uploadGraph(const NonlinearFactorGraph& g) {
   check(gtb_set_graph_order(eng_, (int64_t)order.size() / 2, order.data()));
 }
 
+Values device_detail::unpackValues(int t, const std::vector<Key>& keys, const double* rows) {
+  Values out;
+  for (size_t i = 0; i < keys.size(); ++i) {
+    const double* p = rows + i * kStateOut[t];
+    switch (t) {
+      case GTB_POSE2: out.insert(keys[i], Pose2(Rot2::fromCosSin(p[0], p[1]), Point2(p[2], p[3]))); break;
+      case GTB_POSE3: out.insert(keys[i], pose3From(p)); break;
+      case GTB_CAMERA: out.insert(keys[i], Camera(pose3From(p), Cal3Bundler(p[12], p[13], p[14], p[15], p[16]))); break;
+      default: out.insert(keys[i], Point3(p[0], p[1], p[2])); break;
+    }
+  }
+  return out;
+}
+
 Values DeviceProblem::downloadValues(int which) const {
   Values out;
   for (int t = 0; t < GTB_NUM_VTYPES; ++t) {
@@ -280,15 +309,7 @@ Values DeviceProblem::downloadValues(int which) const {
     if (!n) continue;
     std::vector<double> s(n * kStateOut[t]);
     check(gtb_get_variables(eng_, t, which, s.data()));
-    for (size_t i = 0; i < n; ++i) {
-      const double* p = s.data() + i * kStateOut[t];
-      switch (t) {
-        case GTB_POSE2: out.insert(keys_[t][i], Pose2(Rot2::fromCosSin(p[0], p[1]), Point2(p[2], p[3]))); break;
-        case GTB_POSE3: out.insert(keys_[t][i], pose3From(p)); break;
-        case GTB_CAMERA: out.insert(keys_[t][i], Camera(pose3From(p), Cal3Bundler(p[12], p[13], p[14], p[15], p[16]))); break;
-        default: out.insert(keys_[t][i], Point3(p[0], p[1], p[2])); break;
-      }
-    }
+    out.insert(device_detail::unpackValues(t, keys_[t], s.data()));
   }
   return out;
 }

@@ -26,6 +26,30 @@
 
 namespace gtsam {
 
+/// Packing of the reference's containers into the flat tables of the C ABI, shared by the batch optimizers and DeviceISAM2.
+namespace device_detail {
+struct PackedValues {
+  std::vector<Key> keys[GTB_NUM_VTYPES];       // per type, in Values order
+  std::vector<double> state[GTB_NUM_VTYPES];   // rows as gtb_set_variables takes them
+};
+struct Bucket {
+  std::vector<uint64_t> keys;
+  std::vector<double> z, noise;
+  std::vector<int32_t> kind;
+  int loss = -1;       // -1: no factor seen yet; GTB_LOSS_*
+  double lossK = 0;
+  size_t n = 0;
+};
+struct PackedGraph {
+  Bucket bucket[GTB_NUM_BUCKETS];
+  std::vector<std::pair<int, size_t>> slots;   // graph position -> (bucket, index); bucket < 0: null factor
+};
+PackedValues packValues(const Values& v);
+PackedGraph packGraph(const NonlinearFactorGraph& g);
+/// rows as gtb_get_variables returns them (POSE2: cos, sin, x, y) -> Values
+Values unpackValues(int vtype, const std::vector<Key>& keys, const double* rows);
+}  // namespace device_detail
+
 /// NonlinearFactorGraph + Values packed into the engine's flat tables, and results unpacked into GTSAM objects.
 class DeviceProblem {
  public:

@@ -22,8 +22,11 @@
 
 #include <cmath>
 #include <cstdio>
+#include <fstream>
+#include <sstream>
 #include <iostream>
 
+#include "DeviceISAM2.h"
 #include "DeviceOptimizers.h"
 
 #include <gtsam/nonlinear/internal/LevenbergMarquardtState.h>
@@ -188,6 +191,68 @@ int main(int argc, char** argv) {
       }
       report("solve() throws IndeterminantLinearSystemException where the reference does", threw == threwRef,
              std::string("device ") + (threw ? "threw" : "did not throw") + ", reference " + (threwRef ? "threw" : "did not throw"));
+    }
+    // ---- ISAM2: the schedule of examples/ISAM2_City10000.cpp:62-134 on the stock gtsam::ISAM2 and on DeviceISAM2 ----
+    {
+      std::ifstream in(data + "/T1_city10000_04_head1264.txt");
+      ISAM2Params params;
+      params.optimizationParams = ISAM2GaussNewtonParams(0.0);
+      params.relinearizeThreshold = 0.01;
+      params.relinearizeSkip = 1;
+      ISAM2 stock(params);
+      DeviceISAM2 dev(params);
+      const auto priorModel = noiseModel::Diagonal::Sigmas(Vector3(1e-4, 1e-4, 1e-4));
+      const auto odoModel = noiseModel::Diagonal::Sigmas(Vector3(1.0 / 30.0, 1.0 / 30.0, 1.0 / 100.0));
+      const auto loopModel = noiseModel::Diagonal::Sigmas(Vector3(10.0, 10.0, 10.0));
+      NonlinearFactorGraph fresh;
+      Values freshValues;
+      freshValues.insert(Symbol('x', 0), Pose2(0, 0, 0));
+      fresh.addPrior<Pose2>(Symbol('x', 0), Pose2(0, 0, 0), priorModel);
+      stock.update(fresh, freshValues);
+      dev.update(fresh, freshValues);
+      Values est = stock.calculateEstimate(), estDev = dev.calculateEstimate();
+      double worst = 0;
+      size_t updates = 0, relinStock = 0, relinDev = 0;
+      std::string line;
+      while (updates < 400 && std::getline(in, line)) {
+        std::istringstream ls(line);
+        std::string tag;
+        long long from, to, d0, d1, nh;
+        double x, y, th;
+        if (!(ls >> tag >> from >> d0 >> to >> d1 >> nh >> x >> y >> th)) continue;
+        const Pose2 z(x, y, th);
+        fresh.resize(0);
+        freshValues.clear();
+        if (from == to - 1) {
+          // both arms start the new pose from the STOCK estimate, so that they receive identical inputs
+          freshValues.insert(Symbol('x', to), est.at<Pose2>(Symbol('x', from)) * z);
+          fresh.emplace_shared<BetweenFactor<Pose2>>(Symbol('x', from), Symbol('x', to), z, odoModel);
+        } else {
+          fresh.emplace_shared<BetweenFactor<Pose2>>(Symbol('x', from), Symbol('x', to), z, loopModel);
+        }
+        stock.update(fresh, freshValues);
+        const ISAM2Result r = dev.update(fresh, freshValues);
+        relinDev += r.variablesRelinearized;
+        est = stock.calculateEstimate();
+        estDev = dev.calculateEstimate();
+        ++updates;
+        if (updates % 50 == 0 || updates == 400) worst = std::max(worst, valuesDiff(est, estDev));
+      }
+      char buf[200];
+      std::snprintf(buf, sizeof buf, "%zu updates, %zu poses, max |estimate_dev - estimate_ref| = %.2e (bar 1e-9), %zu relinearisations on the device",
+                    updates, dev.size(), worst, relinDev);
+      report("DeviceISAM2 follows gtsam::ISAM2 update by update (City10000 schedule)", updates == 400 && est.size() == estDev.size() && worst < 1e-9, buf);
+      (void)relinStock;
+      // unsupported configurations are refused
+      bool threw = false;
+      try {
+        ISAM2Params dl;
+        dl.optimizationParams = ISAM2DoglegParams();
+        DeviceISAM2 bad(dl);
+      } catch (const std::invalid_argument&) {
+        threw = true;
+      }
+      report("DeviceISAM2 refuses Dogleg parameters", threw, threw ? "std::invalid_argument" : "accepted");
     }
     // ---- unsupported input is rejected loudly (no CPU fallback) ----
     {
