@@ -1,4 +1,4 @@
-"""The oracle of the ISAM2 row (not built on the device yet): the reference's own
+"""The oracle of the ISAM2 row (the device side is tests/test_isam2_gpu.py): the reference's own
 gtsam::ISAM2 driven by oracle/_ref/ref_tool mode=isam2 with the schedule of examples/ISAM2_City10000.cpp:62-134.
 Checked here: the committed fixture against a fresh run of the reference (when it is built in this container),
 its bookkeeping against an independent reading of the input file, the reported error against a numpy restatement, and
