@@ -969,7 +969,7 @@ constexpr int CWID = 8;      // columns per role-A column warp (one DMMA n-tile)
 constexpr int SLICE = 7 * CWID;   // columns per role-A CTA: warp 0 factors the diagonal block, warps 1..7 own 8 columns each
 constexpr int kStepSmemTile = 2 * 3 * TW * LDT * (int)sizeof(double);                   // two operands, 3-deep ring of K-chunks
 // role A: Ps, Ds, Ws (8 x 8 inverses), dinv, flag, warp 0's scratch, then Xs + Ts per column warp
-constexpr int kRoleAWarp0 = 2 * PW * LDP + PW * 12 + PW + 2 + NB * 12;
+constexpr int kRoleAWarp0 = 2 * PW * LDP + PW * 12 + PW + 2;
 constexpr int kRoleAColWarp = CWID * LDP + CWID * 12;
 constexpr int kStepSmemA = (kRoleAWarp0 + 7 * kRoleAColWarp) * (int)sizeof(double);
 constexpr int kStepSmem = kStepSmemA > kStepSmemTile ? kStepSmemA : kStepSmemTile;
@@ -1275,7 +1275,6 @@ __global__ void __launch_bounds__(256) front_step_kernel(ElimDev E, const StepTa
   double* Ws = Ds + PW * LDP;         // Ws[i * 12 + r] = inv(D_bb)(r, i % 8), b = i / 8
   double* dinv = Ws + PW * 12;        // 1 / D(i, i)
   int* s_ok = reinterpret_cast<int*>(dinv + PW);
-  double* T0 = dinv + PW + 2;         // warp 0's scratch for the solve of the off-diagonal block
   double* Xs = sm + kRoleAWarp0 + (warp > 0 ? warp - 1 : 0) * kRoleAColWarp;   // Xs[c * LDP + i]
   double* Ts = Xs + CWID * LDP;                                                 // Ts[c * 12 + ii]
   const bool probe = E.dbg && p == 2 && task == 0 && c == E.dbg_clique && lane == 0;   // GTB_DEBUG=8: cycle stamps
