@@ -8,6 +8,7 @@
 //   GaussNewtonOptimizer::iterate                      nonlinear/GaussNewtonOptimizer.cpp:44-66
 // There is no CPU fallback: every numeric entry point needs a CUDA device.
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cmath>
 #include <cstdio>
@@ -1492,7 +1493,16 @@ static void set_ordering_ids(Engine* e, const std::vector<int32_t>& order) {
     static const double ratio = getenv("GTB_AMALGAMATE") ? atof(getenv("GTB_AMALGAMATE")) : 1.35;
     static const int max_f = getenv("GTB_AMALG_MAXF") ? atoi(getenv("GTB_AMALG_MAXF")) : 512;
     static const int min_s = getenv("GTB_AMALG_MINS") ? atoi(getenv("GTB_AMALG_MINS")) : 512;
+    const auto t0 = std::chrono::steady_clock::now();
     build_plan(e->sym, kDenseMaxDim, &e->rplan, &e->plan, ratio, max_f, min_s);
+    const auto t1 = std::chrono::steady_clock::now();
+    e->has_plan = true;
+    install_plan(e);
+    if (getenv("GTB_PLAN_TIMES"))
+      fprintf(stderr, "plan times: build_plan %.3f ms, install_plan (schedule + upload) %.3f ms\n",
+              std::chrono::duration<double, std::milli>(t1 - t0).count(),
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count());
+    return;
   } catch (const std::runtime_error& ex) {
     throw StatusError(GTB_ERR_INCONSISTENT, ex.what());
   }
@@ -2159,7 +2169,10 @@ gtb_status gtb_set_ordering_builtin(gtb_engine* e, int which) {
     for (int64_t i = 0; i < e->vars[GTB_CAMERA].n; ++i) order.push_back(e->type_var[GTB_CAMERA][i]);
     need((int32_t)order.size() == V, "Schur ordering needs a problem with only cameras and points");
   } else if (which == 2) {
+    const auto t0 = std::chrono::steady_clock::now();
     order = nested_dissection_order(e->sym);
+    if (getenv("GTB_PLAN_TIMES"))
+      fprintf(stderr, "plan times: nested dissection %.3f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     need((int32_t)order.size() == V, "nested dissection lost a variable");
   } else {
     need(false, "unknown builtin ordering");

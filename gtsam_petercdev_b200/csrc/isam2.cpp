@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <unordered_map>
@@ -57,6 +58,13 @@ struct gtb_isam2 {
   std::vector<uint64_t> insertion;       // committed keys in the order they were added
   std::vector<uint64_t> ordering;        // caller's elimination order (may name keys that do not exist yet: skipped)
   bool have_ordering = false;
+  // Without a caller's order: the library's nested dissection, recomputed every reorder_every updates; in between the last one
+  // is kept and the variables added since are eliminated last, in the order they came (the periodic reordering of ISAM,
+  // nonlinear/NonlinearISAM.h:30-36; here it only trades ordering time against a slightly taller tree, the estimate is
+  // order-independent).
+  int32_t reorder_every = 8;
+  std::vector<uint64_t> auto_order;
+  int64_t auto_order_update = 0;
   gtb_engine* eng = nullptr;
   bool have_delta = false;               // eng holds theta, delta and theta (+) delta of the last update
   std::string err;
@@ -146,13 +154,31 @@ gtb_status rebuild(gtb_isam2* s) {
   }
   st = pass(s, gtb_finalize_problem(s->eng), "gtb_finalize_problem");
   if (st != GTB_OK) return st;
-  if (!s->have_ordering) return pass(s, gtb_set_ordering_builtin(s->eng, 2), "gtb_set_ordering_builtin");
-  // the caller's order for the keys it names, then the rest in the order they were added (the newest variables last:
-  // they are the ones the next update touches, cf. the constrained ordering of ISAM2.cpp:301-340)
+  if (!s->have_ordering && (s->auto_order.empty() || s->update_count - s->auto_order_update >= s->reorder_every)) {
+    st = pass(s, gtb_set_ordering_builtin(s->eng, 2), "gtb_set_ordering_builtin");
+    if (st != GTB_OK) return st;
+    // keep an equivalent order for the next updates: the frontal keys of the cliques in post-order
+    int64_t nc = 0, nk = 0, a = 0, b = 0;
+    gtb_plan_sizes(s->eng, &nc, &nk, &a, &b);
+    std::vector<int64_t> nfrontal((size_t)nc), nkeys((size_t)nc);
+    std::vector<uint64_t> keys((size_t)nk);
+    gtb_plan_get(s->eng, nfrontal.data(), nkeys.data(), keys.data(), nullptr);
+    s->auto_order.clear();
+    size_t off = 0;
+    for (int64_t c = 0; c < nc; ++c) {
+      s->auto_order.insert(s->auto_order.end(), keys.begin() + off, keys.begin() + off + nfrontal[c]);
+      off += (size_t)nkeys[c];
+    }
+    s->auto_order_update = s->update_count;
+    return GTB_OK;
+  }
+  // the caller's order (or the last computed one) for the keys it names, then the rest in the order they were added (the
+  // newest variables last: they are the ones the next update touches, cf. the constrained ordering of ISAM2.cpp:301-340)
+  const std::vector<uint64_t>& base = s->have_ordering ? s->ordering : s->auto_order;
   std::vector<uint64_t> order;
   order.reserve(s->insertion.size());
   std::unordered_set<uint64_t> placed;
-  for (uint64_t k : s->ordering)
+  for (uint64_t k : base)
     if (s->known.count(k) && placed.insert(k).second) order.push_back(k);
   for (uint64_t k : s->insertion)
     if (placed.insert(k).second) order.push_back(k);
@@ -169,6 +195,7 @@ gtb_status gtb_isam2_create(int device, double relinearize_threshold, int32_t re
   s->device = device;
   s->threshold = relinearize_threshold;
   s->skip = relinearize_skip;
+  if (const char* v = getenv("GTB_ISAM2_REORDER_EVERY")) s->reorder_every = std::max(1, atoi(v));
   *out = s;
   return GTB_OK;
 }

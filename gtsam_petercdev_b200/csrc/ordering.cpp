@@ -25,22 +25,32 @@ struct Graph {
 
 Graph adjacency(const SymbolicInput& in) {
   const int32_t n = in.n_vars;
-  std::vector<std::pair<int32_t, int32_t>> edges;
-  for (int64_t f = 0; f < in.n_factors; ++f) {
-    if (in.fac_nkeys[f] < 2) continue;
-    const int32_t a = in.fac_var[2 * f], b = in.fac_var[2 * f + 1];
-    if (a == b || a < 0 || b < 0) continue;
-    edges.emplace_back(a, b);
-    edges.emplace_back(b, a);
-  }
-  std::sort(edges.begin(), edges.end());
-  edges.erase(std::unique(edges.begin(), edges.end()), edges.end());
   Graph g;
   g.off.assign(n + 1, 0);
-  for (const auto& e : edges) g.off[e.first + 1]++;
+  auto each_edge = [&](auto&& fn) {
+    for (int64_t f = 0; f < in.n_factors; ++f) {
+      if (in.fac_nkeys[f] < 2) continue;
+      const int32_t a = in.fac_var[2 * f], b = in.fac_var[2 * f + 1];
+      if (a == b || a < 0 || b < 0) continue;
+      fn(a, b);
+      fn(b, a);
+    }
+  };
+  each_edge([&](int32_t a, int32_t) { g.off[a + 1]++; });
   for (int32_t v = 0; v < n; ++v) g.off[v + 1] += g.off[v];
-  g.adj.resize(edges.size());
-  for (size_t i = 0; i < edges.size(); ++i) g.adj[i] = edges[i].second;
+  std::vector<int32_t> raw(g.off[n]);
+  std::vector<int64_t> fill(g.off.begin(), g.off.end() - 1);
+  each_edge([&](int32_t a, int32_t b) { raw[fill[a]++] = b; });
+  // rows ascending and without duplicates (two factors on the same pair of variables), compacted in place
+  g.adj.reserve(raw.size());
+  std::vector<int64_t> off(n + 1, 0);
+  for (int32_t v = 0; v < n; ++v) {
+    std::sort(raw.begin() + g.off[v], raw.begin() + g.off[v + 1]);
+    for (int64_t k = g.off[v]; k < g.off[v + 1]; ++k)
+      if (k == g.off[v] || raw[k] != raw[k - 1]) g.adj.push_back(raw[k]);
+    off[v + 1] = (int64_t)g.adj.size();
+  }
+  g.off.swap(off);
   return g;
 }
 
@@ -100,29 +110,21 @@ struct Dissector {
   // `nodes` is one connected subset, all labelled L
   void dissect(std::vector<int32_t>& nodes, int32_t L) {
     if ((int)nodes.size() <= leaf) return emit_by_degree(nodes, L);
-    // pseudo-peripheral root: start from a variable of least degree, move to a least-degree variable of the last level
-    // while that deepens the structure
+    // pseudo-peripheral root: the variable a breadth-first search from the subset's smallest variable reaches last, once
+    // more from there while that deepens the structure (each pass is one sweep over the subset's edges)
     int32_t root = nodes[0];
-    int best = degree_in(root, L);
-    for (int32_t v : nodes) {
-      const int d = degree_in(v, L);
-      if (d < best || (d == best && v < root)) { best = d; root = v; }
-    }
+    for (int32_t v : nodes) root = std::min(root, v);
     std::vector<int32_t> order;
     std::vector<int64_t> loff;
     int height = -1;
-    for (int it = 0; it < 6; ++it) {
+    for (int it = 0; it < 3; ++it) {
       bfs(root, L, order, loff);
       const int h = (int)loff.size() - 2;   // levels 0 .. h
       clear_levels(order);
       if (h <= height) break;
       height = h;
       int32_t cand = order[loff[h]];
-      int cd = degree_in(cand, L);
-      for (int64_t k = loff[h]; k < loff[h + 1]; ++k) {
-        const int d = degree_in(order[k], L);
-        if (d < cd || (d == cd && order[k] < cand)) { cd = d; cand = order[k]; }
-      }
+      for (int64_t k = loff[h]; k < loff[h + 1]; ++k) cand = std::min(cand, order[k]);
       if (cand == root) break;
       root = cand;
     }
@@ -154,15 +156,11 @@ struct Dissector {
     }
     clear_levels(order);
     for (int32_t v : sep) label[v] = -1;   // out of every subset until it is emitted
-    // connected components of what is left, in order of their smallest variable
-    std::vector<int32_t> rest;
-    rest.reserve(order.size() - sep.size());
-    for (int32_t v : order)
-      if (label[v] == L) rest.push_back(v);
-    std::sort(rest.begin(), rest.end());
+    // connected components of what is left
+    // (seeded in the order of the level structure: deterministic, and the part before the separator comes first)
     std::vector<std::vector<int32_t>> comps;
     std::vector<int32_t> comp_label;
-    for (int32_t s : rest) {
+    for (int32_t s : order) {
       if (label[s] != L) continue;
       const int32_t nl = ++next_label;
       comps.emplace_back();
