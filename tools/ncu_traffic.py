@@ -10,7 +10,8 @@ CLASS = {"front_step_kernel": "front_step", "schur_step_kernel": "schur_step", "
          "point_pair_kernel": "point_schur", "point_diag_kernel": "point_schur",
          "small_front_kernel": "small_front", "large_children_kernel": "large_children", "large_zero_kernel": "large_zero",
          "large_factors_kernel": "large_factors", "backsolve_kernel": "backsolve", "backsolve_gemv_kernel": "backsolve_gemv",
-         "linearize_kernel": "linearize", "error_kernel": "error", "linear_error_kernel": "linear_error"}
+         "linearize_kernel": "linearize", "error_kernel": "error", "linear_error_kernel": "linear_error",
+         "backsolve_points_kernel": "backsolve", "pair_reduce_kernel": "point_schur", "extend_add_kernel": "large_children"}
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
