@@ -58,8 +58,19 @@ def make_problem(workload):
 def ordering_for(problem, workload, name):
     """Ordering keys, or a builtin name.  COLAMD / METIS orderings are the reference's own (computed once by
     oracle/_ref/ref_tool, committed as permutations under tests/golden/): ordering is an input of the path."""
-    if name in ("schur", "natural", "nested_dissection"):
+    if name in ("schur", "natural"):
         return name
+    if name == "nested_dissection":
+        # the library's own ordering (gtb_set_ordering_builtin(2)) as keys, so that the reference arm eliminates in the same order:
+        # computed on a host-only engine, read back as the frontal keys of the cliques in post-order (an equivalent order)
+        from gtsam_petercdev_b200.engine import Engine
+        e = Engine(problem, device=-1)
+        e.set_ordering("nested_dissection")
+        pl = e.plan()
+        starts = np.cumsum(pl["clique_nkeys"]) - pl["clique_nkeys"]
+        keys = np.concatenate([pl["clique_keys"][s0:s0 + f] for s0, f in zip(starts, pl["clique_nfrontal"])])
+        e.close()
+        return keys.astype(np.uint64)
     if workload == "c2_real":
         return problem.variables()[0][np.load(os.path.join(ROOT, "tests", "golden", "fullsize__c2_real_metis.npz"))["ordering_" + name]]
     f = os.path.join(ROOT, "tests", "golden", {"c3": "ladybug_shape", "c2": "sphere_shape", "c1": "m3500_shape", "c4": "venice_shape"}[workload] + "_orderings.npz")
