@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from gtsam_petercdev_b200.isam2 import ISAM2, X, drive_city10000 as drive, read_city10000 as read_city
+from gtsam_petercdev_b200.isam2 import DIAG_SIGMAS, ISAM2, X, drive_city10000 as drive, read_city10000 as read_city
 
 pytestmark = pytest.mark.gpu
 
@@ -106,3 +106,24 @@ def test_relinearize_marked_moves_exactly_the_variables_over_the_threshold():
     assert np.array_equal(after[want], new[want]) and np.array_equal(after[~want], cur[~want])
     with pytest.raises(Exception):
         e.backsolve()                         # the factorisation belongs to the old linearisation point
+
+
+def test_underdetermined_update_raises_and_the_next_one_recovers():
+    """ISAM2::update throws IndeterminantLinearSystemException from the elimination when the gauge is free (after the factors
+    were pushed: they stay in the graph); a later update that fixes the gauge succeeds on the same object."""
+    from gtsam_petercdev_b200.engine import IndeterminantLinearSystemException
+    isam = ISAM2(0.01, 1)
+    isam.add_variables("pose2", [X(0), X(1)], [[0.0, 0.0, 0.0], [1.0, 0.0, 0.0]])
+    isam.add_factors("between2", [[X(0), X(1)]], [[1.0, 0.0, 0.0]], DIAG_SIGMAS, [[0.1, 0.1, 0.05]])
+    with pytest.raises(IndeterminantLinearSystemException) as ei:
+        isam.update()
+    assert ei.value.key in (X(0), X(1))
+    assert isam.count("pose2") == 2
+    with pytest.raises(Exception):
+        isam.calculate_estimate("pose2")          # no solution yet
+    isam.add_factors("prior2", [X(0)], [[0.0, 0.0, 0.0]], DIAG_SIGMAS, [[1e-3, 1e-3, 1e-3]])
+    r = isam.update()
+    assert r["n_factors"] == 2 and r["n_variables"] == 2 and r["variables_relinearized"] == 0
+    est = xyt(isam.calculate_estimate("pose2"))
+    assert np.abs(est - np.array([[0.0, 0.0, 0.0], [1.0, 0.0, 0.0]])).max() < 1e-9
+    isam.close()
