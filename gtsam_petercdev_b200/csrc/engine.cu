@@ -513,7 +513,19 @@ static void set_variables(Engine* e, int vt, int64_t n, const uint64_t* keys, co
     // state refresh (the per-step host -> device copy)
     need(n == v.n, "variable count changed after gtb_finalize_problem");
     if (e->has_device && n) {
-      // convert straight into a pinned staging buffer so that the copy is a real asynchronous DMA
+      // A page-locked caller buffer whose rows need no conversion is copied from where it lies (one DMA, no staging pass over
+      // 4 MB on the host per C3 step).  The caller keeps it unchanged until the next call that synchronises (header).
+      if (kStateIn[vt] == kStateDev[vt] && vt != 0) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, state) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+          CK(cudaMemcpyAsync(e->d_state[e->cur][vt].p, state, v.state.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+          e->linearized = e->factorized = e->solved = e->retracted = false;
+          e->lm_have_error = false;
+          return;
+        }
+        cudaGetLastError();   // (an unregistered pointer is not an error here)
+      }
+      // otherwise: convert straight into a pinned staging buffer so that the copy is a real asynchronous DMA
       if (!e->h_stage[vt]) {
         e->h_stage[vt] = static_cast<double*>(pinned_alloc(v.state.size() * sizeof(double), &e->h_stage_cap[vt]));
         CK(cudaEventCreateWithFlags(&e->stage_ev[vt], cudaEventDisableTiming));

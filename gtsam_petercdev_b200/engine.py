@@ -89,7 +89,9 @@ class Engine:
 
     # ---- problem / plan ---------------------------------------------------------------------------
     def set_state(self, vtype, state):
-        """Per-step host -> device refresh of one variable type (same layout as Problem arrays)."""
+        """Per-step host -> device refresh of one variable type (same layout as Problem arrays).  A page-locked array (e.g. a
+        pinned torch tensor's .numpy()) is copied asynchronously from where it lies: keep it alive and unchanged until the next
+        call that synchronises (trial(), error(), variables() ...)."""
         state = np.ascontiguousarray(state, dtype=np.float64)
         self._ck(self.lib.gtb_set_variables(self.h, vtype, len(state), None, _ptr(state)))
 

@@ -67,7 +67,10 @@ const char* gtb_version(void);
 
 /* ---- problem upload (replaces Values / NonlinearFactorGraph containers) ----- */
 /* Values::insert for n variables of one type.  Calling again with the same n re-uploads the state only
- * (the per-step host->device copy).                                                                      */
+ * (the per-step host->device copy): the rows are converted into a page-locked staging buffer and copied from there, so
+ * `state` may be reused as soon as the call returns -- EXCEPT when `state` itself is page-locked (cudaHostAlloc /
+ * cudaHostRegister) and its rows need no conversion (every type but POSE2): then the copy is enqueued straight from
+ * `state`, which must stay unchanged until the next call that synchronises (gtb_trial, gtb_error, gtb_get_*, ...).   */
 gtb_status gtb_set_variables(gtb_engine* e, int vtype, int64_t n, const uint64_t* keys, const double* state);
 /* NonlinearFactorGraph::push_back of n factors of one bucket; keys is n x (2|1).                         */
 gtb_status gtb_set_factors(gtb_engine* e, int bucket, int64_t n, const uint64_t* keys, const double* z,

@@ -185,3 +185,25 @@ def test_engine_driven_from_another_thread_and_call_order_is_enforced():
     e.accept()
     with pytest.raises(EngineError):
         e.accept()                       # the trial was consumed
+
+
+def test_state_refresh_from_page_locked_memory_is_the_same_copy():
+    """gtb_set_variables copies straight from a page-locked caller buffer (no staging pass) when the rows need no conversion;
+    the result must be the bytes a refresh from pageable memory gives."""
+    import torch
+    p = golden_problem("ba_30_500")
+    e = Engine(p, device=0)
+    e.set_ordering("schur")
+    rng = np.random.default_rng(11)
+    for name, t in (("cam", 2), ("point", 3)):
+        moved = p.a[name] + 1e-3 * rng.normal(size=p.a[name].shape)
+        if name == "cam":
+            moved[:, :9] = p.a[name][:, :9]          # keep the rotations orthonormal
+        e.set_state(t, np.ascontiguousarray(moved))
+        pageable = e.variables(t, 0).copy()
+        err_pageable = e.error(0)
+        e.set_state(t, np.ascontiguousarray(p.a[name]))
+        pinned = torch.from_numpy(np.ascontiguousarray(moved)).pin_memory()
+        e.set_state(t, pinned.numpy())
+        assert np.array_equal(e.variables(t, 0), pageable) and e.error(0) == err_pageable
+        e.set_state(t, np.ascontiguousarray(p.a[name]))
