@@ -135,12 +135,13 @@ def bench_config(args):
 
 
 def source_digest():
-    """SHA-256 over the kernel sources: an ncu traffic file is only quoted for the build it was taken from."""
+    """SHA-256 over the device code (the .cuh files: every kernel lives there): an ncu traffic file is only quoted for the kernels
+    it was taken from.  Host-side files (engine.cu: tables, scheduler, C ABI; the .cpp files) do not change what a launch reads."""
     import hashlib
     h = hashlib.sha256()
     d = os.path.join(ROOT, "gtsam_petercdev_b200", "csrc")
     for f in sorted(os.listdir(d)):
-        if f.endswith((".cu", ".cuh", ".cpp", ".h")):
+        if f.endswith(".cuh"):
             h.update(f.encode())
             h.update(open(os.path.join(d, f), "rb").read())
     return h.hexdigest()[:16]

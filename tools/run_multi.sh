@@ -4,7 +4,7 @@ set -x
 N=$1
 O=gpurun_out/scale
 mkdir -p $O
-python bench.py --no-cpu-baseline --steps 10 --warmup 3 > $O/bench_c3_1gpu_on_${N}gpu_box.json 2> $O/bench_c3_1gpu_on_${N}gpu_box.err
+[ "$N" = "2" ] && python bench.py --no-cpu-baseline --steps 10 --warmup 3 > $O/bench_c3_1gpu_on_${N}gpu_box.json 2> $O/bench_c3_1gpu_on_${N}gpu_box.err
 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N --steps 10 --warmup 3 --no-cpu-baseline > $O/bench_c3_${N}gpu.json 2> $O/bench_c3_${N}gpu.err
 if [ "$2" = "c4" ]; then
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29532 bench.py --gpus $N --steps 5 --warmup 3 --workload c4 --no-cpu-baseline > $O/bench_c4_${N}gpu.json 2> $O/bench_c4_${N}gpu.err
