@@ -110,10 +110,14 @@ struct Dissector {
   // `nodes` is one connected subset, all labelled L
   void dissect(std::vector<int32_t>& nodes, int32_t L) {
     if ((int)nodes.size() <= leaf) return emit_by_degree(nodes, L);
-    // pseudo-peripheral root: the variable a breadth-first search from the subset's smallest variable reaches last, once
-    // more from there while that deepens the structure (each pass is one sweep over the subset's edges)
+    // pseudo-peripheral root: from a variable of least degree to a least-degree variable of the last level of its level
+    // structure, while that deepens the structure (each pass is one sweep over the subset's edges)
     int32_t root = nodes[0];
-    for (int32_t v : nodes) root = std::min(root, v);
+    int best = degree_in(root, L);
+    for (int32_t v : nodes) {   // start from a variable of least degree (ties: smallest id)
+      const int d = degree_in(v, L);
+      if (d < best || (d == best && v < root)) { best = d; root = v; }
+    }
     std::vector<int32_t> order;
     std::vector<int64_t> loff;
     int height = -1;
@@ -124,7 +128,11 @@ struct Dissector {
       if (h <= height) break;
       height = h;
       int32_t cand = order[loff[h]];
-      for (int64_t k = loff[h]; k < loff[h + 1]; ++k) cand = std::min(cand, order[k]);
+      int cd = degree_in(cand, L);
+      for (int64_t k = loff[h]; k < loff[h + 1]; ++k) {
+        const int d = degree_in(order[k], L);
+        if (d < cd || (d == cd && order[k] < cand)) { cd = d; cand = order[k]; }
+      }
       if (cand == root) break;
       root = cand;
     }
