@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -134,11 +135,28 @@ void commit_staged(gtb_isam2* s) {
 }
 
 // A fresh engine holding the whole problem at theta, planned with the current ordering.
+// GTB_ISAM2_TIMES=1: mean host time of the stages of rebuild() every 500 updates (stderr)
+double g_lap[6];
+long g_laps;
+void lap(int k, double& t) {
+  const double n = now_ms();
+  g_lap[k] += n - t;
+  t = n;
+}
+
 gtb_status rebuild(gtb_isam2* s) {
+  static const bool times = getenv("GTB_ISAM2_TIMES") != nullptr;
+  double t = now_ms();
+  if (times && ++g_laps % 500 == 0) {
+    fprintf(stderr, "isam2 rebuild, mean ms over %ld updates: destroy %.3f create %.3f tables %.3f finalize %.3f ordering + plan %.3f\n", g_laps,
+            g_lap[0] / g_laps, g_lap[1] / g_laps, g_lap[2] / g_laps, g_lap[3] / g_laps, g_lap[4] / g_laps);
+  }
   if (s->eng) gtb_destroy(s->eng);
   s->eng = nullptr;
   s->have_delta = false;
+  lap(0, t);
   gtb_status st = gtb_create(s->device, &s->eng);
+  lap(1, t);
   if (st != GTB_OK) return fail(s, st, "gtb_create failed (no CUDA device?)");
   for (int t = 0; t < GTB_NUM_VTYPES; ++t) {
     const VarTable& v = s->vars[t];
@@ -152,8 +170,11 @@ gtb_status rebuild(gtb_isam2* s) {
     st = pass(s, gtb_set_factors(s->eng, b, f.n, f.keys.data(), f.z.data(), f.kind.data(), f.noise.data()), "gtb_set_factors");
     if (st != GTB_OK) return st;
   }
+  lap(2, t);
   st = pass(s, gtb_finalize_problem(s->eng), "gtb_finalize_problem");
+  lap(3, t);
   if (st != GTB_OK) return st;
+  struct PlanLap { double& t; ~PlanLap() { lap(4, t); } } plan_lap{t};
   if (!s->have_ordering && (s->auto_order.empty() || s->update_count - s->auto_order_update >= s->reorder_every)) {
     st = pass(s, gtb_set_ordering_builtin(s->eng, 2), "gtb_set_ordering_builtin");
     if (st != GTB_OK) return st;

@@ -15,6 +15,9 @@
 // The output must be bit-identical to the reference's Bayes tree (tests/test_symbolic.py checks it against
 // oracle dumps for COLAMD, METIS and Schur orderings).
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <stdexcept>
 
 #include "plan.h"
@@ -212,6 +215,14 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
                 int32_t amalg_min_S) {
   const int32_t n = in.n_vars;
   const int64_t M = in.n_factors;
+  static const bool times = getenv("GTB_PLAN_TIMES") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!times) return;
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "  build_plan: %-28s %.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+    t_prev = now;
+  };
   if ((int64_t)in.order.size() != n)
     throw std::runtime_error("ordering must contain every variable exactly once (partial elimination is not supported)");
   std::vector<int32_t> pos_of(n, -1);
@@ -265,6 +276,7 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
     }
   }
 
+  lap("variable index + etree");
   // ---- symbolic elimination: separator of every elimination-tree node ------------------------------
   std::vector<std::vector<int32_t>> sep(n);
   {
@@ -285,6 +297,7 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
     }
   }
 
+  lap("separators");
   // ---- junction tree: merge children into parents ----------------------------------------------------
   std::vector<Cluster> cl(n);
   std::vector<uint8_t> merged_away(n, 0);
@@ -332,8 +345,10 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
   }
 
   // ---- the reference's clique layout, bit-exact -------------------------------------------------------
+  lap("supernodes");
   std::vector<int32_t> clique_exact;
   flatten(in, cl, sep, eparent, P, &clique_exact);
+  lap("flatten (reported plan)");
   if (!N) return;
 
   // ---- relaxed amalgamation for the NUMERIC plan ------------------------------------------------------
@@ -358,6 +373,7 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
     for (int32_t v : sep[j]) Sn[j] += in.var_dim[v];
     area[j] = 0.5 * Fn[j] * (Fn[j] + 1.0) + (double)Fn[j] * (Sn[j] + 1.0);
   }
+  bool any_amalgamated = false;
   if (amalg_ratio > 1.0) {
     for (int32_t j = 0; j < n; ++j) {
       if (merged_away[j] || is_small_front(Fn[j], Fn[j] + Sn[j] + 1)) continue;
@@ -392,13 +408,21 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
       area[j] += area[c];
       Fn[j] += Fn[c];
       merged_away[c] = 1;
+      any_amalgamated = true;
       Cluster().factors.swap(ch.factors);
       Cluster().children.swap(ch.children);
       std::vector<int32_t>().swap(sep[c]);
     }
   }
+  lap("amalgamation");
   std::vector<int32_t> clique_num;
-  flatten(in, cl, sep, eparent, N, &clique_num);
+  if (any_amalgamated) {
+    flatten(in, cl, sep, eparent, N, &clique_num);
+  } else {   // nothing merged (every pose graph): the numeric plan IS the reported one
+    *N = *P;
+    clique_num = clique_exact;
+  }
+  lap("flatten (numeric plan)");
   // members of every numeric clique: reference clique ids in elimination order, with the frontal scalar where each ends
   Plan& q = *N;
   q.orig_off.assign(q.n_cliques + 1, 0);
