@@ -236,7 +236,7 @@ def run_isam2(args, reference_arm):
     the C ABI) over the first --updates lines of City10000, beside the reference's gtsam::ISAM2 on the same lines on this
     host.  A step = one update; value = updates per second over the whole run (wall clock: the update is host-driven)."""
     lines = args.updates
-    cfg = {"workload": WORKLOADS["c5"], "updates": lines, "ordering": "built-in nested dissection, recomputed per update (device arm); "
+    cfg = {"workload": WORKLOADS["c5"], "updates": lines, "ordering": "built-in nested dissection, recomputed every 8 updates (device arm); "
            "constrained COLAMD per update (reference arm)"}
     base = {"metric": "ISAM2 updates/s (City10000 schedule)", "unit": "updates/s", "n_gpus": 1, "higher_is_better": True, "scaling": "n/a",
             "vs_baseline": None, "dtype": "f64", "data": "the reference's examples/Data/T1_city10000_04.txt (first %d lines)" % lines,

@@ -269,7 +269,7 @@ gtb_status gtb_marginal_covariance(gtb_engine* e, int64_t n, const uint64_t* key
  * Usage: stage the new variables and factors (same row layouts as gtb_set_variables / gtb_set_factors; a key may be staged
  * once), then gtb_isam2_update.  Ordering: gtb_isam2_set_ordering gives an elimination order for the variables known so
  * far (the reference computes a constrained COLAMD per update, ISAM2.cpp:301-340; any order gives the same estimate);
- * variables that are not listed are eliminated last in the order they were added.  Without it: the built-in nested dissection (gtb_set_ordering_builtin(2)), recomputed at every update. */
+ * variables that are not listed are eliminated last in the order they were added.  Without it: the built-in nested dissection (gtb_set_ordering_builtin(2)), recomputed every 8 updates (GTB_ISAM2_REORDER_EVERY), the variables added in between eliminated last. */
 typedef struct gtb_isam2 gtb_isam2;
 typedef struct {
   int64_t update_count;            /* ISAM2::update_count_                                            */
