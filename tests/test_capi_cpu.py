@@ -104,3 +104,41 @@ def test_isam2_layer_host_side():
         s.update()
     assert ei.value.status == capi.ERR_KEY_MISSING
     s.close()
+
+
+def test_isam2_layer_plans_every_update_with_a_valid_ordering():
+    """The ordering an ISAM2 update eliminates with -- the library's nested dissection every 8th update, in between the last one
+    with the new variables appended, or the caller's order with the rest appended -- is a permutation of the variables at every
+    update.  Checked on the host: the update stops at the first numeric call (no device), after the plan was built."""
+    import ctypes as C
+    from gtsam_petercdev_b200.engine import EngineError, _ptr
+    from gtsam_petercdev_b200.isam2 import ISAM2, X
+    lib = capi.lib()
+
+    def frontal_keys(s):
+        eng = lib.gtb_isam2_engine(s.h)
+        nc, nk = C.c_int64(), C.c_int64()
+        assert lib.gtb_plan_sizes(eng, C.byref(nc), C.byref(nk), None, None) == capi.OK
+        nf, nkeys = np.zeros(nc.value, dtype=np.int64), np.zeros(nc.value, dtype=np.int64)
+        keys = np.zeros(nk.value, dtype=np.uint64)
+        assert lib.gtb_plan_get(eng, _ptr(nf), _ptr(nkeys), _ptr(keys), None) == capi.OK
+        starts = np.cumsum(nkeys) - nkeys
+        return np.concatenate([keys[a:a + f] for a, f in zip(starts, nf)])
+
+    for given in (False, True):
+        s = ISAM2(0.01, 1, device=-1)
+        if given:
+            s.set_ordering([X(i) for i in (5, 3, 40, 1, 0, 2, 4)])     # names a key that never exists: skipped
+        s.add_variables("pose2", [X(0)], [[0.0, 0.0, 0.0]])
+        s.add_factors("prior2", [X(0)], [[0.0, 0.0, 0.0]])
+        for i in range(1, 21):
+            with pytest.raises(EngineError) as ei:
+                s.update()
+            assert ei.value.status == capi.ERR_NO_DEVICE
+            got = frontal_keys(s)
+            assert sorted(got.tolist()) == [X(k) for k in range(i)], (given, i)
+            s.add_variables("pose2", [X(i)], [[float(i), 0.0, 0.0]])
+            s.add_factors("between2", [[X(i - 1), X(i)]], [[1.0, 0.0, 0.0]])
+            if i % 5 == 0:
+                s.add_factors("between2", [[X(0), X(i)]], [[float(i), 0.0, 0.0]])   # a loop closure
+        s.close()
