@@ -278,22 +278,44 @@ void build_plan(const SymbolicInput& in, int32_t small_max, Plan* P, Plan* N, do
 
   lap("variable index + etree");
   // ---- symbolic elimination: separator of every elimination-tree node ------------------------------
+  // (ascending variable id.  The children's separators are sorted already: the union is built by linear merges onto the few
+  // keys of the node's own factors instead of a sort of the whole set -- separators of a 10,000-pose graph hold hundreds of
+  // variables and the ISAM2 layer plans at every update)
   std::vector<std::vector<int32_t>> sep(n);
   {
     std::vector<int32_t> mark(n, -1);
+    std::vector<int32_t> own, merged;
     for (int32_t j = 0; j < n; ++j) {
       const int32_t v = in.order[j];
       std::vector<int32_t>& s = sep[j];
       mark[v] = j;
+      own.clear();
       for (int32_t g : efactors[j])
         for (int k = 0; k < in.fac_nkeys[g]; ++k) {
           const int32_t u = in.fac_var[2 * (int64_t)g + k];
-          if (mark[u] != j) { mark[u] = j; s.push_back(u); }
+          if (mark[u] != j) { mark[u] = j; own.push_back(u); }
         }
-      for (int32_t c : echildren[j])
-        for (int32_t u : sep[c])
-          if (mark[u] != j) { mark[u] = j; s.push_back(u); }
-      std::sort(s.begin(), s.end());
+      std::sort(own.begin(), own.end());
+      s.swap(own);
+      for (int32_t c : echildren[j]) {
+        const std::vector<int32_t>& cs = sep[c];
+        merged.clear();
+        merged.reserve(s.size() + cs.size());
+        size_t a = 0, b = 0;
+        while (a < s.size() || b < cs.size()) {
+          if (b == cs.size() || (a < s.size() && s[a] < cs[b])) {
+            merged.push_back(s[a++]);
+          } else if (a < s.size() && s[a] == cs[b]) {
+            merged.push_back(s[a++]);
+            ++b;
+          } else {
+            if (cs[b] != v) merged.push_back(cs[b]);
+            ++b;
+          }
+        }
+        s.swap(merged);
+      }
+      own.clear();
     }
   }
 
