@@ -134,7 +134,6 @@ void commit_staged(gtb_isam2* s) {
   }
 }
 
-// A fresh engine holding the whole problem at theta, planned with the current ordering.
 // GTB_ISAM2_TIMES=1: mean host time of the stages of rebuild() every 500 updates (stderr)
 double g_lap[6];
 long g_laps;
@@ -144,6 +143,7 @@ void lap(int k, double& t) {
   t = n;
 }
 
+// A fresh engine holding the whole problem at theta, planned with the current ordering.
 gtb_status rebuild(gtb_isam2* s) {
   static const bool times = getenv("GTB_ISAM2_TIMES") != nullptr;
   double t = now_ms();
@@ -158,10 +158,10 @@ gtb_status rebuild(gtb_isam2* s) {
   gtb_status st = gtb_create(s->device, &s->eng);
   lap(1, t);
   if (st != GTB_OK) return fail(s, st, "gtb_create failed (no CUDA device?)");
-  for (int t = 0; t < GTB_NUM_VTYPES; ++t) {
-    const VarTable& v = s->vars[t];
+  for (int vt = 0; vt < GTB_NUM_VTYPES; ++vt) {
+    const VarTable& v = s->vars[vt];
     if (v.keys.empty()) continue;
-    st = pass(s, gtb_set_variables(s->eng, t, (int64_t)v.keys.size(), v.keys.data(), v.state.data()), "gtb_set_variables");
+    st = pass(s, gtb_set_variables(s->eng, vt, (int64_t)v.keys.size(), v.keys.data(), v.state.data()), "gtb_set_variables");
     if (st != GTB_OK) return st;
   }
   for (int b = 0; b < GTB_NUM_BUCKETS; ++b) {
